@@ -1,0 +1,111 @@
+/* libvistaf — C ABI of the B200-native VISTAF multimodal sensing hot path.
+ *
+ * The reference (rimelq/VISTAF-RoboSkin) has no FFI of its own: its boundary for this path is the
+ * Python module API consumed by Code/multimodal_sensor.py (shape_ftp.main :1428,
+ * force_sensor.depth_map_to_volume_cm3 :93 / predict_force_from_volume :149,
+ * temperature_sensor.main :749).  The Python modules of the same names in this repo bind the entry
+ * points below through ctypes (INTEGRATION.md shows the stub).  Conventions:
+ *   - plain pointers and sizes only; the caller owns every input / output / workspace buffer,
+ *     the library owns only the opaque plan handles;
+ *   - `*_batch` calls take DEVICE pointers and a cudaStream_t (as void*), are asynchronous;
+ *   - `*_host` calls take HOST pointers, stage through the caller-provided device workspace and
+ *     synchronise before returning (used by the drop-in single-pair Python API and the e2e bench);
+ *   - return 0 on success; vistaf_last_error() describes the last failure of the calling process;
+ *   - per-frame soft failures (empty ROI, no carrier peak, phase residues ...) are reported in the
+ *     `status` word of the per-frame record, never through the return code.
+ */
+#ifndef VISTAF_H
+#define VISTAF_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VISTAF_MAX_TERMS 35
+#define VISTAF_MAX_ISO 64
+
+/* per-frame status bits */
+#define VISTAF_ST_EMPTY_ROI        0x001  /* temperature_sensor.py:443  / shape_ftp.py:1677 */
+#define VISTAF_ST_NO_PEAK          0x002  /* temperature_sensor.py:457 */
+#define VISTAF_ST_SATURATED        0x004  /* saturated pixels present: Telea fill of the maps not applied (T10) */
+#define VISTAF_ST_ROTATED_CARRIER  0x008  /* carrier angle != 0: oriented blur ran axis-aligned (T12) */
+#define VISTAF_ST_RESIDUES         0x010  /* phase residues inside the reliable mask: unwrap is path dependent (F10) */
+#define VISTAF_ST_FEW_RELIABLE     0x020  /* < 200 reliable pixels: polynomial detrend skipped (shape_ftp.py:1103) */
+#define VISTAF_ST_SIGN_FLIPPED     0x040  /* auto sign flip taken (shape_ftp.py:1759) */
+#define VISTAF_ST_CONTACT_P95      0x080  /* contact threshold fell back to p95 / p98 (shape_ftp.py:1733-1738) */
+#define VISTAF_ST_BG_FALLBACK      0x100  /* background < 15 % of reliable: detrend on reliable (shape_ftp.py:1744) */
+
+/* StandardScaler -> PolynomialFeatures -> linear model [-> isotonic], temperature_sensor.py:236 */
+typedef struct {
+  int32_t n_features;                 /* 3 (L,a,b) or 4 (L,a,b,gray) */
+  int32_t n_terms;
+  int32_t n_iso;                      /* 0 = no isotonic calibrator */
+  int32_t pad_;
+  double mean[4], scale[4];
+  int32_t powers[VISTAF_MAX_TERMS][4];
+  double coef[VISTAF_MAX_TERMS];
+  double intercept;
+  double iso_x[VISTAF_MAX_ISO], iso_y[VISTAF_MAX_ISO];
+} VistafPolyModel;
+
+/* temperature_sensor.py:34-98 */
+typedef struct {
+  int32_t height, width;
+  double roi_cx, roi_cy, roi_r;       /* outer circle, float64 (temperature_sensor.py:157) */
+  float color_t_min, color_t_max, guard_band, switch_margin, final_t_min, final_t_max;
+  int32_t band_radius, dc_exclusion;
+  float peak_max_dy_frac, illum_sigma;
+  int32_t sat_thresh, sat_dilate;
+  int32_t close_kx, close_ky, open_kx, open_ky;
+  float chroma_min;
+  int32_t support_dilate;
+  float sigma_across, sigma_along;
+  VistafPolyModel color_model, wide_model;
+  int32_t lab_gamma[256];             /* OpenCV 8-bit BGR2Lab tables (tools/make_lab_lut.py) */
+  int32_t lab_cbrt[3072];
+} VistafTempParams;
+
+typedef struct {
+  float mean_C, median_C, std_C, min_C, max_C;   /* multimodal_sensor.py:555-567 */
+  int32_t valid_pixels;
+  int32_t peak_x, peak_y;                        /* carrier peak, fftshift-ed pixel coordinates */
+  float phi0, mean_gray_a, mean_gray_b, median_gray;
+  int32_t sat_pixels, roi_eff_pixels, dark_pixels, color_ok_pixels;
+  int32_t status;
+  int32_t pad_[3];
+} VistafTempRecord;                               /* 80 bytes */
+
+typedef struct {
+  float* fused;        /* [B][H][W]  temperature_map_fused  (NaN outside ROI) */
+  float* final_map;    /* [B][H][W]  temperature_map_final */
+  uint8_t* sat;        /* [B][H][W]  0/1 masks; any may be NULL */
+  uint8_t* dark;
+  uint8_t* light;
+  uint8_t* color_support;
+  uint8_t* color_ok;
+  uint8_t* source;     /* 0 wide / 128 blend / 255 colour (debug_fused_source.png) */
+  VistafTempRecord* records; /* [B] */
+} VistafTempOutputs;
+
+typedef struct VistafTempPlan VistafTempPlan;
+
+const char* vistaf_last_error(void);
+int vistaf_version(void);
+
+/* Temperature path (replaces temperature_sensor.main :749 numeric body, batched). */
+int vistaf_temp_plan_create(const VistafTempParams* params, VistafTempPlan** plan);
+void vistaf_temp_plan_destroy(VistafTempPlan* plan);
+/* bytes of device workspace needed to process `chunk` frames at a time */
+size_t vistaf_temp_workspace_bytes(const VistafTempPlan* plan, int chunk);
+/* frames_bgr: DEVICE uint8 [batch][H][W][3]; outputs: DEVICE pointers. */
+int vistaf_temp_batch(VistafTempPlan* plan, const uint8_t* frames_bgr, int batch, const VistafTempOutputs* out,
+                      void* workspace, size_t workspace_bytes, void* cuda_stream);
+/* copies the plan's ROI mask (uint8 [H][W]) to a DEVICE buffer */
+int vistaf_temp_roi_mask(const VistafTempPlan* plan, uint8_t* roi_dev, void* cuda_stream);
+/* debugging / parity: name -> byte offset and size of an intermediate plane of frame 0 in the workspace */
+int vistaf_temp_workspace_plane(const VistafTempPlan* plan, int chunk, const char* name, size_t* offset, size_t* bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,143 @@
+// Separable float32 Gaussian blur with OpenCV semantics (cv2.GaussianBlur, ksize = round(8*sigma+1)|1,
+// BORDER_REFLECT_101), templated on a load functor (row pass prologue) and a store functor
+// (column pass epilogue) so normalisation / masking / clamping fuse into the two sweeps.
+// Both passes stage a tile + halo in shared memory and give each thread 8 consecutive outputs
+// along the filter axis with a sliding register window (1 LDS per 8 FMA).
+#pragma once
+#include "common.cuh"
+
+#define BLUR_MAXK 368          // >= 361 taps (sigma 45), multiple of 8
+#define BLUR_ROW_SEG 1280      // outputs per row block (160 threads x 8)
+#define BLUR_ROW_THREADS 160
+#define BLUR_ROW_PITCH 228     // (1280 + 368 + 8)/8 = 207 -> next value == 4 (mod 32)
+
+struct GaussKernel {
+  int ksize;                 // odd
+  int kpad;                  // ksize rounded up to a multiple of 8
+  float w[BLUR_MAXK];        // zero padded
+};
+
+static inline GaussKernel make_gauss(double sigma, int ksize_override = 0) {
+  GaussKernel g;
+  int k = ksize_override > 0 ? ksize_override : (((int)lrint(sigma * 8.0 + 1.0)) | 1);
+  if (k > 361) k = 361;
+  g.ksize = k;
+  g.kpad = (k + 7) & ~7;
+  double sum = 0.0, t[BLUR_MAXK];
+  const double s2 = -0.5 / (sigma * sigma);
+  for (int i = 0; i < k; i++) {
+    double x = i - (k - 1) * 0.5;
+    t[i] = exp(s2 * x * x);
+    sum += t[i];
+  }
+  for (int i = 0; i < BLUR_MAXK; i++) g.w[i] = i < k ? (float)(t[i] / sum) : 0.f;
+  return g;
+}
+
+// Row pass.  grid = (ceil(w/1280), h, batch), block = 160.  Load: float operator()(int b,int y,int x).
+template <class Load>
+__global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* __restrict__ tmp, int h, int w,
+                                                                 long long plane, GaussKernel g) {
+  __shared__ float s[8 * BLUR_ROW_PITCH];
+  __shared__ float wk[BLUR_MAXK];
+  const int b = blockIdx.z, y = blockIdx.y, x0 = blockIdx.x * BLUR_ROW_SEG;
+  const int rad = g.ksize >> 1;
+  const int need = BLUR_ROW_SEG + g.kpad + 8;
+  for (int e = threadIdx.x; e < need; e += BLUR_ROW_THREADS) {
+    int x = x0 - rad + e;
+    float v = 0.f;
+    if (e < BLUR_ROW_SEG + g.ksize - 1 && x < w + rad) v = ld(b, y, reflect101(x, w));
+    s[(e & 7) * BLUR_ROW_PITCH + (e >> 3)] = v;
+  }
+  for (int e = threadIdx.x; e < g.kpad; e += BLUR_ROW_THREADS) wk[e] = g.w[e];
+  __syncthreads();
+  const int t = threadIdx.x;
+  float acc[8], win[16];
+#pragma unroll
+  for (int j = 0; j < 8; j++) { acc[j] = 0.f; win[j] = s[j * BLUR_ROW_PITCH + t]; }
+  for (int kb = 0; kb < g.kpad; kb += 8) {
+    const int c = t + (kb >> 3) + 1;
+#pragma unroll
+    for (int j = 0; j < 8; j++) win[8 + j] = s[j * BLUR_ROW_PITCH + c];
+#pragma unroll
+    for (int kk = 0; kk < 8; kk++) {
+      const float wv = wk[kb + kk];
+#pragma unroll
+      for (int j = 0; j < 8; j++) acc[j] = fmaf(wv, win[kk + j], acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; j++) win[j] = win[8 + j];
+  }
+  float* o = tmp + (long long)b * plane + (long long)y * w;
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    int x = x0 + t * 8 + j;
+    if (x < w) o[x] = acc[j];
+  }
+}
+
+// Column pass.  grid = (ceil(w/32), ceil(h/(8*TYT)), batch), block = (32, TYT).
+// dynamic smem = (8*TYT + kpad + 8) * 32 floats.  Store: void operator()(int b,int y,int x,float v).
+template <class Store>
+__global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int w, long long plane, GaussKernel g) {
+  extern __shared__ float sc[];
+  __shared__ float wk[BLUR_MAXK];
+  const int TY = 8 * blockDim.y;
+  const int b = blockIdx.z, x = blockIdx.x * 32 + threadIdx.x, y0 = blockIdx.y * TY;
+  const int rad = g.ksize >> 1;
+  const int need = TY + g.kpad + 8;
+  const float* src = tmp + (long long)b * plane;
+  for (int e = threadIdx.y; e < need; e += blockDim.y) {
+    int y = y0 - rad + e;
+    float v = 0.f;
+    if (e < TY + g.ksize - 1 && x < w && y < h + rad) v = src[(long long)reflect101(y, h) * w + x];
+    sc[e * 32 + threadIdx.x] = v;
+  }
+  const int tid = threadIdx.y * 32 + threadIdx.x;
+  for (int e = tid; e < g.kpad; e += 32 * blockDim.y) wk[e] = g.w[e];
+  __syncthreads();
+  const int r0 = threadIdx.y * 8;
+  float acc[8], win[16];
+#pragma unroll
+  for (int j = 0; j < 8; j++) { acc[j] = 0.f; win[j] = sc[(r0 + j) * 32 + threadIdx.x]; }
+  for (int kb = 0; kb < g.kpad; kb += 8) {
+#pragma unroll
+    for (int j = 0; j < 8; j++) win[8 + j] = sc[(r0 + kb + 8 + j) * 32 + threadIdx.x];
+#pragma unroll
+    for (int kk = 0; kk < 8; kk++) {
+      const float wv = wk[kb + kk];
+#pragma unroll
+      for (int j = 0; j < 8; j++) acc[j] = fmaf(wv, win[kk + j], acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; j++) win[j] = win[8 + j];
+  }
+  if (x < w) {
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      int y = y0 + r0 + j;
+      if (y < h) st(b, y, x, acc[j]);
+    }
+  }
+}
+
+// Host launcher: dst/epilogue through Store, source/prologue through Load, tmp = scratch plane(s).
+template <class Load, class Store>
+static int gauss_blur(Load ld, Store st, float* tmp, int h, int w, int batch, const GaussKernel& gx,
+                      const GaussKernel& gy, cudaStream_t stream) {
+  const long long plane = (long long)h * w;
+  dim3 g1(cdiv(w, BLUR_ROW_SEG), h, batch);
+  k_blur_rows<Load><<<g1, BLUR_ROW_THREADS, 0, stream>>>(ld, tmp, h, w, plane, gx);
+  CKL();
+  const int tyt = gy.ksize > 100 ? 32 : 16;
+  dim3 blk(32, tyt), g2(cdiv(w, 32), cdiv(h, 8 * tyt), batch);
+  size_t sm = sizeof(float) * 32 * (size_t)(8 * tyt + gy.kpad + 8);
+  static bool attr_done = false;   // per template instantiation
+  if (!attr_done && sm > 48 * 1024) {
+    CK(cudaFuncSetAttribute((const void*)k_blur_cols<Store>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    attr_done = true;
+  }
+  k_blur_cols<Store><<<g2, blk, sm, stream>>>(tmp, st, h, w, plane, gy);
+  CKL();
+  return 0;
+}

@@ -1,0 +1,86 @@
+"""Synthetic fringe + TLC frames of the camera's resolution.
+
+Host-side numpy generator: the single definition of the synthetic workload, so the oracle, the
+reference (when golden vectors are made) and the CUDA path all see the same bytes.  A frame is a
+2160x3840 BGR uint8 image of the skin disc: vertical two-tone stripes (black TLC / coloured TLC)
+of the grating period, phase-modulated by a Gaussian indentation, coloured from a palette indexed
+by a smooth temperature field, with illumination fall-off and sensor noise.
+
+Frames are pre-registered (no shift / rotation between reference and deformed), so throughput
+configs run with APPLY_GLOBAL_SHIFT=False and USE_ECC_CROP_ALIGNMENT=False on both sides.
+"""
+from __future__ import annotations
+
+import json
+import os
+
+import numpy as np
+
+H, W = 2160, 3840
+DISC_C = (2012.0, 1129.0)
+DISC_R = 720.0
+PERIOD_PX = 65.84
+_PAL = None
+
+
+def _palette():
+    global _PAL
+    if _PAL is None:
+        p = os.path.join(os.path.dirname(os.path.abspath(__file__)), "calibration", "synthetic_palette.json")
+        rows = json.load(open(p))["rows"]
+        _PAL = (np.array([r["T"] for r in rows], np.float32),
+                np.array([r["light"] for r in rows], np.float32),
+                np.array([r["dark"] for r in rows], np.float32))
+    return _PAL
+
+
+def frame_params(seed: int, reference: bool = False, amp_max: float = 1.3) -> dict:
+    """Scene parameters drawn from default_rng(seed); the reference frame has no indentation."""
+    rng = np.random.default_rng(int(seed) + (1 << 20 if reference else 0))
+    ang = rng.uniform(0, 2 * np.pi)
+    rad = rng.uniform(0, 250.0)
+    p = dict(
+        A=0.0 if reference else float(rng.uniform(0.1, amp_max)),
+        sigma=float(rng.uniform(60.0, 160.0)),
+        x0=float(DISC_C[0] + rad * np.cos(ang)), y0=float(DISC_C[1] + rad * np.sin(ang)),
+        T0=float(rng.uniform(20.5, 28.0)), dT=float(rng.uniform(0.0, 10.0)),
+        sT=float(rng.uniform(150.0, 400.0)),
+        tx=float(DISC_C[0] + rng.uniform(-300, 300)), ty=float(DISC_C[1] + rng.uniform(-300, 300)),
+        glare=(not reference) and (int(seed) % 16 == 15),
+        noise_seed=int(rng.integers(0, 2 ** 31)),
+    )
+    if reference:
+        p.update(T0=22.0, dT=0.0)
+    return p
+
+
+def make_frame(seed: int, reference: bool = False, amp_max: float = 1.3, h: int = H, w: int = W) -> np.ndarray:
+    """BGR uint8 (h, w, 3)."""
+    p = frame_params(seed, reference, amp_max)
+    rng = np.random.default_rng(p["noise_seed"])
+    img = np.full((h, w, 3), 25.0, np.float32)
+    # work inside the disc's bounding box only
+    x_lo, x_hi = int(max(0, DISC_C[0] - DISC_R - 2)), int(min(w, DISC_C[0] + DISC_R + 3))
+    y_lo, y_hi = int(max(0, DISC_C[1] - DISC_R - 2)), int(min(h, DISC_C[1] + DISC_R + 3))
+    yy, xx = np.mgrid[y_lo:y_hi, x_lo:x_hi].astype(np.float32)
+    r2 = (xx - DISC_C[0]) ** 2 + (yy - DISC_C[1]) ** 2
+    inside = r2 <= DISC_R ** 2
+    phi = -p["A"] * np.exp(-((xx - p["x0"]) ** 2 + (yy - p["y0"]) ** 2) / (2.0 * p["sigma"] ** 2))
+    theta = (2.0 * np.pi / PERIOD_PX) * xx + phi
+    wl = 0.5 * (1.0 + np.tanh(np.sin(theta) / (2.0 * np.pi * 3.0 / PERIOD_PX)))      # light-stripe weight
+    T = p["T0"] + p["dT"] * np.exp(-((xx - p["tx"]) ** 2 + (yy - p["ty"]) ** 2) / (2.0 * p["sT"] ** 2))
+    pt, pl, pd = _palette()
+    illum = 1.0 + 0.15 * np.cos(np.sqrt(r2) / DISC_R * (np.pi / 2.0))
+    box = img[y_lo:y_hi, x_lo:x_hi]
+    for c in range(3):
+        col = wl * np.interp(T, pt, pl[:, c]).astype(np.float32) + (1.0 - wl) * np.interp(T, pt, pd[:, c]).astype(np.float32)
+        box[..., c] = np.where(inside, col * illum, box[..., c])
+    if p["glare"]:
+        for gx, gy in ((DISC_C[0] - 210.0, DISC_C[1] - 160.0), (DISC_C[0] + 260.0, DISC_C[1] + 120.0)):
+            box[((xx - gx) ** 2 + (yy - gy) ** 2) <= 12.0 ** 2] = 255.0
+    img += 2.0 * rng.standard_normal((h, w, 3), dtype=np.float32)
+    return np.clip(np.rint(img), 0, 255).astype(np.uint8)
+
+
+def make_batch(seeds, **kw) -> np.ndarray:
+    return np.stack([make_frame(s, **kw) for s in seeds], axis=0)
