@@ -1,0 +1,121 @@
+"""ctypes binding of libvistaf.so (include/vistaf.h).  PyTorch is used only for device memory and
+streams.  There is NO CPU fallback: importing this module without the built library, or calling
+into it without a CUDA device, raises."""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libvistaf.so")
+CAL_DIR = os.path.join(_HERE, "calibration")
+
+MAX_TERMS, MAX_ISO = 35, 64
+
+ST_EMPTY_ROI, ST_NO_PEAK, ST_SATURATED, ST_ROTATED_CARRIER = 0x1, 0x2, 0x4, 0x8
+ST_RESIDUES, ST_FEW_RELIABLE, ST_SIGN_FLIPPED, ST_CONTACT_P95, ST_BG_FALLBACK = 0x10, 0x20, 0x40, 0x80, 0x100
+
+
+class PolyModel(C.Structure):
+    _fields_ = [("n_features", C.c_int32), ("n_terms", C.c_int32), ("n_iso", C.c_int32), ("pad_", C.c_int32),
+                ("mean", C.c_double * 4), ("scale", C.c_double * 4),
+                ("powers", (C.c_int32 * 4) * MAX_TERMS), ("coef", C.c_double * MAX_TERMS),
+                ("intercept", C.c_double), ("iso_x", C.c_double * MAX_ISO), ("iso_y", C.c_double * MAX_ISO)]
+
+
+class TempParams(C.Structure):
+    _fields_ = [("height", C.c_int32), ("width", C.c_int32),
+                ("roi_cx", C.c_double), ("roi_cy", C.c_double), ("roi_r", C.c_double),
+                ("color_t_min", C.c_float), ("color_t_max", C.c_float), ("guard_band", C.c_float),
+                ("switch_margin", C.c_float), ("final_t_min", C.c_float), ("final_t_max", C.c_float),
+                ("band_radius", C.c_int32), ("dc_exclusion", C.c_int32),
+                ("peak_max_dy_frac", C.c_float), ("illum_sigma", C.c_float),
+                ("sat_thresh", C.c_int32), ("sat_dilate", C.c_int32),
+                ("close_kx", C.c_int32), ("close_ky", C.c_int32), ("open_kx", C.c_int32), ("open_ky", C.c_int32),
+                ("chroma_min", C.c_float), ("support_dilate", C.c_int32),
+                ("sigma_across", C.c_float), ("sigma_along", C.c_float),
+                ("color_model", PolyModel), ("wide_model", PolyModel),
+                ("lab_gamma", C.c_int32 * 256), ("lab_cbrt", C.c_int32 * 3072)]
+
+
+class TempRecord(C.Structure):
+    _fields_ = [("mean_C", C.c_float), ("median_C", C.c_float), ("std_C", C.c_float), ("min_C", C.c_float),
+                ("max_C", C.c_float), ("valid_pixels", C.c_int32), ("peak_x", C.c_int32), ("peak_y", C.c_int32),
+                ("phi0", C.c_float), ("mean_gray_a", C.c_float), ("mean_gray_b", C.c_float),
+                ("median_gray", C.c_float), ("sat_pixels", C.c_int32), ("roi_eff_pixels", C.c_int32),
+                ("dark_pixels", C.c_int32), ("color_ok_pixels", C.c_int32), ("status", C.c_int32),
+                ("pad_", C.c_int32 * 3)]
+
+
+TEMP_RECORD_DTYPE = np.dtype([(n, np.float32 if t is C.c_float else np.int32) for n, t in TempRecord._fields_[:-1]]
+                             + [("pad_", np.int32, (3,))])
+assert TEMP_RECORD_DTYPE.itemsize == C.sizeof(TempRecord) == 80
+
+
+class TempOutputs(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("fused", "final_map", "sat", "dark", "light", "color_support",
+                                          "color_ok", "source", "records")]
+
+
+_lib = None
+
+
+def lib():
+    """Load libvistaf.so; fail loudly if it has not been built (python __graft_entry__.py build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"libvistaf.so not built: {LIB_PATH} (run `python __graft_entry__.py`); "
+                               "there is no CPU fallback for the sensing path")
+        L = C.CDLL(LIB_PATH)
+        L.vistaf_last_error.restype = C.c_char_p
+        L.vistaf_temp_workspace_bytes.restype = C.c_size_t
+        L.vistaf_temp_workspace_bytes.argtypes = [C.c_void_p, C.c_int]
+        L.vistaf_temp_plan_create.argtypes = [C.POINTER(TempParams), C.POINTER(C.c_void_p)]
+        L.vistaf_temp_plan_destroy.argtypes = [C.c_void_p]
+        L.vistaf_temp_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(TempOutputs), C.c_void_p,
+                                        C.c_size_t, C.c_void_p]
+        L.vistaf_temp_roi_mask.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.vistaf_temp_workspace_plane.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.POINTER(C.c_size_t),
+                                                  C.POINTER(C.c_size_t)]
+        _lib = L
+    return _lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        raise RuntimeError(f"libvistaf {what} failed: {lib().vistaf_last_error().decode()}")
+
+
+def load_poly_model(json_name: str) -> PolyModel:
+    d = json.load(open(os.path.join(CAL_DIR, json_name)))
+    m = PolyModel()
+    m.n_features, m.n_terms = len(d["use_features"]), len(d["coef"])
+    for i, (a, b) in enumerate(zip(d["scaler_mean"], d["scaler_scale"])):
+        m.mean[i], m.scale[i] = a, b
+    for t, (pw, c) in enumerate(zip(d["powers"], d["coef"])):
+        m.coef[t] = c
+        for f, p in enumerate(pw):
+            m.powers[t][f] = p
+    m.intercept = d["intercept"]
+    iso = d.get("isotonic")
+    m.n_iso = len(iso["x"]) if iso else 0
+    if iso:
+        for i, (x, y) in enumerate(zip(iso["x"], iso["y"])):
+            m.iso_x[i], m.iso_y[i] = x, y
+    return m
+
+
+def lab_tables():
+    d = json.load(open(os.path.join(CAL_DIR, "lab_lut.json")))
+    return d["gamma"], d["cbrt"]
+
+
+def require_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        raise RuntimeError("VISTAF B200 path needs a CUDA device; there is no CPU fallback")
+    return torch

@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* 
 }
 
 // Column pass.  grid = (ceil(w/32), ceil(h/(8*TYT)), batch), block = (32, TYT).
-// dynamic smem = (8*TYT + kpad + 8) * 32 floats.  Store: void operator()(int b,int y,int x,float v).
+// dynamic smem = (8*TYT + kpad + 8) * 32 floats.  Store: void operator()(int b,int y,int x,float v); void finish(int b).
 template <class Store>
 __global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int w, long long plane, GaussKernel g) {
   extern __shared__ float sc[];
@@ -112,13 +112,15 @@ __global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int 
 #pragma unroll
     for (int j = 0; j < 8; j++) win[j] = win[8 + j];
   }
+  Store stl = st;                 // per-thread copy: stores may accumulate (reductions fused in the epilogue)
   if (x < w) {
 #pragma unroll
     for (int j = 0; j < 8; j++) {
       int y = y0 + r0 + j;
-      if (y < h) st(b, y, x, acc[j]);
+      if (y < h) stl(b, y, x, acc[j]);
     }
   }
+  stl.finish(b);                  // block-wide; every thread reaches this
 }
 
 // Host launcher: dst/epilogue through Store, source/prologue through Load, tmp = scratch plane(s).

@@ -50,7 +50,8 @@ __device__ __forceinline__ float warp_min(float v) {
 // Block-wide sum of NV doubles per thread; result valid in thread 0.  sh: >= NV*32 doubles.
 template <int NV>
 __device__ __forceinline__ void block_sum(double (&v)[NV], double* sh) {
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+  const int lane = tid & 31, wid = tid >> 5, nw = (blockDim.x * blockDim.y + 31) >> 5;
 #pragma unroll
   for (int i = 0; i < NV; i++) v[i] = warp_sum(v[i]);
   __syncthreads();

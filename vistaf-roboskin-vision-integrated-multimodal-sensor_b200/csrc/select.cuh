@@ -39,7 +39,7 @@ __device__ __forceinline__ float sel_pos(unsigned int count, float q) {
   if (q < 0.f) return (float)((count - 1) >> 1);
   return (float)(count - 1) * (q / 100.0f);
 }
-__global__ void k_sel_begin(SelectState* st, float q) {
+static __global__ void k_sel_begin(SelectState* st, float q) {
   SelectState& s = st[blockIdx.x];
   for (int i = threadIdx.x; i < 256; i += blockDim.x) s.hist[i] = 0;
   if (threadIdx.x == 0) {
@@ -71,7 +71,7 @@ __global__ void k_sel_hist(Val val, SelectState* st, long long n, int shift) {
     if (h[i]) atomicAdd(&st[b].hist[i], h[i]);
 }
 
-__global__ void k_sel_pick(SelectState* st, int shift) {
+static __global__ void k_sel_pick(SelectState* st, int shift) {
   SelectState& s = st[blockIdx.x];
   if (threadIdx.x == 0) {
     unsigned int k = s.krem, acc = 0;
@@ -112,7 +112,7 @@ __global__ void k_sel_neighbour(Val val, SelectState* st, long long n) {
 }
 
 // numpy _lerp in float32: a + (b-a)*t, switched to b - (b-a)*(1-t) for t >= 0.5, t = frac(pos).
-__global__ void k_sel_finish(SelectState* st, float q) {
+static __global__ void k_sel_finish(SelectState* st, float q) {
   SelectState& s = st[blockIdx.x];
   if (s.count == 0) { s.vk = s.vk1 = s.result = __int_as_float(0x7fc00000); return; }
   float pos = sel_pos(s.count, q);

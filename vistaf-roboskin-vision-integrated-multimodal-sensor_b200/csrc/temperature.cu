@@ -1,0 +1,969 @@
+// Temperature path on sm_100a: BGR frame -> stripe segmentation (FFT sideband) -> blurred CIELAB
+// features -> two polynomial regressors -> fusion -> oriented smoothing -> statistics.
+// Mirrors Code/temperature_sensor.py (reference file:line cited per kernel); batched over frames.
+#include "../../include/vistaf.h"
+#include "common.cuh"
+#include "fft.cuh"
+#include "blur.cuh"
+#include "select.cuh"
+#include "morph.cuh"
+#include <string.h>
+#include <new>
+
+#define TOPK 16
+#define COLS_PER_BLOCK 4
+#define MAXBAND 45            // 2*22+1
+
+struct Cand { float mag; int ky, kx; int pad; };
+
+struct TempWs {               // per-chunk workspace layout (byte offsets), planes are [chunk][...]
+  size_t gray8, satraw, sat, norm, tmp, A, G, maskA, m1, m2, cand, scal, sel, total;
+};
+
+struct TempScal {             // per-frame scalars living in the workspace
+  unsigned int hist[256];
+  unsigned int sat_raw_count, sat_count, n_eff, status;
+  float median;
+  float mu_f;
+  double norm_sum;
+  double csum[2];
+  double sumA, sumB;
+  unsigned int cntA, cntB;
+  int peak_x, peak_y;
+  int a_is_dark;
+  unsigned int dark_count, color_ok_count;
+  double t_sum, t_sumsq;
+  float t_min, t_max;
+  unsigned int t_count, pad;
+};
+
+struct VistafTempPlan {
+  VistafTempParams P;
+  int H, W, Wh;
+  uint8_t* roi;               // device [H][W]
+  int y0, y1, x0, x1;         // ROI bounding box (inclusive-exclusive)
+  Fft1D fw, fh;
+  GaussKernel g_illum, g_across, g_along;
+  MorphSE se_sat;
+  VistafPolyModel* models;    // device [2]: colour, wide
+  int* lab_gamma;             // device
+  int* lab_cbrt;
+  int nblk_cols;
+};
+
+// ------------------------------------------------------------------ ROI (temperature_sensor.py:180-184)
+__global__ void k_roi_mask(uint8_t* roi, int h, int w, double cx, double cy, double r2) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= w) return;
+  double dx = __dsub_rn((double)x, cx), dy = __dsub_rn((double)y, cy);
+  double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+  roi[(size_t)y * w + x] = d2 <= r2 ? 1 : 0;
+}
+
+// ------------------------------------------------------------------ T2/T3 front: gray, saturation
+// cv2.cvtColor(BGR2GRAY) 8-bit: (9798 R + 19235 G + 3735 B + 2^14) >> 15   (temperature_sensor.py:379,439)
+__device__ __forceinline__ int gray8_of(int b, int g, int r) { return (9798 * r + 19235 * g + 3735 * b + 16384) >> 15; }
+
+__global__ void k_temp_gray(const uint8_t* __restrict__ frames, const uint8_t* __restrict__ roi,
+                            uint8_t* __restrict__ gray8, uint8_t* __restrict__ satraw, TempScal* sc, int npix,
+                            int sat_thresh) {
+  const int b = blockIdx.y;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;      // group of 4 pixels
+  int nsat = 0;
+  if (q * 4 < npix) {
+    const uint32_t* src = (const uint32_t*)(frames + (size_t)b * npix * 3) + (size_t)q * 3;
+    uint32_t w0 = __ldg(src), w1 = __ldg(src + 1), w2 = __ldg(src + 2);
+    const uint32_t wv[3] = {w0, w1, w2};
+    int px[12];
+#pragma unroll
+    for (int i = 0; i < 12; i++) px[i] = (int)((wv[i >> 2] >> (8 * (i & 3))) & 255u);
+    uchar4 rm = *(const uchar4*)(roi + (size_t)q * 4);
+    uint8_t r4[4] = {rm.x, rm.y, rm.z, rm.w};
+    uint8_t g4[4], s4[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      int g = gray8_of(px[3 * i], px[3 * i + 1], px[3 * i + 2]);
+      g4[i] = (uint8_t)g;
+      s4[i] = (g >= sat_thresh && r4[i]) ? 1 : 0;
+      nsat += s4[i];
+    }
+    *(uchar4*)(gray8 + (size_t)b * npix + (size_t)q * 4) = make_uchar4(g4[0], g4[1], g4[2], g4[3]);
+    *(uchar4*)(satraw + (size_t)b * npix + (size_t)q * 4) = make_uchar4(s4[0], s4[1], s4[2], s4[3]);
+  }
+  nsat = warp_sum(nsat);
+  if ((threadIdx.x & 31) == 0 && nsat) atomicAdd(&sc[b].sat_raw_count, (unsigned)nsat);
+}
+
+// dilate(sat, ellipse k) & roi — only when the frame has saturated pixels (temperature_sensor.py:381-386)
+__global__ void k_temp_sat_dilate(const uint8_t* __restrict__ satraw, const uint8_t* __restrict__ roi,
+                                  uint8_t* __restrict__ sat, TempScal* sc, int h, int w, MorphSE se) {
+  const int b = blockIdx.z;
+  if (sc[b].sat_raw_count == 0) return;
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  const bool inb = x < w;
+  const uint8_t* s = satraw + (size_t)b * h * w;
+  int v = 0;
+  if (inb && roi[(size_t)y * w + x]) {
+    for (int i = 0; i < se.rows && !v; i++) {
+      int yy = y + i - se.rows / 2;
+      if (yy < 0 || yy >= h || se.half[i] < 0) continue;
+      for (int xx = max(0, x - se.half[i]); xx <= min(w - 1, x + se.half[i]); xx++)
+        if (s[(size_t)yy * w + xx]) { v = 1; break; }
+    }
+  }
+  if (inb) sat[(size_t)b * h * w + (size_t)y * w + x] = (uint8_t)v;
+  int c = warp_sum(v);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&sc[b].sat_count, (unsigned)c);
+}
+
+__device__ __forceinline__ bool sat_at(const TempScal& s, const uint8_t* sat, size_t i) {
+  return s.sat_raw_count != 0 && sat[i] != 0;
+}
+
+// histogram of gray over roi_eff -> exact median of integer-valued float32 (temperature_sensor.py:446-447)
+__global__ void k_temp_hist(const uint8_t* __restrict__ gray8, const uint8_t* __restrict__ roi,
+                            const uint8_t* __restrict__ sat, TempScal* sc, int npix) {
+  __shared__ unsigned int h[256];
+  const int b = blockIdx.y;
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) h[i] = 0;
+  __syncthreads();
+  const uint8_t* g = gray8 + (size_t)b * npix;
+  const uint8_t* s = sat + (size_t)b * npix;
+  const bool has_sat = sc[b].sat_raw_count != 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x)
+    if (roi[i] && !(has_sat && s[i])) atomicAdd(&h[g[i]], 1u);
+  __syncthreads();
+  for (int i = threadIdx.x; i < 256; i += blockDim.x)
+    if (h[i]) atomicAdd(&sc[b].hist[i], h[i]);
+}
+
+__global__ void k_temp_median(TempScal* sc) {
+  TempScal& s = sc[blockIdx.x];
+  if (threadIdx.x != 0) return;
+  unsigned int n = 0;
+  for (int i = 0; i < 256; i++) n += s.hist[i];
+  s.n_eff = n;
+  if (n == 0) { s.status |= VISTAF_ST_EMPTY_ROI; s.median = 0.f; return; }
+  unsigned int k0 = (n - 1) / 2, k1 = n / 2, acc = 0;
+  int v0 = -1, v1 = -1;
+  for (int i = 0; i < 256; i++) {
+    acc += s.hist[i];
+    if (v0 < 0 && acc > k0) v0 = i;
+    if (v1 < 0 && acc > k1) { v1 = i; break; }
+  }
+  s.median = ((float)v0 + (float)v1) / 2.0f;
+}
+
+// ------------------------------------------------------------------ T3: illumination normalisation
+// g[~roi] = median; norm = g / GaussianBlur(g, sigma 20) (blur < 1e-6 -> 1); mu = mean(norm[roi_eff])
+// (temperature_sensor.py:446-450, 363-375).  Load / Store functors for gauss_blur().
+struct IllumLoad {
+  const uint8_t* gray8; const uint8_t* roi; const TempScal* sc; long long plane; int w;
+  __device__ float operator()(int b, int y, int x) const {
+    long long i = (long long)y * w + x;
+    return roi[i] ? (float)gray8[(long long)b * plane + i] : sc[b].median;
+  }
+};
+struct IllumStore {
+  const uint8_t* gray8; const uint8_t* roi; const uint8_t* sat; TempScal* sc; float* norm; long long plane; int w;
+  double acc;
+  __device__ void operator()(int b, int y, int x, float blur) {
+    long long i = (long long)y * w + x;
+    const bool in = roi[i] != 0;
+    float g = in ? (float)gray8[(long long)b * plane + i] : sc[b].median;
+    if (blur < 1e-6f) blur = 1.0f;
+    float n = __fdiv_rn(g, blur);
+    norm[(long long)b * plane + i] = n;
+    if (in && !sat_at(sc[b], sat + (long long)b * plane, i)) acc += (double)n;
+  }
+  __device__ void finish(int b) {
+    __shared__ double sh[32];
+    double v[1] = {acc};
+    block_sum<1>(v, sh);
+    if (threadIdx.x == 0 && threadIdx.y == 0 && v[0] != 0.0) atomicAdd(&sc[b].norm_sum, v[0]);
+  }
+};
+
+__global__ void k_temp_mu(TempScal* sc) {
+  TempScal& s = sc[blockIdx.x];
+  double mu = s.n_eff ? s.norm_sum / (double)s.n_eff : 1.0;
+  if (fabs(mu) <= 1e-9) mu = 1.0;
+  s.mu_f = (float)mu;
+}
+
+// ------------------------------------------------------------------ T4: forward FFT
+// Row pass, two real rows per complex transform (z = row0 + i*row1), unpacked by Hermitian symmetry
+// into the half spectrum A[y][kx], kx = 0..W/2.  I_norm = norm / mu is applied on load.
+__global__ void __launch_bounds__(256) k_temp_fft_rows(const float* __restrict__ norm, float2* __restrict__ A,
+                                                        const TempScal* sc, Fft1D p, int h, int wh) {
+  extern __shared__ float2 sm[];
+  const int n = p.n, b = blockIdx.y, r = blockIdx.x * 2;
+  float2* a = sm;
+  float2* bb = sm + n;
+  const float mu = sc[b].mu_f;
+  const float* r0 = norm + ((size_t)b * h + r) * n;
+  const float* r1 = r0 + n;
+  const bool has1 = r + 1 < h;
+  for (int x = threadIdx.x; x < n; x += blockDim.x)
+    a[x] = make_float2(__fdiv_rn(r0[x], mu), has1 ? __fdiv_rn(r1[x], mu) : 0.f);
+  float2* z = fft_smem<-1>(a, bb, p, 1, n);
+  float2* o0 = A + ((size_t)b * h + r) * wh;
+  float2* o1 = o0 + wh;
+  for (int k = threadIdx.x; k < wh; k += blockDim.x) {
+    float2 zk = z[k], zn = z[(n - k) % n];
+    o0[k] = make_float2(0.5f * (zk.x + zn.x), 0.5f * (zk.y - zn.y));
+    if (has1) o1[k] = make_float2(0.5f * (zk.y + zn.y), 0.5f * (zn.x - zk.x));
+  }
+}
+
+// Is the fftshift-ed bin (x, y) inside the DC exclusion box? (temperature_sensor.py:323-327)
+__device__ __forceinline__ bool dc_excluded(int x, int y, int h, int w, int dc) {
+  int cy = h / 2, cx = w / 2;
+  return y >= max(0, cy - dc) && y < min(h, cy + dc) && x >= max(0, cx - dc) && x < min(w, cx + dc);
+}
+
+// Column pass over the half spectrum + fused |F| and per-block top-16 (the dense spectrum is never
+// written: only the band around the carrier is needed later and is recomputed from A).
+__global__ void __launch_bounds__(512) k_temp_fft_cols_peaks(const float2* __restrict__ A, Cand* __restrict__ cand,
+                                                              Fft1D p, int w, int wh, int dc) {
+  extern __shared__ float2 sm[];
+  const int n = p.n, lds = n + 1, b = blockIdx.y, c0 = blockIdx.x * COLS_PER_BLOCK;
+  const int nc = min(COLS_PER_BLOCK, wh - c0);
+  float2* a = sm;
+  float2* bb = sm + (size_t)COLS_PER_BLOCK * lds;
+  const float2* src = A + (size_t)b * n * wh;
+  for (int t = threadIdx.x; t < nc * n; t += blockDim.x) {
+    int y = t / nc, c = t - y * nc;
+    a[c * lds + y] = src[(size_t)y * wh + c0 + c];
+  }
+  float2* F = fft_smem<-1>(a, bb, p, nc, lds);
+  float* mag = (float*)(F == a ? bb : a);          // scratch buffer is free now
+  __syncthreads();
+  for (int t = threadIdx.x; t < nc * n; t += blockDim.x) {
+    int c = t / n, ky = t - c * n, kx = c0 + c;
+    float2 v = F[c * lds + ky];
+    float m = sqrtf(v.x * v.x + v.y * v.y);
+    // entry 1: (kx, ky); entry 2 (twin, same magnitude): (-kx, -ky).  Drop the bin if both are excluded.
+    int x1 = (kx + w / 2) % w, y1 = (ky + n / 2) % n;
+    bool ex1 = dc_excluded(x1, y1, n, w, dc);
+    bool ex2 = true;
+    if (kx != 0 && kx != w / 2) {
+      int x2 = (w - kx + w / 2) % w, y2 = ((n - ky) % n + n / 2) % n;
+      ex2 = dc_excluded(x2, y2, n, w, dc);
+    }
+    mag[t] = (ex1 && ex2) ? -1.f : m;
+  }
+  __syncthreads();
+  __shared__ float smax[16];
+  __shared__ int sidx[16];
+  Cand* out = cand + ((size_t)b * gridDim.x + blockIdx.x) * TOPK;
+  for (int round = 0; round < TOPK; round++) {
+    float best = -2.f;
+    int bi = -1;
+    for (int t = threadIdx.x; t < nc * n; t += blockDim.x) {
+      float m = mag[t];
+      if (m > best) { best = m; bi = t; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      float ob = __shfl_xor_sync(0xffffffffu, best, o);
+      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ob > best || (ob == best && oi >= 0 && (bi < 0 || oi < bi))) { best = ob; bi = oi; }
+    }
+    if ((threadIdx.x & 31) == 0) { smax[threadIdx.x >> 5] = best; sidx[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int i = 1; i < (int)(blockDim.x >> 5); i++)
+        if (smax[i] > best || (smax[i] == best && sidx[i] >= 0 && (bi < 0 || sidx[i] < bi))) { best = smax[i]; bi = sidx[i]; }
+      Cand cd;
+      cd.mag = best; cd.pad = 0;
+      if (bi >= 0 && best >= 0.f) { int c = bi / n; cd.kx = c0 + c; cd.ky = bi - c * n; mag[bi] = -1.f; }
+      else { cd.kx = -1; cd.ky = -1; cd.mag = -1.f; }
+      out[round] = cd;
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ T4: carrier peak
+// Merge the per-block candidates of one frame: expand each half-plane bin into its (up to) two
+// full-plane entries, keep the 16 largest outside the DC box, then apply the selection rule of
+// temperature_sensor.py:341-360 (right half plane, |dy| <= 0.14 h, largest magnitude).
+__global__ void __launch_bounds__(256) k_temp_peak_select(const Cand* __restrict__ cand, TempScal* sc, int ncand,
+                                                           int h, int w, int dc, float max_dy_frac) {
+  extern __shared__ float emag[];                  // 2*ncand entry magnitudes
+  __shared__ float smax[8];
+  __shared__ int sidx[8];
+  __shared__ int top_x[TOPK], top_y[TOPK];
+  __shared__ float top_m[TOPK];
+  const int b = blockIdx.x;
+  const Cand* c = cand + (size_t)b * ncand;
+  for (int e = threadIdx.x; e < 2 * ncand; e += blockDim.x) {
+    Cand cd = c[e >> 1];
+    float m = -1.f;
+    if (cd.kx >= 0) {
+      int x, y;
+      bool ok = true;
+      if ((e & 1) == 0) { x = (cd.kx + w / 2) % w; y = (cd.ky + h / 2) % h; }
+      else {
+        ok = cd.kx != 0 && cd.kx != w / 2;
+        x = (w - cd.kx + w / 2) % w; y = ((h - cd.ky) % h + h / 2) % h;
+      }
+      if (ok && !dc_excluded(x, y, h, w, dc)) m = cd.mag;
+    }
+    emag[e] = m;
+  }
+  __syncthreads();
+  int ntop = 0;
+  for (int round = 0; round < TOPK; round++) {
+    float best = -2.f;
+    int bi = -1;
+    for (int e = threadIdx.x; e < 2 * ncand; e += blockDim.x)
+      if (emag[e] > best) { best = emag[e]; bi = e; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      float ob = __shfl_xor_sync(0xffffffffu, best, o);
+      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ob > best || (ob == best && oi >= 0 && (bi < 0 || oi < bi))) { best = ob; bi = oi; }
+    }
+    if ((threadIdx.x & 31) == 0) { smax[threadIdx.x >> 5] = best; sidx[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int i = 1; i < 8; i++)
+        if (smax[i] > best || (smax[i] == best && sidx[i] >= 0 && (bi < 0 || sidx[i] < bi))) { best = smax[i]; bi = sidx[i]; }
+      if (bi >= 0 && best >= 0.f) {
+        Cand cd = c[bi >> 1];
+        int x, y;
+        if ((bi & 1) == 0) { x = (cd.kx + w / 2) % w; y = (cd.ky + h / 2) % h; }
+        else { x = (w - cd.kx + w / 2) % w; y = ((h - cd.ky) % h + h / 2) % h; }
+        top_x[round] = x; top_y[round] = y; top_m[round] = best;
+        emag[bi] = -1.f;
+      } else top_m[round] = -1.f;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const int cy = h / 2, cx = w / 2, max_dy = (int)(max_dy_frac * (float)h);
+    for (int i = 0; i < TOPK; i++) if (top_m[i] >= 0.f) ntop++;
+    if (ntop == 0) { sc[b].status |= VISTAF_ST_NO_PEAK; sc[b].peak_x = cx; sc[b].peak_y = cy; return; }
+    bool any_right = false, any_near = false;
+    for (int i = 0; i < TOPK; i++) if (top_m[i] >= 0.f && top_x[i] > cx) any_right = true;
+    for (int i = 0; i < TOPK; i++)
+      if (top_m[i] >= 0.f && (!any_right || top_x[i] > cx) && abs(top_y[i] - cy) <= max_dy) any_near = true;
+    int sel = -1;
+    for (int i = 0; i < TOPK; i++) {
+      if (top_m[i] < 0.f) continue;
+      if (any_right && !(top_x[i] > cx)) continue;
+      if (any_near && !(abs(top_y[i] - cy) <= max_dy)) continue;
+      if (sel < 0 || top_m[i] > top_m[sel]) sel = i;
+    }
+    sc[b].peak_x = top_x[sel];
+    sc[b].peak_y = top_y[sel];
+    if (top_y[sel] != cy) sc[b].status |= VISTAF_ST_ROTATED_CARRIER;
+  }
+}
+
+// ------------------------------------------------------------------ T5: band-pass + inverse, column part
+// Block (j, b): column j of the (2R+1)^2 box around the peak.  F[ky,kx] on the disc is recomputed by
+// a direct DFT of column |kx| of A (Hermitian twin for kx < 0), then G[y][j] = sum_ky F e^{+2 pi i ky y/H}/(HW).
+__global__ void __launch_bounds__(256) k_temp_band(const float2* __restrict__ A, float2* __restrict__ G,
+                                                    const TempScal* sc, Fft1D ph, int w, int wh, int R) {
+  extern __shared__ float2 col[];                  // H entries
+  __shared__ float2 Fd[MAXBAND];
+  const int h = ph.n, b = blockIdx.y, j = blockIdx.x, nb = 2 * R + 1;
+  const int px = sc[b].peak_x, py = sc[b].peak_y;
+  const int xs = px + j - R;                        // fftshift-ed column of this block
+  const bool col_ok = xs >= 0 && xs < w;
+  int kx = xs - w / 2;                              // signed frequency
+  const bool twin = kx < 0;
+  const int ka = twin ? -kx : kx;                   // column of A (0..W/2)
+  const float2* src = A + (size_t)b * h * wh;
+  for (int y = threadIdx.x; y < h; y += blockDim.x) col[y] = col_ok ? src[(size_t)y * wh + ka] : make_float2(0.f, 0.f);
+  __syncthreads();
+  // step 1: the nb bins of this column, one warp per bin (strided), lanes split the y sum
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int i = wid; i < nb; i += nw) {
+    const int ys = py + i - R;
+    const int dx = j - R, dy = i - R;
+    bool in = col_ok && ys >= 0 && ys < h && (dx * dx + dy * dy) <= R * R;
+    float2 acc = make_float2(0.f, 0.f);
+    if (in) {
+      int ky = ((ys - h / 2) % h + h) % h;
+      int kq = twin ? (h - ky) % h : ky;            // F[ky,kx] = conj(F[-ky,-kx])
+      for (int y = lane; y < h; y += 32) {
+        float2 t = __ldg(ph.tw + (int)(((long long)kq * y) % h));
+        acc = cadd(acc, cmul(col[y], t));
+      }
+    }
+    acc.x = warp_sum(acc.x); acc.y = warp_sum(acc.y);
+    if (lane == 0) Fd[i] = twin ? make_float2(acc.x, -acc.y) : acc;
+  }
+  __syncthreads();
+  // step 2: inverse along y for this column
+  const float scale = 1.0f / ((float)h * (float)w);
+  for (int y = threadIdx.x; y < h; y += blockDim.x) {
+    float2 acc = make_float2(0.f, 0.f);
+    for (int i = 0; i < nb; i++) {
+      int ys = py + i - R;
+      if (ys < 0 || ys >= h) continue;
+      int ky = ((ys - h / 2) % h + h) % h;
+      float2 t = __ldg(ph.tw + (int)(((long long)ky * y) % h));
+      t.y = -t.y;                                   // e^{+i...}
+      acc = cadd(acc, cmul(Fd[i], t));
+    }
+    G[((size_t)b * h + y) * MAXBAND + j] = make_float2(acc.x * scale, acc.y * scale);
+  }
+}
+
+// ------------------------------------------------------------------ T5/T6: inverse rows
+// z[y][:] = IFFT_W(sparse spectrum of <= 45 bins).  PASS 1 accumulates c = sum_roi_eff z * (I_norm - 1)
+// (temperature_sensor.py:469-470); PASS 2 rotates by phi0 = angle(c), thresholds s = Re(z e^{-i phi0}) >= 0
+// and accumulates the mean gray of both classes (:471-480).  Only ROI rows are launched.
+template <int PASS>
+__global__ void __launch_bounds__(256) k_temp_ifft_rows(const float2* __restrict__ G, const float* __restrict__ norm,
+                                                         const uint8_t* __restrict__ gray8,
+                                                         const uint8_t* __restrict__ roi, const uint8_t* __restrict__ sat,
+                                                         uint8_t* __restrict__ maskA, TempScal* sc, Fft1D p, int h,
+                                                         int ybeg, int R) {
+  extern __shared__ float2 sm[];
+  __shared__ double red[4 * 32];
+  const int n = p.n, b = blockIdx.y, y = ybeg + blockIdx.x, nb = 2 * R + 1;
+  float2* a = sm;
+  float2* bb = sm + n;
+  TempScal& S = sc[b];
+  for (int x = threadIdx.x; x < n; x += blockDim.x) a[x] = make_float2(0.f, 0.f);
+  __syncthreads();
+  if ((int)threadIdx.x < nb) {
+    int xs = S.peak_x + (int)threadIdx.x - R;
+    if (xs >= 0 && xs < n) a[((xs - n / 2) % n + n) % n] = G[((size_t)b * h + y) * MAXBAND + threadIdx.x];
+  }
+  float2* z = fft_smem<1>(a, bb, p, 1, n);
+  const size_t row = (size_t)y * n, fr = (size_t)b * h * n;
+  const bool has_sat = S.sat_raw_count != 0;
+  if (PASS == 1) {
+    const float mu = S.mu_f;
+    double v[2] = {0.0, 0.0};
+    for (int x = threadIdx.x; x < n; x += blockDim.x) {
+      if (roi[row + x] && !(has_sat && sat[fr + row + x])) {
+        float m = __fsub_rn(__fdiv_rn(norm[fr + row + x], mu), 1.0f);
+        v[0] += (double)(z[x].x * m);
+        v[1] += (double)(z[x].y * m);
+      }
+    }
+    block_sum<2>(v, red);
+    if (threadIdx.x == 0) { atomicAdd(&S.csum[0], v[0]); atomicAdd(&S.csum[1], v[1]); }
+  } else {
+    const double phi0 = atan2(S.csum[1], S.csum[0]);
+    const double cs = cos(phi0), sn = sin(phi0);
+    double v[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int x = threadIdx.x; x < n; x += blockDim.x) {
+      int mA = 0;
+      if (roi[row + x] && !(has_sat && sat[fr + row + x])) {
+        float s = (float)((double)z[x].x * cs + (double)z[x].y * sn);
+        float g = (float)gray8[fr + row + x];
+        if (s >= 0.f) { mA = 1; v[0] += g; v[1] += 1.0; } else { v[2] += g; v[3] += 1.0; }
+      }
+      maskA[fr + row + x] = (uint8_t)mA;
+    }
+    block_sum<4>(v, red);
+    if (threadIdx.x == 0) {
+      atomicAdd(&S.sumA, v[0]); atomicAdd(&S.cntA, (unsigned)v[1]);
+      atomicAdd(&S.sumB, v[2]); atomicAdd(&S.cntB, (unsigned)v[3]);
+    }
+  }
+}
+
+__global__ void k_temp_choose_dark(TempScal* sc) {
+  TempScal& s = sc[blockIdx.x];
+  double ma = s.cntA ? s.sumA / s.cntA : 1e9, mb = s.cntB ? s.sumB / s.cntB : 1e9;
+  s.a_is_dark = ma <= mb ? 1 : 0;
+}
+
+// dark candidate before morphology: A or (roi_eff & ~A)  (temperature_sensor.py:482-489)
+struct DarkLoad {
+  const uint8_t* maskA; const uint8_t* roi; const uint8_t* sat; const TempScal* sc; long long plane; int w; int ybeg, yend;
+  __device__ int operator()(int b, int y, int x) const {
+    if (y < ybeg || y >= yend) return 0;             // maskA is only written for ROI rows
+    long long i = (long long)y * w + x;
+    if (!roi[i] || sat_at(sc[b], sat + (long long)b * plane, i)) return 0;
+    int a = maskA[(long long)b * plane + i] != 0;
+    return sc[b].a_is_dark ? a : !a;
+  }
+};
+struct PostRoiEff {
+  const uint8_t* roi; const uint8_t* sat; const TempScal* sc; long long plane; int w;
+  __device__ int operator()(int b, int y, int x, int v) const {
+    long long i = (long long)y * w + x;
+    return v && roi[i] && !sat_at(sc[b], sat + (long long)b * plane, i);
+  }
+};
+
+// ------------------------------------------------------------------ T7-T11: features, models, fusion
+struct DevModel {
+  int nfeat, nterms, niso, pad;
+  float mean[4], scale[4];
+  int prev[VISTAF_MAX_TERMS], feat[VISTAF_MAX_TERMS];   // XP[t] = XP[prev[t]] * z[feat[t]]  (sklearn build order)
+  double coef[VISTAF_MAX_TERMS];
+  double intercept;
+  double iso_x[VISTAF_MAX_ISO], iso_y[VISTAF_MAX_ISO];
+};
+
+// StandardScaler (float32) -> PolynomialFeatures (float32 products) -> dot (float64) -> float32
+// [-> isotonic clip + linear interpolation in float64 -> float32]   (temperature_sensor.py:236-240)
+__device__ float model_predict(const DevModel* __restrict__ M, const float* x) {
+  float z[4], XP[VISTAF_MAX_TERMS];
+  const int nf = M->nfeat, nt = M->nterms;
+  for (int i = 0; i < nf; i++) z[i] = __fdiv_rn(__fsub_rn(x[i], M->mean[i]), M->scale[i]);
+  XP[0] = 1.0f;
+  double acc = M->intercept + M->coef[0];
+  for (int t = 1; t < nt; t++) {
+    float v = M->prev[t] == 0 ? z[M->feat[t]] : __fmul_rn(XP[M->prev[t]], z[M->feat[t]]);
+    XP[t] = v;
+    acc = fma(M->coef[t], (double)v, acc);
+  }
+  float pred = (float)acc;
+  if (M->niso > 0) {
+    const int n = M->niso;
+    double v = fmin(fmax((double)pred, M->iso_x[0]), M->iso_x[n - 1]);
+    int lo = 0, hi = n - 1;                       // largest j with iso_x[j] <= v
+    while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (M->iso_x[mid] <= v) lo = mid; else hi = mid; }
+    if (v >= M->iso_x[n - 1]) pred = (float)M->iso_y[n - 1];
+    else if (v == M->iso_x[lo]) pred = (float)M->iso_y[lo];
+    else {
+      double slope = (M->iso_y[lo + 1] - M->iso_y[lo]) / (M->iso_x[lo + 1] - M->iso_x[lo]);
+      pred = (float)(slope * (v - M->iso_x[lo]) + M->iso_y[lo]);
+    }
+  }
+  return pred;
+}
+
+struct FeatArgs {
+  const uint8_t* frames; const uint8_t* roi; const uint8_t* sat; const uint8_t* dark;
+  TempScal* sc; const DevModel* models; const int* gam; const int* cbr;
+  float* fused; uint8_t *o_sat, *o_light, *o_support, *o_colorok, *o_source;
+  int h, w;
+  float color_lo, color_hi, ok_lo, ok_hi, blend_lo, blend_hi, final_lo, final_hi, chroma_min;
+};
+
+#define FT_W 32
+#define FT_H 16
+__global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
+  __shared__ uint8_t tile[(FT_H + 4) * (FT_W + 4) * 3];
+  const int b = blockIdx.z, x0 = blockIdx.x * FT_W, y0 = blockIdx.y * FT_H, h = a.h, w = a.w;
+  const size_t plane = (size_t)h * w;
+  const uint8_t* img = a.frames + (size_t)b * plane * 3;
+  const int tid = threadIdx.y * FT_W + threadIdx.x;
+  // 5x5 Gaussian on uint8 uses BORDER_REFLECT_101 (cv2.GaussianBlur default)
+  for (int e = tid; e < (FT_H + 4) * (FT_W + 4); e += FT_W * FT_H) {
+    int ty = e / (FT_W + 4), tx = e - ty * (FT_W + 4);
+    int y = reflect101(y0 - 2 + ty, h), x = reflect101(x0 - 2 + tx, w);
+    const uint8_t* p = img + ((size_t)y * w + x) * 3;
+    tile[e * 3] = p[0]; tile[e * 3 + 1] = p[1]; tile[e * 3 + 2] = p[2];
+  }
+  __syncthreads();
+  const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
+  int n_ok = 0, n_dark = 0;
+  if (x < w && y < h) {
+    const size_t i = (size_t)y * w + x, bi = (size_t)b * plane + i;
+    const TempScal& S = a.sc[b];
+    const bool in_roi = a.roi[i] != 0;
+    const bool is_sat = in_roi && sat_at(S, a.sat + (size_t)b * plane, i);
+    float fused = __int_as_float(0x7fc00000);
+    int light = 0, support = 0, cok = 0, source = 0;
+    if (in_roi) {
+      const bool roi_eff = !is_sat;
+      const int is_dark = a.dark[bi] != 0;
+      light = roi_eff && !is_dark;
+      n_dark += is_dark;
+      // blurred BGR: ((1 4 6 4 1)x(1 4 6 4 1) * p + 128) >> 8
+      const int kw[5] = {1, 4, 6, 4, 1};
+      int s[3] = {0, 0, 0};
+#pragma unroll
+      for (int dy = 0; dy < 5; dy++)
+#pragma unroll
+        for (int dx = 0; dx < 5; dx++) {
+          const uint8_t* p = tile + ((threadIdx.y + dy) * (FT_W + 4) + threadIdx.x + dx) * 3;
+          int k = kw[dy] * kw[dx];
+          s[0] += k * p[0]; s[1] += k * p[1]; s[2] += k * p[2];
+        }
+      const int B = (s[0] + 128) >> 8, Gc = (s[1] + 128) >> 8, Rc = (s[2] + 128) >> 8;
+      // OpenCV 8-bit BGR2Lab, integer path (tables verified on all 2^24 colours, tools/make_lab_lut.py)
+      const int R = __ldg(a.gam + Rc), G = __ldg(a.gam + Gc), Bl = __ldg(a.gam + B);
+      const int fX = __ldg(a.cbr + ((R * 1777 + G * 1541 + Bl * 778 + 2048) >> 12));
+      const int fY = __ldg(a.cbr + ((R * 871 + G * 2929 + Bl * 296 + 2048) >> 12));
+      const int fZ = __ldg(a.cbr + ((R * 73 + G * 448 + Bl * 3575 + 2048) >> 12));
+      int L = (296 * fY - 1336934 + 16384) >> 15;
+      int A = (500 * (fX - fY) + 128 * 32768 + 16384) >> 15;
+      int Bb = (200 * (fY - fZ) + 128 * 32768 + 16384) >> 15;
+      L = min(max(L, 0), 255); A = min(max(A, 0), 255); Bb = min(max(Bb, 0), 255);
+      const int gray = gray8_of(B, Gc, Rc);
+      const float feat[4] = {(float)L, (float)A, (float)Bb, (float)gray};
+      // colour support: dilate(light, 3x3 cross) & roi_eff & ~sat & chroma >= 10  (temperature_sensor.py:795-799)
+      int light_d = light;
+      if (!light_d && roi_eff) {
+        const int nx[4] = {x - 1, x + 1, x, x}, ny[4] = {y, y, y - 1, y + 1};
+        for (int q = 0; q < 4 && !light_d; q++) {
+          if (nx[q] < 0 || nx[q] >= w || ny[q] < 0 || ny[q] >= h) continue;
+          size_t j = (size_t)ny[q] * w + nx[q];
+          if (a.roi[j] && !sat_at(S, a.sat + (size_t)b * plane, j) && !a.dark[(size_t)b * plane + j]) light_d = 1;
+        }
+      }
+      const int ca = A - 128, cb = Bb - 128;
+      support = light_d && roi_eff && (sqrtf((float)(ca * ca + cb * cb)) >= a.chroma_min);
+      float wide = __int_as_float(0x7fc00000), color = wide;
+      if (roi_eff) wide = fminf(fmaxf(model_predict(a.models + 1, feat), a.final_lo), a.final_hi);
+      if (support) color = fminf(fmaxf(model_predict(a.models + 0, feat), a.color_lo), a.color_hi);
+      // fusion (temperature_sensor.py:594-641)
+      const bool wide_ok = roi_eff;                 // finite
+      cok = support && color >= a.ok_lo && color <= a.ok_hi;
+      fused = wide;
+      if (cok) { fused = color; source = 255; }
+      if (wide_ok && cok && wide > a.blend_lo && wide < a.blend_hi) {
+        float wg = __fdiv_rn(__fsub_rn(a.blend_hi, wide), __fsub_rn(a.blend_hi, a.blend_lo));
+        wg = fminf(fmaxf(wg, 0.f), 1.f);
+        fused = __fadd_rn(__fmul_rn(wg, color), __fmul_rn(__fsub_rn(1.0f, wg), wide));
+        source = 128;
+      }
+      if (fused == fused) fused = fminf(fmaxf(fused, a.final_lo), a.final_hi);
+      n_ok += cok;
+    }
+    a.fused[bi] = fused;
+    if (a.o_sat) a.o_sat[bi] = is_sat;
+    if (a.o_light) a.o_light[bi] = light;
+    if (a.o_support) a.o_support[bi] = support;
+    if (a.o_colorok) a.o_colorok[bi] = cok;
+    if (a.o_source) a.o_source[bi] = source;
+  }
+  n_ok = warp_sum(n_ok);
+  n_dark = warp_sum(n_dark);
+  if ((tid & 31) == 0) {
+    if (n_ok) atomicAdd(&a.sc[b].color_ok_count, (unsigned)n_ok);
+    if (n_dark) atomicAdd(&a.sc[b].dark_count, (unsigned)n_dark);
+  }
+}
+
+// ------------------------------------------------------------------ T12: oriented smoothing + M1 statistics
+// angle == 0 (all demo and synthetic frames): the rotations are identity warps, so the step reduces to an
+// anisotropic Gaussian (sigma_x = across, sigma_y = along) of the map with NaN -> 0, then NaN outside the
+// ROI and a clamp (temperature_sensor.py:705-742, 853-859).
+struct FusedLoad {
+  const float* fused; long long plane; int w;
+  __device__ float operator()(int b, int y, int x) const {
+    float v = fused[(long long)b * plane + (long long)y * w + x];
+    return v == v ? v : 0.f;
+  }
+};
+struct FinalStore {
+  const uint8_t* roi; float* out; TempScal* sc; long long plane; int w; float lo, hi;
+  double s1, s2; float mn, mx; unsigned int cnt;
+  __device__ void operator()(int b, int y, int x, float v) {
+    long long i = (long long)y * w + x;
+    float r = __int_as_float(0x7fc00000);
+    if (roi[i]) {
+      r = fminf(fmaxf(v, lo), hi);
+      s1 += (double)r; s2 += (double)r * (double)r;
+      mn = fminf(mn, r); mx = fmaxf(mx, r); cnt++;
+    }
+    out[(long long)b * plane + i] = r;
+  }
+  __device__ void finish(int b) {
+    __shared__ double sh[3 * 32];
+    __shared__ float shm[2 * 32];
+    double v[3] = {s1, s2, (double)cnt};
+    block_sum<3>(v, sh);
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int nw = (blockDim.x * blockDim.y + 31) >> 5;
+    float a = warp_min(mn), c = warp_max(mx);
+    __syncthreads();
+    if (lane == 0) { shm[wid] = a; shm[32 + wid] = c; }
+    __syncthreads();
+    if (tid == 0) {
+      for (int i = 1; i < nw; i++) { a = fminf(a, shm[i]); c = fmaxf(c, shm[32 + i]); }
+      if (v[2] > 0.0) {
+        atomicAdd(&sc[b].t_sum, v[0]); atomicAdd(&sc[b].t_sumsq, v[1]); atomicAdd(&sc[b].t_count, (unsigned)v[2]);
+        atomicMin((int*)&sc[b].t_min, __float_as_int(a));      // temperatures are positive: int order == float order
+        atomicMax((int*)&sc[b].t_max, __float_as_int(c));
+      }
+    }
+  }
+};
+struct FinalVal {              // value stream for the median: final map over the ROI
+  const float* fin; const uint8_t* roi; long long plane;
+  __device__ bool operator()(int b, long long i, float& v) const {
+    if (!roi[i]) return false;
+    v = fin[(long long)b * plane + i];
+    return v == v;
+  }
+};
+
+__global__ void k_temp_init(TempScal* sc, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  TempScal z;
+  memset(&z, 0, sizeof(z));
+  z.t_min = 3.0e38f; z.t_max = 0.f;
+  sc[i] = z;
+}
+
+__global__ void k_temp_records(const TempScal* sc, const SelectState* sel, VistafTempRecord* rec, int n, int cx, int cy) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const TempScal& s = sc[i];
+  VistafTempRecord r;
+  memset(&r, 0, sizeof(r));
+  const double cnt = (double)s.t_count;
+  if (s.t_count) {
+    double mean = s.t_sum / cnt;
+    double var = fmax(s.t_sumsq / cnt - mean * mean, 0.0);
+    r.mean_C = (float)mean; r.std_C = (float)sqrt(var); r.min_C = s.t_min; r.max_C = s.t_max;
+    r.median_C = sel[i].result;
+  } else {
+    r.mean_C = r.std_C = r.min_C = r.max_C = r.median_C = __int_as_float(0x7fc00000);
+  }
+  r.valid_pixels = (int)s.t_count;
+  r.peak_x = s.peak_x; r.peak_y = s.peak_y;
+  r.phi0 = (float)atan2(s.csum[1], s.csum[0]);
+  r.mean_gray_a = s.cntA ? (float)(s.sumA / s.cntA) : 1e9f;
+  r.mean_gray_b = s.cntB ? (float)(s.sumB / s.cntB) : 1e9f;
+  r.median_gray = s.median;
+  r.sat_pixels = (int)s.sat_count; r.roi_eff_pixels = (int)s.n_eff;
+  r.dark_pixels = (int)s.dark_count; r.color_ok_pixels = (int)s.color_ok_count;
+  r.status = (int)s.status | (s.sat_count ? VISTAF_ST_SATURATED : 0);
+  rec[i] = r;
+}
+
+// ================================================================== host side
+static void temp_layout(const VistafTempPlan* p, int chunk, TempWs& L) {
+  const size_t npix = (size_t)p->H * p->W, c = (size_t)chunk;
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t r = o; o += align256(bytes); return r; };
+  L.gray8 = take(c * npix);
+  L.satraw = take(c * npix);
+  L.sat = take(c * npix);
+  L.norm = take(c * npix * 4);
+  L.tmp = take(c * npix * 4);
+  L.A = take(c * (size_t)p->H * p->Wh * 8);
+  L.G = take(c * (size_t)p->H * MAXBAND * 8);
+  L.maskA = take(c * npix);
+  L.m1 = take(c * npix);
+  L.m2 = take(c * npix);
+  L.cand = take(c * (size_t)p->nblk_cols * TOPK * sizeof(Cand));
+  L.scal = take(c * sizeof(TempScal));
+  L.sel = take(c * sizeof(SelectState));
+  L.total = o;
+}
+
+static int build_dev_model(const VistafPolyModel& m, DevModel& d) {
+  memset(&d, 0, sizeof(d));
+  d.nfeat = m.n_features; d.nterms = m.n_terms; d.niso = m.n_iso;
+  if (d.nfeat < 1 || d.nfeat > 4 || d.nterms < 1 || d.nterms > VISTAF_MAX_TERMS || d.niso > VISTAF_MAX_ISO)
+    return vistaf_set_err("model shape out of range", cudaErrorInvalidValue, __FILE__, __LINE__);
+  for (int i = 0; i < d.nfeat; i++) { d.mean[i] = (float)m.mean[i]; d.scale[i] = (float)m.scale[i]; }
+  for (int t = 0; t < d.nterms; t++) {
+    d.coef[t] = m.coef[t];
+    int deg = 0, low = -1;
+    for (int f = 0; f < d.nfeat; f++) { deg += m.powers[t][f]; if (low < 0 && m.powers[t][f] > 0) low = f; }
+    if (deg == 0) { if (t != 0) return vistaf_set_err("bias term must be first", cudaErrorInvalidValue, __FILE__, __LINE__); continue; }
+    int want[4] = {0, 0, 0, 0};
+    for (int f = 0; f < d.nfeat; f++) want[f] = m.powers[t][f] - (f == low ? 1 : 0);
+    int prev = -1;
+    for (int u = 0; u < t; u++) {
+      bool eq = true;
+      for (int f = 0; f < d.nfeat; f++) eq = eq && m.powers[u][f] == want[f];
+      if (eq) { prev = u; break; }
+    }
+    if (prev < 0) return vistaf_set_err("polynomial terms not in PolynomialFeatures order", cudaErrorInvalidValue, __FILE__, __LINE__);
+    d.prev[t] = prev; d.feat[t] = low;
+  }
+  d.intercept = m.intercept;
+  for (int i = 0; i < d.niso; i++) { d.iso_x[i] = m.iso_x[i]; d.iso_y[i] = m.iso_y[i]; }
+  return 0;
+}
+
+extern "C" int vistaf_temp_plan_create(const VistafTempParams* P, VistafTempPlan** out) {
+  if (!P || !out) return vistaf_set_err("null argument", cudaErrorInvalidValue, __FILE__, __LINE__);
+  if (P->width % 4 || P->band_radius * 2 + 1 > MAXBAND || P->sat_dilate > MORPH_MAXROWS || P->close_ky > MORPH_MAXROWS)
+    return vistaf_set_err("unsupported temperature parameters", cudaErrorInvalidValue, __FILE__, __LINE__);
+  VistafTempPlan* p = new (std::nothrow) VistafTempPlan();
+  if (!p) return vistaf_set_err("out of host memory", cudaErrorMemoryAllocation, __FILE__, __LINE__);
+  memset(p, 0, sizeof(*p));
+  p->P = *P;
+  p->H = P->height; p->W = P->width; p->Wh = P->width / 2 + 1;
+  p->nblk_cols = cdiv(p->Wh, COLS_PER_BLOCK);
+  if (fft1d_create(&p->fw, p->W) || fft1d_create(&p->fh, p->H)) return 1;
+  if ((size_t)p->W * 16 > 200 * 1024 || (size_t)COLS_PER_BLOCK * (p->H + 1) * 16 > 220 * 1024)
+    return vistaf_set_err("frame too large for the shared-memory FFT", cudaErrorInvalidValue, __FILE__, __LINE__);
+  p->g_illum = make_gauss(P->illum_sigma);
+  p->g_across = make_gauss(P->sigma_across);
+  p->g_along = make_gauss(P->sigma_along);
+  p->se_sat = se_ellipse(P->sat_dilate | 1);
+  const size_t npix = (size_t)p->H * p->W;
+  CK(cudaMalloc(&p->roi, npix));
+  k_roi_mask<<<dim3(cdiv(p->W, 256), p->H), 256>>>(p->roi, p->H, p->W, P->roi_cx, P->roi_cy, P->roi_r * P->roi_r);
+  CKL();
+  uint8_t* hroi = new uint8_t[npix];
+  CK(cudaMemcpy(hroi, p->roi, npix, cudaMemcpyDeviceToHost));
+  p->y0 = p->H; p->y1 = 0; p->x0 = p->W; p->x1 = 0;
+  for (int y = 0; y < p->H; y++)
+    for (int x = 0; x < p->W; x++)
+      if (hroi[(size_t)y * p->W + x]) {
+        if (y < p->y0) p->y0 = y;
+        if (y + 1 > p->y1) p->y1 = y + 1;
+        if (x < p->x0) p->x0 = x;
+        if (x + 1 > p->x1) p->x1 = x + 1;
+      }
+  delete[] hroi;
+  if (p->y1 <= p->y0) { p->y0 = 0; p->y1 = 1; p->x0 = 0; p->x1 = 1; }
+  DevModel dm[2];
+  if (build_dev_model(P->color_model, dm[0]) || build_dev_model(P->wide_model, dm[1])) return 1;
+  CK(cudaMalloc(&p->models, sizeof(dm)));
+  CK(cudaMemcpy(p->models, dm, sizeof(dm), cudaMemcpyHostToDevice));
+  CK(cudaMalloc(&p->lab_gamma, sizeof(int) * 256));
+  CK(cudaMalloc(&p->lab_cbrt, sizeof(int) * 3072));
+  CK(cudaMemcpy(p->lab_gamma, P->lab_gamma, sizeof(int) * 256, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(p->lab_cbrt, P->lab_cbrt, sizeof(int) * 3072, cudaMemcpyHostToDevice));
+  // opt-in shared memory for the FFT kernels
+  CK(cudaFuncSetAttribute((const void*)k_temp_fft_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, p->W * 16));
+  CK(cudaFuncSetAttribute((const void*)k_temp_ifft_rows<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->W * 16));
+  CK(cudaFuncSetAttribute((const void*)k_temp_ifft_rows<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->W * 16));
+  CK(cudaFuncSetAttribute((const void*)k_temp_fft_cols_peaks, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                          COLS_PER_BLOCK * (p->H + 1) * 16));
+  CK(cudaFuncSetAttribute((const void*)k_temp_peak_select, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                          2 * p->nblk_cols * TOPK * 4));
+  CK(cudaDeviceSynchronize());
+  *out = p;
+  return 0;
+}
+
+extern "C" void vistaf_temp_plan_destroy(VistafTempPlan* p) {
+  if (!p) return;
+  fft1d_destroy(&p->fw); fft1d_destroy(&p->fh);
+  cudaFree(p->roi); cudaFree(p->models); cudaFree(p->lab_gamma); cudaFree(p->lab_cbrt);
+  delete p;
+}
+
+extern "C" size_t vistaf_temp_workspace_bytes(const VistafTempPlan* p, int chunk) {
+  TempWs L;
+  temp_layout(p, chunk < 1 ? 1 : chunk, L);
+  return L.total;
+}
+
+extern "C" int vistaf_temp_roi_mask(const VistafTempPlan* p, uint8_t* dst, void* stream) {
+  CK(cudaMemcpyAsync(dst, p->roi, (size_t)p->H * p->W, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+
+extern "C" int vistaf_temp_workspace_plane(const VistafTempPlan* p, int chunk, const char* name, size_t* off, size_t* bytes) {
+  TempWs L;
+  temp_layout(p, chunk, L);
+  const size_t npix = (size_t)p->H * p->W;
+  struct { const char* n; size_t o, b; } tab[] = {
+      {"gray8", L.gray8, npix}, {"satraw", L.satraw, npix}, {"sat", L.sat, npix}, {"norm", L.norm, npix * 4},
+      {"A", L.A, (size_t)p->H * p->Wh * 8}, {"G", L.G, (size_t)p->H * MAXBAND * 8}, {"maskA", L.maskA, npix},
+      {"scal", L.scal, sizeof(TempScal)}, {"cand", L.cand, (size_t)p->nblk_cols * TOPK * sizeof(Cand)}};
+  for (auto& t : tab)
+    if (!strcmp(t.n, name)) { *off = t.o; *bytes = t.b; return 0; }
+  return vistaf_set_err("unknown workspace plane", cudaErrorInvalidValue, __FILE__, __LINE__);
+}
+
+static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const VistafTempOutputs& O, size_t f0,
+                      char* ws, const TempWs& L, cudaStream_t st) {
+  const VistafTempParams& P = p->P;
+  const int H = p->H, W = p->W, Wh = p->Wh;
+  const int npix = H * W;
+  const long long plane = (long long)npix;
+  uint8_t* gray8 = (uint8_t*)(ws + L.gray8);
+  uint8_t* satraw = (uint8_t*)(ws + L.satraw);
+  uint8_t* sat = (uint8_t*)(ws + L.sat);
+  float* norm = (float*)(ws + L.norm);
+  float* tmp = (float*)(ws + L.tmp);
+  float2* A = (float2*)(ws + L.A);
+  float2* G = (float2*)(ws + L.G);
+  uint8_t* maskA = (uint8_t*)(ws + L.maskA);
+  uint8_t* m1 = (uint8_t*)(ws + L.m1);
+  uint8_t* m2 = (uint8_t*)(ws + L.m2);
+  Cand* cand = (Cand*)(ws + L.cand);
+  TempScal* sc = (TempScal*)(ws + L.scal);
+  SelectState* sel = (SelectState*)(ws + L.sel);
+  const uint8_t* fr = frames + f0 * (size_t)npix * 3;
+
+  k_temp_init<<<cdiv(nb, 128), 128, 0, st>>>(sc, nb);
+  k_temp_gray<<<dim3(cdiv(npix / 4, 256), nb), 256, 0, st>>>(fr, p->roi, gray8, satraw, sc, npix, P.sat_thresh);
+  k_temp_sat_dilate<<<dim3(cdiv(W, 256), H, nb), 256, 0, st>>>(satraw, p->roi, sat, sc, H, W, p->se_sat);
+  k_temp_hist<<<dim3(296, nb), 256, 0, st>>>(gray8, p->roi, sat, sc, npix);
+  k_temp_median<<<nb, 32, 0, st>>>(sc);
+  CKL();
+  // illumination normalisation
+  IllumLoad il{gray8, p->roi, sc, plane, W};
+  IllumStore is{gray8, p->roi, sat, sc, norm, plane, W, 0.0};
+  if (gauss_blur(il, is, tmp, H, W, nb, p->g_illum, p->g_illum, st)) return 1;
+  k_temp_mu<<<nb, 1, 0, st>>>(sc);
+  // forward FFT + carrier peak
+  k_temp_fft_rows<<<dim3(cdiv(H, 2), nb), 256, (size_t)W * 16, st>>>(norm, A, sc, p->fw, H, Wh);
+  k_temp_fft_cols_peaks<<<dim3(p->nblk_cols, nb), 512, (size_t)COLS_PER_BLOCK * (H + 1) * 16, st>>>(A, cand, p->fh, W, Wh,
+                                                                                                  P.dc_exclusion);
+  const int ncand = p->nblk_cols * TOPK;
+  k_temp_peak_select<<<nb, 256, (size_t)2 * ncand * 4, st>>>(cand, sc, ncand, H, W, P.dc_exclusion, P.peak_max_dy_frac);
+  CKL();
+  // band-pass + inverse
+  const int R = P.band_radius, nbnd = 2 * R + 1;
+  k_temp_band<<<dim3(nbnd, nb), 256, (size_t)H * 8, st>>>(A, G, sc, p->fh, W, Wh, R);
+  const int nrows = p->y1 - p->y0;
+  k_temp_ifft_rows<1><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R);
+  k_temp_ifft_rows<2><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R);
+  k_temp_choose_dark<<<nb, 1, 0, st>>>(sc);
+  CKL();
+  // close RECT(kx x ky) then open RECT(kx x ky), then & roi_eff  (temperature_sensor.py:390-406, 490)
+  DarkLoad dl{maskA, p->roi, sat, sc, plane, W, p->y0, p->y1};
+  MorphSE se_c = se_rect(P.close_kx | 1, P.close_ky | 1), se_o = se_rect(P.open_kx | 1, P.open_ky | 1);
+  uint8_t* dark = O.dark ? O.dark + f0 * (size_t)npix : maskA;      // final dark mask destination
+  if (morph<true>(dl, PostId(), m1, H, W, nb, se_c, st)) return 1;
+  if (morph<false>(MaskLoad{m1, plane, W}, PostId(), m2, H, W, nb, se_c, st)) return 1;
+  if (morph<false>(MaskLoad{m2, plane, W}, PostId(), m1, H, W, nb, se_o, st)) return 1;
+  if (morph<true>(MaskLoad{m1, plane, W}, PostRoiEff{p->roi, sat, sc, plane, W}, dark, H, W, nb, se_o, st)) return 1;
+  // features, models, fusion
+  FeatArgs fa;
+  fa.frames = fr; fa.roi = p->roi; fa.sat = sat; fa.dark = dark; fa.sc = sc;
+  fa.models = (const DevModel*)p->models; fa.gam = p->lab_gamma; fa.cbr = p->lab_cbrt;
+  fa.fused = O.fused + f0 * (size_t)npix;
+  fa.o_sat = O.sat ? O.sat + f0 * (size_t)npix : nullptr;
+  fa.o_light = O.light ? O.light + f0 * (size_t)npix : nullptr;
+  fa.o_support = O.color_support ? O.color_support + f0 * (size_t)npix : nullptr;
+  fa.o_colorok = O.color_ok ? O.color_ok + f0 * (size_t)npix : nullptr;
+  fa.o_source = O.source ? O.source + f0 * (size_t)npix : nullptr;
+  fa.h = H; fa.w = W;
+  fa.color_lo = P.color_t_min - 5.0f; fa.color_hi = P.color_t_max + 5.0f;
+  fa.ok_lo = P.color_t_min - P.guard_band; fa.ok_hi = P.color_t_max + P.guard_band;
+  fa.blend_lo = P.color_t_max - P.switch_margin; fa.blend_hi = P.color_t_max + P.switch_margin;
+  fa.final_lo = P.final_t_min; fa.final_hi = P.final_t_max; fa.chroma_min = P.chroma_min;
+  k_temp_features<<<dim3(cdiv(W, FT_W), cdiv(H, FT_H), nb), dim3(FT_W, FT_H), 0, st>>>(fa);
+  CKL();
+  // oriented smoothing (axis aligned) + statistics
+  float* fin = O.final_map + f0 * (size_t)npix;
+  FusedLoad fl{fa.fused, plane, W};
+  FinalStore fs{p->roi, fin, sc, plane, W, P.final_t_min, P.final_t_max, 0.0, 0.0, 3.0e38f, 0.f, 0u};
+  if (gauss_blur(fl, fs, tmp, H, W, nb, p->g_across, p->g_along, st)) return 1;
+  FinalVal fv{fin, p->roi, plane};
+  if (select_quantile(fv, sel, (long long)npix, nb, -1.0f, true, st)) return 1;
+  k_temp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, sel, O.records + f0, nb, W / 2, H / 2);
+  CKL();
+  return 0;
+}
+
+extern "C" int vistaf_temp_batch(VistafTempPlan* p, const uint8_t* frames, int batch, const VistafTempOutputs* out,
+                                 void* workspace, size_t ws_bytes, void* stream) {
+  if (!p || !frames || !out || !out->fused || !out->final_map || !out->records || !workspace)
+    return vistaf_set_err("vistaf_temp_batch: null argument", cudaErrorInvalidValue, __FILE__, __LINE__);
+  TempWs L1;
+  temp_layout(p, 1, L1);
+  int chunk = (int)(ws_bytes / L1.total);
+  if (chunk > batch) chunk = batch;
+  TempWs L;
+  while (chunk >= 1) { temp_layout(p, chunk, L); if (L.total <= ws_bytes) break; chunk--; }
+  if (chunk < 1) return vistaf_set_err("vistaf_temp_batch: workspace too small for one frame", cudaErrorInvalidValue, __FILE__, __LINE__);
+  for (int f0 = 0; f0 < batch; f0 += chunk) {
+    int nb = batch - f0 < chunk ? batch - f0 : chunk;
+    if (temp_chunk(p, frames, nb, *out, (size_t)f0, (char*)workspace, L, (cudaStream_t)stream)) return 1;
+  }
+  return 0;
+}
