@@ -105,6 +105,93 @@ int vistaf_temp_roi_mask(const VistafTempPlan* plan, uint8_t* roi_dev, void* cud
 /* debugging / parity: name -> byte offset and size of an intermediate plane of frame 0 in the workspace */
 int vistaf_temp_workspace_plane(const VistafTempPlan* plan, int chunk, const char* name, size_t* offset, size_t* bytes);
 
+/* ------------------------------------------------------------------ FTP shape + force path */
+/* calibrated curve families shared by shape_ftp.model_predict (:682) and force_sensor (:129-140) */
+#define VISTAF_MODEL_LINEAR0 0
+#define VISTAF_MODEL_LINEAR 1
+#define VISTAF_MODEL_POLY2 2
+#define VISTAF_MODEL_SAT_EXP 3
+#define VISTAF_MODEL_GROWTH 4
+#define VISTAF_MODEL_HINGE_SAT 5
+
+typedef struct {
+  int32_t type;          /* VISTAF_MODEL_* */
+  int32_t pad_;
+  double p[3];           /* (a) | (a,b) | (c2,c1,c0) | (a,b) | (a,b) | (a,b,c) */
+} VistafCurveModel;
+
+/* shape_ftp.py:16-218 (constants read by the numeric path) on an (crop_h x crop_w) gray crop */
+typedef struct {
+  int32_t crop_h, crop_w;
+  int32_t cx, cy, r;                 /* ROI circle in crop coordinates (shape_ftp.py:1513-1516) */
+  int32_t roi_erode_px, apod_taper;
+  int32_t patch_half, dc_exclusion, n_peaks, fft_pad;
+  float peak_max_dy_frac;
+  float illum_sigma, pre_blur_sigma, quality_sigma, smooth_sigma, unrel_sigma;
+  float amp_percentile;
+  int32_t close_kernel, edge_margin;
+  float bad_int_pct, bad_grad_pct;
+  int32_t bad_dilate, bad_inpaint_radius;
+  float core_pct, contact_pct;
+  int32_t dilate_kernel, dilate_iters;
+  float min_contact_frac, max_contact_frac;
+  float frontier_band;
+  float blob_min_peak_mm, blob_rel_frac;
+  int32_t use_negated_height;        /* calibration JSON use_negated_height_for_fit */
+  int32_t pad_;
+  VistafCurveModel height_model;     /* phase -> mm   (shape_ftp.py:672-705) */
+  VistafCurveModel force_model;      /* cm^3 -> N     (force_sensor.py:149-167) */
+  double grating_pitch_mm, depth_eps_mm;   /* force_sensor.py:32-33 */
+} VistafFtpParams;
+
+typedef struct {
+  double force_N, volume_cm3, contact_area_mm2, max_depth_mm;   /* multimodal_sensor.py:412-419 */
+  double mm_per_px, period_px;
+  float amp_thr, contact_thr, bg_median, core_median;
+  int32_t reliable_px, output_reliable_px, contact_dilated_px, contact_kept_px, bad_px, residues;
+  int32_t seed_x, seed_y;
+  int32_t status;
+  int32_t pad_;
+} VistafFtpRecord;                                   /* 104 bytes */
+
+typedef struct {
+  float* height_mm;          /* [B][h][w] depth map in mm, NaN outside the ROI (height_map_mm_crop) */
+  uint8_t* reliable;         /* [B][h][w] 0/1; any mask may be NULL */
+  uint8_t* output_reliable;
+  uint8_t* contact_dilated;
+  uint8_t* contact_kept;
+  VistafFtpRecord* records;  /* [B] */
+} VistafFtpOutputs;
+
+typedef struct {
+  float peak_x, peak_y;      /* refined carrier peak (fftshift-ed bins of the padded FFT) */
+  int32_t fft_h, fft_w;
+  float kx, ky, period_px;
+  int32_t bad_px;
+} VistafFtpReferenceInfo;
+
+typedef struct VistafFtpPlan VistafFtpPlan;
+
+int vistaf_ftp_plan_create(const VistafFtpParams* params, VistafFtpPlan** plan);
+void vistaf_ftp_plan_destroy(VistafFtpPlan* plan);
+size_t vistaf_ftp_workspace_bytes(const VistafFtpPlan* plan, int chunk);
+/* crop + cv2 BGR2GRAY of full frames (shape_ftp.py:1508-1511): frames DEVICE uint8 [B][H][W][3] -> gray DEVICE uint8 [B][h][w] */
+int vistaf_crop_gray(const uint8_t* frames_bgr, int batch, int H, int W, int x1, int y1, int h, int w, uint8_t* gray,
+                     void* cuda_stream);
+/* reference-frame half of shape_ftp.py:1632-1639 (dense FFT, carrier search, demodulation); cached in the plan */
+int vistaf_ftp_set_reference(VistafFtpPlan* plan, const uint8_t* ref_gray, void* workspace, size_t workspace_bytes,
+                             VistafFtpReferenceInfo* info, void* cuda_stream);
+/* deformed frames: gray DEVICE uint8 [B][h][w] (already aligned); shape_ftp.py:1641-1865 + force_sensor.py:93-167 */
+int vistaf_ftp_batch(VistafFtpPlan* plan, const uint8_t* def_gray, int batch, const VistafFtpOutputs* out, void* workspace,
+                     size_t workspace_bytes, void* cuda_stream);
+int vistaf_ftp_masks(const VistafFtpPlan* plan, uint8_t* roi_dev, uint8_t* circ_dev, float* apo_dev, void* cuda_stream);
+int vistaf_ftp_workspace_plane(const VistafFtpPlan* plan, int chunk, const char* name, size_t* offset, size_t* bytes);
+/* force_sensor.depth_map_to_volume_cm3 (:93-123) on DEVICE maps: out3 = DEVICE float64 [B][3] (volume_cm3, area_mm2, max_depth_mm) */
+int vistaf_depth_to_volume(const float* height_mm, const uint8_t* roi_or_null, int batch, long long npix, double mm_per_px,
+                           double depth_eps_mm, double* out3, void* cuda_stream);
+/* host-side scalar: force_sensor.predict_force_from_volume (:149-167); returns NaN for an unknown type */
+double vistaf_curve_predict(const VistafCurveModel* model, double x);
+
 #ifdef __cplusplus
 }
 #endif

@@ -954,11 +954,10 @@ extern "C" int vistaf_temp_batch(VistafTempPlan* p, const uint8_t* frames, int b
                                  void* workspace, size_t ws_bytes, void* stream) {
   if (!p || !frames || !out || !out->fused || !out->final_map || !out->records || !workspace)
     return vistaf_set_err("vistaf_temp_batch: null argument", cudaErrorInvalidValue, __FILE__, __LINE__);
-  TempWs L1;
+  TempWs L1, L;
   temp_layout(p, 1, L1);
-  int chunk = (int)(ws_bytes / L1.total);
+  int chunk = (int)(ws_bytes / L1.total) + 1;        // per-plane alignment padding makes layout(n) <= n*layout(1)
   if (chunk > batch) chunk = batch;
-  TempWs L;
   while (chunk >= 1) { temp_layout(p, chunk, L); if (L.total <= ws_bytes) break; chunk--; }
   if (chunk < 1) return vistaf_set_err("vistaf_temp_batch: workspace too small for one frame", cudaErrorInvalidValue, __FILE__, __LINE__);
   for (int f0 = 0; f0 < batch; f0 += chunk) {
