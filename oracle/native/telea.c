@@ -176,7 +176,7 @@ static void telea(const void* img_, const uint8_t* mask_in, int h, int w, int ra
               if (f[pk] != INSIDE && ((l - j) * (l - j) + (k - i) * (k - i) <= range * range)) {
                 float ry = (float)(i - k), rx = (float)(j - l);
                 float len2 = rx * rx + ry * ry;
-                float dst = (float)(1. / (len2 * sqrt((double)len2)));
+                float dst = (float)(1. / (len2 * sqrtf(len2)));
                 float lev = (float)(1. / (1 + fabs(t[pk] - t[p])));
                 float dir = rx * gTx + ry * gTy;
                 if (fabs(dir) <= 0.01) dir = 0.000001f;
@@ -193,7 +193,7 @@ static void telea(const void* img_, const uint8_t* mask_in, int h, int w, int ra
                 } else {
                   if (f[pk - W] != INSIDE) gIy = O(kp, lm) - O(km - 1, lm); else gIy = 0;
                 }
-                Ia += wgt * O(km, lm);
+                Ia += wgt * O(k - 1, l - 1);
                 Jx -= wgt * (gIx * rx);
                 Jy -= wgt * (gIy * ry);
                 s += wgt;
@@ -203,12 +203,12 @@ static void telea(const void* img_, const uint8_t* mask_in, int h, int w, int ra
         }
         float sat;
         if (is_u8) {
-          sat = (float)((Ia / s + (Jx + Jy) / (sqrt(Jx * Jx + Jy * Jy) + 1.0e-20f) + 0.5f));
+          sat = (float)((Ia / s + (Jx + Jy) / (sqrtf(Jx * Jx + Jy * Jy) + 1.0e-20f) + 0.5f));
           int v = (int)lrintf(sat);                       /* cv::saturate_cast<uchar>(float) rounds to nearest even */
           v = v < 0 ? 0 : v > 255 ? 255 : v;
           O(i - 1, j - 1) = (float)v;
         } else {
-          sat = (float)((Ia / s + (Jx + Jy) / (sqrt(Jx * Jx + Jy * Jy) + 1.0e-20f)));
+          sat = (float)((Ia / s + (Jx + Jy) / (sqrtf(Jx * Jx + Jy * Jy) + 1.0e-20f)));
           O(i - 1, j - 1) = sat;
         }
 #undef O
