@@ -16,6 +16,7 @@
  */
 #ifndef VISTAF_H
 #define VISTAF_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
@@ -136,9 +137,8 @@ typedef struct {
   int32_t dilate_kernel, dilate_iters;
   float min_contact_frac, max_contact_frac;
   float frontier_band;
-  float blob_min_peak_mm, blob_rel_frac;
   int32_t use_negated_height;        /* calibration JSON use_negated_height_for_fit */
-  int32_t pad_;
+  double blob_min_peak_mm, blob_rel_frac;   /* shape_ftp.py:1215 (python floats: 0.1, 1/3) */
   VistafCurveModel height_model;     /* phase -> mm   (shape_ftp.py:672-705) */
   VistafCurveModel force_model;      /* cm^3 -> N     (force_sensor.py:149-167) */
   double grating_pitch_mm, depth_eps_mm;   /* force_sensor.py:32-33 */

@@ -60,6 +60,71 @@ class TempOutputs(C.Structure):
                                           "color_ok", "source", "records")]
 
 
+# ------------------------------------------------------------------ FTP shape + force path (include/vistaf.h)
+MODEL_TYPES = {"linear0": 0, "linear": 1, "poly2": 2, "sat_exp": 3, "growth": 4, "hinge_saturating": 5}
+MODEL_PARAM_NAMES = {"linear0": ("a",), "linear": ("a", "b"), "poly2": ("c2", "c1", "c0"), "sat_exp": ("a", "b"),
+                     "growth": ("a", "b"), "hinge_saturating": ("a", "b", "c")}
+
+
+class CurveModel(C.Structure):
+    _fields_ = [("type", C.c_int32), ("pad_", C.c_int32), ("p", C.c_double * 3)]
+
+
+def curve_model(best_model: dict) -> CurveModel:
+    """best_model = {"type": ..., "params": {...}} as stored in the calibration JSONs (shape_ftp.py:672, force_sensor.py:142)."""
+    t = best_model["type"]
+    if t not in MODEL_TYPES:
+        raise ValueError(f"Unknown model type in calibration: {t}")
+    m = CurveModel()
+    m.type = MODEL_TYPES[t]
+    for i, k in enumerate(MODEL_PARAM_NAMES[t]):
+        m.p[i] = float(best_model["params"][k])
+    return m
+
+
+class FtpParams(C.Structure):
+    _fields_ = [("crop_h", C.c_int32), ("crop_w", C.c_int32), ("cx", C.c_int32), ("cy", C.c_int32), ("r", C.c_int32),
+                ("roi_erode_px", C.c_int32), ("apod_taper", C.c_int32),
+                ("patch_half", C.c_int32), ("dc_exclusion", C.c_int32), ("n_peaks", C.c_int32), ("fft_pad", C.c_int32),
+                ("peak_max_dy_frac", C.c_float),
+                ("illum_sigma", C.c_float), ("pre_blur_sigma", C.c_float), ("quality_sigma", C.c_float),
+                ("smooth_sigma", C.c_float), ("unrel_sigma", C.c_float), ("amp_percentile", C.c_float),
+                ("close_kernel", C.c_int32), ("edge_margin", C.c_int32),
+                ("bad_int_pct", C.c_float), ("bad_grad_pct", C.c_float),
+                ("bad_dilate", C.c_int32), ("bad_inpaint_radius", C.c_int32),
+                ("core_pct", C.c_float), ("contact_pct", C.c_float),
+                ("dilate_kernel", C.c_int32), ("dilate_iters", C.c_int32),
+                ("min_contact_frac", C.c_float), ("max_contact_frac", C.c_float), ("frontier_band", C.c_float),
+                ("use_negated_height", C.c_int32),
+                ("blob_min_peak_mm", C.c_double), ("blob_rel_frac", C.c_double),
+                ("height_model", CurveModel), ("force_model", CurveModel),
+                ("grating_pitch_mm", C.c_double), ("depth_eps_mm", C.c_double)]
+
+
+class FtpRecord(C.Structure):
+    _fields_ = [("force_N", C.c_double), ("volume_cm3", C.c_double), ("contact_area_mm2", C.c_double),
+                ("max_depth_mm", C.c_double), ("mm_per_px", C.c_double), ("period_px", C.c_double),
+                ("amp_thr", C.c_float), ("contact_thr", C.c_float), ("bg_median", C.c_float), ("core_median", C.c_float),
+                ("reliable_px", C.c_int32), ("output_reliable_px", C.c_int32), ("contact_dilated_px", C.c_int32),
+                ("contact_kept_px", C.c_int32), ("bad_px", C.c_int32), ("residues", C.c_int32),
+                ("seed_x", C.c_int32), ("seed_y", C.c_int32), ("status", C.c_int32), ("pad_", C.c_int32)]
+
+
+_T = {C.c_double: np.float64, C.c_float: np.float32, C.c_int32: np.int32}
+FTP_RECORD_DTYPE = np.dtype([(n, _T[t]) for n, t in FtpRecord._fields_])
+assert FTP_RECORD_DTYPE.itemsize == C.sizeof(FtpRecord) == 104
+
+
+class FtpOutputs(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("height_mm", "reliable", "output_reliable", "contact_dilated",
+                                          "contact_kept", "records")]
+
+
+class FtpReferenceInfo(C.Structure):
+    _fields_ = [("peak_x", C.c_float), ("peak_y", C.c_float), ("fft_h", C.c_int32), ("fft_w", C.c_int32),
+                ("kx", C.c_float), ("ky", C.c_float), ("period_px", C.c_float), ("bad_px", C.c_int32)]
+
+
 _lib = None
 
 
@@ -81,6 +146,23 @@ def lib():
         L.vistaf_temp_roi_mask.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.vistaf_temp_workspace_plane.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.POINTER(C.c_size_t),
                                                   C.POINTER(C.c_size_t)]
+        L.vistaf_ftp_plan_create.argtypes = [C.POINTER(FtpParams), C.POINTER(C.c_void_p)]
+        L.vistaf_ftp_plan_destroy.argtypes = [C.c_void_p]
+        L.vistaf_ftp_workspace_bytes.restype = C.c_size_t
+        L.vistaf_ftp_workspace_bytes.argtypes = [C.c_void_p, C.c_int]
+        L.vistaf_crop_gray.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_void_p, C.c_void_p]
+        L.vistaf_ftp_set_reference.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                                               C.POINTER(FtpReferenceInfo), C.c_void_p]
+        L.vistaf_ftp_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(FtpOutputs), C.c_void_p, C.c_size_t,
+                                       C.c_void_p]
+        L.vistaf_ftp_masks.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.vistaf_ftp_workspace_plane.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.POINTER(C.c_size_t),
+                                                 C.POINTER(C.c_size_t)]
+        L.vistaf_depth_to_volume.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_double, C.c_double,
+                                             C.c_void_p, C.c_void_p]
+        L.vistaf_curve_predict.restype = C.c_double
+        L.vistaf_curve_predict.argtypes = [C.POINTER(CurveModel), C.c_double]
         _lib = L
     return _lib
 

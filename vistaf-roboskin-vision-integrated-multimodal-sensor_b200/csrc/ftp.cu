@@ -1,6 +1,19 @@
 // Fourier-Transform-Profilometry shape path + force model on sm_100a (Code/shape_ftp.py, Code/force_sensor.py).
 // Deformed frames are processed as a batch against one cached reference frame; every stage is a
 // kernel over the whole batch (grid.z / grid.y = frame).  Reference file:line cited per stage.
+//
+// Stage map (shape_ftp.py):
+//   A  demodulation :810-1040   Sobel + exact percentiles -> bad pixels -> Telea fill -> illumination
+//                               normalisation (sigma 45) -> pre-blur -> apodise -> median -> reflect pad ->
+//                               carrier patch of the 1374^2 spectrum (pruned DFT: 21 columns x 21 rows are
+//                               all the dense transform's consumer reads) -> windowed inverse -> fractional
+//                               ramp -> ratio with the cached reference field -> wrapped phase, amplitude
+//   B  reliable mask :739-776   quality blur -> p25 -> close -> largest 8-CC -> chamfer erosion
+//   C  unwrap :1043-1080        integer wrap-count field by weighted union-find (labels.cuh)
+//   D  detrend :1357-1420, :1716-1751   IRLS plane, two-pass IRLS quadric, contact / background split
+//   E  smoothing, sign :1755-1768
+//   F  frontier / assembly / phase->mm :1803-1851, :682-705
+//   G  blob filter :1215-1281, force reduction force_sensor.py:93-167
 #include "../../include/vistaf.h"
 #include "common.cuh"
 #include "fft.cuh"
@@ -8,54 +21,81 @@
 #include "select.cuh"
 #include "morph.cuh"
 #include "labels.cuh"
+#include "telea.cuh"
 #include <string.h>
 #include <new>
 #include <vector>
+#include <algorithm>
 
 int fft2d_dense(const void* in, float2* out, const Fft1D& pw, const Fft1D& ph, int h, int w, int batch, int sign,
                 bool real_in, cudaStream_t st);
 
-#define NPATCH 21                 // 2*PATCH_HALF_WIDTH_BINS + 1 (shape_ftp.py:25)
+namespace vftp {
+#define NPATCH_MAX 41             // 2*PATCH_HALF_WIDTH_BINS + 1 <= 41
 #define FNAN __int_as_float(0x7fc00000)
+#define IRLS_C 4.685f
 
 struct FtpScal {                  // per-frame scalars in the workspace
-  SelectState sel[2];
   double ne[28];                  // normal equations: 21 upper-triangular + 6 rhs + count
   float coef[6];
   float sigma, med;               // IRLS scale / location
-  float hi_thr, grad_thr, mu, amp_thr, contact_thr, bg_med, core_thr, core_med;
-  unsigned long long seed_key;    // (quality key << 32) | ~index
-  unsigned int n_rel, n_bg, n_contact, n_contact_d, n_outrel, n_bad, n_kept, residues, status;
-  int bg_is_rel, flip, few;
-  float gmax;                     // blob filter
-  double vol_sum; unsigned int vol_cnt; float vol_max;
+  int irls_n, irls_skip;
+  float hi_thr, grad_thr, mu, amp_thr, contact_thr, bg_med, core_thr, core_med, q2;
+  ull seed_key;                   // (quality key << 32) | ~index
+  ull best_cc;                    // (area << 32) | ~root
+  unsigned int n_rel, n_bg, n_contact, n_contact_d, n_bad, n_kept, residues, uf_bad, status;
+  int seed_root, seed_k;
+  int bg_is_rel, flip, detrend1;
+  unsigned int gmax_bits;         // blob filter: max depth (float bits, depth >= 0)
+  double vol_sum; unsigned int vol_cnt; unsigned int vol_max_bits;
   double pos_sum, neg_sum;
 };
 
-struct FtpWs {
-  size_t img, grad, bad, I, tmp, Iw, T, G, wrapped, amp, quality, mA, mB, reliable, lab, unw, krel, runs, nruns,
-      runoff, z0, z1, den, dist, contact, bg, scal, total;
+struct FtpWs {                    // byte offsets into the chunk workspace
+  size_t img, grad, bad0, bad, tmp, I, Iw, R, Pw, wrapped, qprod, quality, m1, m2, reliable, uf, area, unw,
+      contact, contact_d, hnum, hm, dist_in, dist_out, dtmp, snum, sm, peak, scal, sel, telea, total;
 };
 
+}  // namespace vftp
 struct VistafFtpPlan {
   VistafFtpParams P;
-  int h, w, N;                    // crop size, padded FFT size
+  int h, w, N, np;                // crop size, padded FFT size, patch size
   uint8_t *roi, *circ, *valid;    // device [h][w]
-  float* apo;                     // device [h][w]
+  float *apo, *den9;              // device [h][w]
   Fft1D fN;
   GaussKernel g_illum, g_pre, g_qual, g_smooth, g_unrel;
   MorphSE se_bad, se_close, se_dil, se_edge;
-  // reference-frame products (shape_ftp.py:1632-1639)
   bool have_ref;
-  float2* cref;                   // device [h][w]
+  float2* cref;                   // reference-frame field (shape_ftp.py:1632-1639), device [h][w]
   float* amp_ref;
   float peak_xf, peak_yf;
   int pxi, pyi;
   double kx, ky;
-  float2 *rampx, *rampy;          // fractional demodulation ramps, device [N]
-  float* hann;                    // device [NPATCH]
+  float2 *rampx, *rampy;          // fractional demodulation ramps over padded coordinates, device [N]
+  float* hann;                    // device [np]
+  int* kxs; int* kys;             // device [np]: unsigned frequency index of every patch column / row
   int roi_count;
+  int ref_bad;
 };
+
+namespace vftp {
+// ------------------------------------------------------------------ calibrated curves (shape_ftp.py:682-700, force_sensor.py:129-167)
+__host__ __device__ inline double curve_eval(const VistafCurveModel& m, double x) {
+  const double a = m.p[0], b = m.p[1], c = m.p[2];
+  switch (m.type) {
+    case VISTAF_MODEL_LINEAR0: return a * x;
+    case VISTAF_MODEL_LINEAR: return a * x + b;
+    case VISTAF_MODEL_POLY2: return a * x * x + b * x + c;
+    case VISTAF_MODEL_SAT_EXP: return a * (1.0 - exp(-b * fmax(x, 0.0)));
+    case VISTAF_MODEL_GROWTH: return a * (exp(b * fmax(x, 0.0)) - 1.0);
+    case VISTAF_MODEL_HINGE_SAT:
+      return a * ((1.0 - exp(-b * fmax(x - c, 0.0))) - (1.0 - exp(-b * fmax(0.0 - c, 0.0))));
+  }
+  return nan("");
+}
+}  // namespace vftp
+extern "C" double vistaf_curve_predict(const VistafCurveModel* model, double x) { return vftp::curve_eval(*model, x); }
+namespace vftp {
 
 // ------------------------------------------------------------------ F1: geometry (shape_ftp.py:383-403)
 __global__ void k_ftp_geometry(uint8_t* roi, uint8_t* circ, uint8_t* valid, float* apo, int h, int w, int cx, int cy,
@@ -87,12 +127,53 @@ __global__ void k_crop_gray(const uint8_t* __restrict__ frames, uint8_t* __restr
   gray[((size_t)b * h + y) * w + x] = (uint8_t)((9798 * p[2] + 19235 * p[1] + 3735 * p[0] + 16384) >> 15);
 }
 
+}  // namespace vftp
 extern "C" int vistaf_crop_gray(const uint8_t* frames, int batch, int H, int W, int x1, int y1, int h, int w,
                                 uint8_t* gray, void* stream) {
   if (x1 < 0 || y1 < 0 || x1 + w > W || y1 + h > H) return vistaf_set_err("crop outside frame", cudaErrorInvalidValue, __FILE__, __LINE__);
-  k_crop_gray<<<dim3(cdiv(w, 256), h, batch), 256, 0, (cudaStream_t)stream>>>(frames, gray, H, W, x1, y1, h, w);
+  vftp::k_crop_gray<<<dim3(cdiv(w, 256), h, batch), 256, 0, (cudaStream_t)stream>>>(frames, gray, H, W, x1, y1, h, w);
   CKL();
   return 0;
+}
+
+namespace vftp {
+// ------------------------------------------------------------------ generic small helpers
+__global__ void k_ftp_init(FtpScal* sc, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  FtpScal z;
+  memset(&z, 0, sizeof(z));
+  sc[i] = z;
+}
+
+struct PlaneLoad {
+  const float* p; long long plane; int w;
+  __device__ float operator()(int b, int y, int x) const { return p[(long long)b * plane + (long long)y * w + x]; }
+};
+struct PlaneStore {
+  float* p; long long plane; int w;
+  __device__ void operator()(int b, int y, int x, float v) { p[(long long)b * plane + (long long)y * w + x] = v; }
+  __device__ void finish(int) {}
+};
+
+enum { G_HI = 0, G_GRAD, G_MU, G_AMP, G_CONTACT, G_BGMED, G_CORETHR, G_COREMED, G_IRLS_MED, G_IRLS_MAD, G_CONTACT2 };
+__global__ void k_ftp_grab(FtpScal* sc, const SelectState* sel, int which) {   // copy a finished quantile into its slot
+  FtpScal& s = sc[blockIdx.x];
+  const float r = sel[blockIdx.x].result;
+  const unsigned int cnt = sel[blockIdx.x].count;
+  switch (which) {
+    case G_HI: s.hi_thr = cnt ? r : 255.0f; break;                           // shape_ftp.py:630
+    case G_GRAD: s.grad_thr = cnt ? r : 0.0f; break;                         // :640
+    case G_MU: s.mu = cnt ? r : 0.0f; break;                                 // :848 (fallback 0)
+    case G_AMP: s.amp_thr = r; break;
+    case G_CONTACT: s.contact_thr = (cnt && r == r) ? r : 0.0f; break;
+    case G_CONTACT2: if (s.q2 == s.q2 && cnt) s.contact_thr = r; break;
+    case G_BGMED: s.bg_med = (cnt && r == r) ? r : 0.0f; break;
+    case G_CORETHR: s.core_thr = r; break;
+    case G_COREMED: s.core_med = r; s.flip = (cnt > 0 && r > 0.f) ? 1 : 0; break;
+    case G_IRLS_MED: s.med = r; break;
+    case G_IRLS_MAD: s.sigma = __fmul_rn(1.4826f, __fadd_rn(r, 1e-6f)); break;
+  }
 }
 
 // ------------------------------------------------------------------ F2: bad pixels (shape_ftp.py:625-649)
@@ -118,7 +199,7 @@ struct MaskedVal {              // value stream: plane[b][i] where mask[i] (mask
   __device__ bool operator()(int b, long long i, float& v) const {
     if (!m[i]) return false;
     v = p[(long long)b * plane + i];
-    return v == v;
+    return fabsf(v) <= 3.4e38f;
   }
 };
 struct MaskedValB {             // per-frame mask
@@ -126,7 +207,7 @@ struct MaskedValB {             // per-frame mask
   __device__ bool operator()(int b, long long i, float& v) const {
     if (!m[(long long)b * plane + i]) return false;
     v = p[(long long)b * plane + i];
-    return v == v;
+    return fabsf(v) <= 3.4e38f;
   }
 };
 
@@ -138,20 +219,1155 @@ struct BadLoad {                // (img >= hi) | (grad >= gthr), within valid
     return img[(long long)b * plane + i] >= sc[b].hi_thr || grad[(long long)b * plane + i] >= sc[b].grad_thr;
   }
 };
-
-__global__ void k_ftp_grab_thr(FtpScal* sc, int which) {     // copy a finished quantile into its named slot
-  FtpScal& s = sc[blockIdx.x];
-  float r = s.sel[0].result;
-  switch (which) {
-    case 0: s.hi_thr = r; break;
-    case 1: s.grad_thr = r; break;
-    case 2: s.mu = r; break;
-    case 3: s.amp_thr = r; break;
-    case 4: s.contact_thr = r; break;
-    case 5: s.bg_med = r; break;
-    case 6: s.core_thr = r; break;
-    case 7: s.core_med = r; s.flip = (s.sel[0].count > 0 && r > 0.f) ? 1 : 0; break;
-    case 8: s.med = r; break;
-    case 9: s.sigma = 1.4826f * (r + 1e-6f); break;
+__global__ void k_ftp_badraw(BadLoad ld, uint8_t* __restrict__ dst, int h, int w) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+  if (x >= w) return;
+  dst[(size_t)b * h * w + (size_t)y * w + x] = (uint8_t)ld(b, y, x);
+}
+__global__ void k_ftp_count_mask(const uint8_t* __restrict__ m, FtpScal* sc, int npix, int which) {
+  const int b = blockIdx.y;
+  int c = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) c += m[(size_t)b * npix + i] != 0;
+  c = warp_sum(c);
+  if ((threadIdx.x & 31) == 0 && c) {
+    unsigned int* dst = which == 0 ? &sc[b].n_bad : which == 1 ? &sc[b].n_rel : which == 2 ? &sc[b].n_contact
+                      : which == 3 ? &sc[b].n_contact_d : &sc[b].n_kept;
+    atomicAdd(dst, (unsigned)c);
   }
+}
+struct TeleaMask {
+  const uint8_t* m; long long plane; int w;
+  __device__ bool operator()(int b, int y, int x) const { return m[(long long)b * plane + (long long)y * w + x] != 0; }
+};
+
+// ------------------------------------------------------------------ F4: normalisation (shape_ftp.py:831-848)
+struct IllumStoreF {            // I = img / (blur + 1e-6) - 1
+  const float* img; float* I; long long plane; int w;
+  __device__ void operator()(int b, int y, int x, float blur) {
+    long long i = (long long)b * plane + (long long)y * w + x;
+    I[i] = __fsub_rn(__fdiv_rn(img[i], __fadd_rn(blur, 1e-6f)), 1.0f);
+  }
+  __device__ void finish(int) {}
+};
+struct ApoStore {               // Iw = blur(I) * apodization
+  const float* apo; float* Iw; long long plane; int w;
+  __device__ void operator()(int b, int y, int x, float v) {
+    long long i = (long long)y * w + x;
+    Iw[(long long)b * plane + i] = __fmul_rn(v, apo[i]);
+  }
+  __device__ void finish(int) {}
+};
+
+// ------------------------------------------------------------------ F5-F7: carrier patch by pruned DFT
+// Row part: R[y][j] = sum_X Ip[y][X] e^{-2 pi i kx_j X / N} over the reflect-padded row (BORDER_REFLECT, :857)
+// of Iw - mu.  Padded rows are mirror images of inner rows, so only the h inner rows are transformed.
+__global__ void __launch_bounds__(256) k_ftp_rowdft(const float* __restrict__ Iw, const FtpScal* sc, float2* __restrict__ R,
+                                                     const float2* __restrict__ tw, const int* __restrict__ kxs, int h, int w,
+                                                     int N, int pad, int np) {
+  extern __shared__ float row[];                   // N floats
+  const int b = blockIdx.y, y = blockIdx.x;
+  const float mu = sc[b].mu;
+  const float* src = Iw + ((size_t)b * h + y) * w;
+  for (int X = threadIdx.x; X < N; X += blockDim.x) row[X] = __fsub_rn(src[reflect(X - pad, w)], mu);
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int j = wid; j < np; j += nw) {
+    const int k = kxs[j];
+    int idx = (int)(((long long)k * lane) % N);
+    const int step = (int)(((long long)k * 32) % N);
+    float ar = 0.f, ai = 0.f;
+    for (int X = lane; X < N; X += 32) {
+      const float2 t = __ldg(tw + idx);
+      const float v = row[X];
+      ar = fmaf(v, t.x, ar);
+      ai = fmaf(v, t.y, ai);
+      idx += step;
+      if (idx >= N) idx -= N;
+    }
+    ar = warp_sum(ar); ai = warp_sum(ai);
+    if (lane == 0) R[((size_t)b * h + y) * np + j] = make_float2(ar, ai);
+  }
+}
+// Column part + window: Pw[i][j] = hann[i] hann[j] sum_Y R[refl(Y - pad)][j] e^{-2 pi i ky_i Y / N}  (:929-947)
+__global__ void __launch_bounds__(256) k_ftp_coldft(const float2* __restrict__ R, float2* __restrict__ Pw,
+                                                     const float2* __restrict__ tw, const int* __restrict__ kys,
+                                                     const float* __restrict__ hann, int h, int N, int pad, int np) {
+  extern __shared__ float2 col[];                  // h entries
+  const int b = blockIdx.y, j = blockIdx.x;
+  for (int y = threadIdx.x; y < h; y += blockDim.x) col[y] = R[((size_t)b * h + y) * np + j];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int i = wid; i < np; i += nw) {
+    const int k = kys[i];
+    int idx = (int)(((long long)k * lane) % N);
+    const int step = (int)(((long long)k * 32) % N);
+    float2 acc = make_float2(0.f, 0.f);
+    for (int Y = lane; Y < N; Y += 32) {
+      const float2 t = __ldg(tw + idx);
+      const float2 v = col[reflect(Y - pad, h)];
+      acc.x = fmaf(v.x, t.x, fmaf(-v.y, t.y, acc.x));
+      acc.y = fmaf(v.x, t.y, fmaf(v.y, t.x, acc.y));
+      idx += step;
+      if (idx >= N) idx -= N;
+    }
+    acc.x = warp_sum(acc.x); acc.y = warp_sum(acc.y);
+    if (lane == 0) {
+      const float wgt = __fmul_rn(hann[i], hann[j]);
+      Pw[((size_t)b * np + i) * np + j] = make_float2(acc.x * wgt, acc.y * wgt);
+    }
+  }
+}
+// e^{+2 pi i f X / N} from the forward table
+__device__ __forceinline__ float2 tw_inv(const float2* __restrict__ tw, int f, int X, int N) {
+  const int af = f < 0 ? -f : f;
+  float2 t = __ldg(tw + (int)(((long long)af * X) % N));
+  if (f >= 0) t.y = -t.y;
+  return t;
+}
+// Inverse of the re-centred patch on the un-padded rows/columns, fractional ramp (:955-961), and either
+//   REF: store the reference field and its amplitude (:990-997), or
+//   DEF: ratio with the reference field -> wrapped phase (:1681-1689) and amp_ref * amp_def (:741).
+template <bool REF>
+__global__ void __launch_bounds__(256) k_ftp_field(const float2* __restrict__ Pw, const float2* __restrict__ tw,
+                                                    const float2* __restrict__ rampx, const float2* __restrict__ rampy,
+                                                    float2* __restrict__ cref, float* __restrict__ amp_ref,
+                                                    float* __restrict__ wrapped, float* __restrict__ qprod, int h, int w,
+                                                    int N, int pad, int np) {
+  __shared__ float2 Tj[NPATCH_MAX];
+  const int b = blockIdx.y, y = blockIdx.x, Y = y + pad, half = np / 2;
+  if (threadIdx.x < np) {
+    const int j = threadIdx.x;
+    float2 acc = make_float2(0.f, 0.f);
+    for (int i = 0; i < np; i++) {
+      const float2 p = Pw[((size_t)b * np + i) * np + j];
+      const float2 t = tw_inv(tw, i - half, Y, N);
+      acc.x = fmaf(p.x, t.x, fmaf(-p.y, t.y, acc.x));
+      acc.y = fmaf(p.x, t.y, fmaf(p.y, t.x, acc.y));
+    }
+    Tj[j] = acc;
+  }
+  __syncthreads();
+  const float inv = 1.0f / ((float)N * (float)N);
+  const float2 ry = rampy[Y];
+  for (int x = threadIdx.x; x < w; x += blockDim.x) {
+    const int X = x + pad;
+    float2 acc = make_float2(0.f, 0.f);
+    for (int j = 0; j < np; j++) {
+      const float2 p = Tj[j];
+      const float2 t = tw_inv(tw, j - half, X, N);
+      acc.x = fmaf(p.x, t.x, fmaf(-p.y, t.y, acc.x));
+      acc.y = fmaf(p.x, t.y, fmaf(p.y, t.x, acc.y));
+    }
+    float2 c = cmul(make_float2(acc.x * inv, acc.y * inv), cmul(rampx[X], ry));
+    const size_t i = (size_t)y * w + x;
+    const float amp = sqrtf(c.x * c.x + c.y * c.y);
+    if (REF) {
+      cref[i] = c;
+      amp_ref[i] = amp;
+    } else {
+      const float2 r = cmulc(c, cref[i]);
+      wrapped[(size_t)b * h * w + i] = atan2f(r.y, r.x);
+      qprod[(size_t)b * h * w + i] = __fmul_rn(amp_ref[i], amp);
+    }
+  }
+}
+// dense path input (reference frame): reflect-padded, median-removed plane (:857-862)
+__global__ void k_ftp_pad(const float* __restrict__ Iw, const FtpScal* sc, float* __restrict__ Ip, int h, int w, int N, int pad) {
+  int X = blockIdx.x * blockDim.x + threadIdx.x, Y = blockIdx.y;
+  if (X >= N) return;
+  Ip[(size_t)Y * N + X] = __fsub_rn(Iw[(size_t)reflect(Y - pad, h) * w + reflect(X - pad, w)], sc[0].mu);
+}
+
+// ------------------------------------------------------------------ F8: reliable mask (shape_ftp.py:739-776)
+struct RelRawLoad {             // roi & (q >= thr) & finite
+  const float* q; const uint8_t* roi; const FtpScal* sc; long long plane; int w;
+  __device__ int operator()(int b, int y, int x) const {
+    long long i = (long long)y * w + x;
+    if (!roi[i]) return 0;
+    const float v = q[(long long)b * plane + i];
+    return v >= sc[b].amp_thr && fabsf(v) <= 3.4e38f;
+  }
+};
+struct MaskFg {                 // union-find foreground from a 0/1 plane
+  const uint8_t* m; long long plane; int w;
+  __device__ bool operator()(int b, int y, int x) const { return m[(long long)b * plane + (long long)y * w + x] != 0; }
+};
+struct LargestLoad {            // (component == largest) & roi, read from the flattened union-find plane
+  const ull* uf; const uint8_t* roi; const FtpScal* sc; long long plane; int w;
+  __device__ int operator()(int b, int y, int x) const {
+    long long i = (long long)y * w + x;
+    const unsigned int root = uf_parent(uf[(long long)b * plane + i]);
+    if (root == UF_BG || !roi[i]) return 0;
+    const ull best = sc[b].best_cc;
+    return best != 0 && root == 0xffffffffu - (unsigned int)(best & 0xffffffffull);
+  }
+};
+__global__ void k_ftp_seed(const float* __restrict__ q, const uint8_t* __restrict__ rel, FtpScal* sc, int npix) {
+  const int b = blockIdx.y;
+  ull best = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x)
+    if (rel[(size_t)b * npix + i]) {
+      ull k = ((ull)f2key(q[(size_t)b * npix + i]) << 32) | (ull)(0xffffffffu - (unsigned int)i);
+      best = k > best ? k : best;
+    }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { ull t = __shfl_xor_sync(0xffffffffu, best, o); best = t > best ? t : best; }
+  if ((threadIdx.x & 31) == 0 && best) atomicMax(&sc[b].seed_key, best);
+}
+
+// ------------------------------------------------------------------ F10: unwrap (shape_ftp.py:1043-1080)
+// u[n] = u[p] + wrap(w[n] - w[p]): wrap adds -2 pi when the step exceeds pi, +2 pi below -pi, so the wrap
+// count obeys k[n] = k[p] + m(p, n).  A residue-free field makes k path independent.
+struct PhaseEdge {
+  const float* wr; long long plane;
+  __device__ int operator()(int b, int p, int n) const {
+    const float d = __fsub_rn(wr[(long long)b * plane + n], wr[(long long)b * plane + p]);
+    return d > 3.14159274f ? -1 : (d < -3.14159274f ? 1 : 0);
+  }
+};
+__global__ void k_ftp_residues(const float* __restrict__ wr, const uint8_t* __restrict__ rel, FtpScal* sc, int h, int w) {
+  const int b = blockIdx.z, y = blockIdx.y, x = blockIdx.x * blockDim.x + threadIdx.x;
+  int bad = 0;
+  if (x + 1 < w && y + 1 < h) {
+    const size_t o = (size_t)b * h * w;
+    const int p00 = y * w + x, p01 = p00 + 1, p10 = p00 + w, p11 = p10 + 1;
+    const bool m00 = rel[o + p00], m01 = rel[o + p01], m10 = rel[o + p10], m11 = rel[o + p11];
+    PhaseEdge e{wr, (long long)h * w};
+    if (m00 && m01 && m11) bad += (e(b, p00, p01) + e(b, p01, p11) + e(b, p11, p00)) != 0;
+    if (m00 && m10 && m11) bad += (e(b, p00, p10) + e(b, p10, p11) + e(b, p11, p00)) != 0;
+    if (m00 && m01 && m10) bad += (e(b, p00, p01) + e(b, p01, p10) + e(b, p10, p00)) != 0;
+    if (m01 && m10 && m11) bad += (e(b, p01, p11) + e(b, p11, p10) + e(b, p10, p01)) != 0;
+  }
+  bad = warp_sum(bad);
+  if ((threadIdx.x & 31) == 0 && bad) atomicAdd(&sc[b].residues, (unsigned)bad);
+}
+__global__ void k_ftp_seed_root(const ull* __restrict__ uf, FtpScal* sc, int npix) {
+  FtpScal& s = sc[blockIdx.x];
+  if (s.seed_key == 0) { s.seed_root = -1; s.seed_k = 0; return; }
+  const unsigned int idx = 0xffffffffu - (unsigned int)(s.seed_key & 0xffffffffull);
+  const ull v = uf[(size_t)blockIdx.x * npix + idx];
+  s.seed_root = (int)uf_parent(v);
+  s.seed_k = uf_delta(v);
+}
+__global__ void k_ftp_unwrap_apply(const ull* __restrict__ uf, const float* __restrict__ wr, const FtpScal* sc,
+                                   float* __restrict__ unw, int npix) {
+  const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npix) return;
+  const ull v = uf[(size_t)b * npix + i];
+  float u = FNAN;
+  if (uf_parent(v) != UF_BG && (int)uf_parent(v) == sc[b].seed_root) {
+    const int dk = uf_delta(v) - sc[b].seed_k;
+    u = __fadd_rn(wr[(size_t)b * npix + i], (float)(6.283185307179586 * (double)dk));
+  }
+  unw[(size_t)b * npix + i] = u;
+}
+
+// ------------------------------------------------------------------ F11/F12: IRLS polynomial surface (shape_ftp.py:1100-1136)
+__device__ __forceinline__ float poly_fit(const float* c, float xn, float yn, bool order2) {
+  float f = __fadd_rn(__fadd_rn(__fmul_rn(c[0], xn), __fmul_rn(c[1], yn)), c[2]);
+  if (order2)
+    f = __fadd_rn(f, __fadd_rn(__fadd_rn(__fmul_rn(__fmul_rn(c[3], xn), xn), __fmul_rn(__fmul_rn(c[4], xn), yn)),
+                               __fmul_rn(__fmul_rn(c[5], yn), yn)));
+  return f;
+}
+struct FitGeom {
+  int w; float cx, cy;           // (w-1)/2, (h-1)/2
+  __device__ void norm(int i, float& xn, float& yn) const {
+    const int y = i / w, x = i - y * w;
+    xn = __fdiv_rn(__fsub_rn((float)x, cx), cx);
+    yn = __fdiv_rn(__fsub_rn((float)y, cy), cy);
+  }
+};
+// mask selector for the three fits: 0 = reliable, 1 = background (reliable & ~contact_dilated, or reliable)
+struct FitMask {
+  const uint8_t* rel; const uint8_t* contact_d; const FtpScal* sc; long long plane; int use_bg;
+  __device__ bool operator()(int b, long long i) const {
+    if (!rel[(long long)b * plane + i]) return false;
+    if (use_bg && !sc[b].bg_is_rel && contact_d[(long long)b * plane + i]) return false;
+    return true;
+  }
+};
+
+template <bool ORDER2>
+__global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ z, FitMask fm, FtpScal* sc, FitGeom g,
+                                                     int npix, int iter) {
+  constexpr int NC = ORDER2 ? 6 : 3, NV = NC * (NC + 1) / 2 + NC + 1;
+  __shared__ double sh[NV * 32];
+  const int b = blockIdx.y;
+  if (sc[b].irls_skip) return;
+  float coef[6];
+#pragma unroll
+  for (int i = 0; i < 6; i++) coef[i] = sc[b].coef[i];
+  const float med = sc[b].med;
+  const float cs = __fmul_rn(IRLS_C, sc[b].sigma);
+  (void)med;
+  double acc[NV];
+#pragma unroll
+  for (int i = 0; i < NV; i++) acc[i] = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+    if (!fm(b, i)) continue;
+    const float zz = z[(size_t)b * npix + i];
+    if (!(fabsf(zz) <= 3.4e38f)) continue;
+    float xn, yn;
+    g.norm(i, xn, yn);
+    float wt = 1.0f;
+    if (iter > 0) {
+      const float r = __fsub_rn(zz, poly_fit(coef, xn, yn, ORDER2));
+      const float u = __fdiv_rn(r, cs);
+      wt = __fdiv_rn(1.0f, __fadd_rn(1.0f, __fmul_rn(u, u)));
+    }
+    const double w2 = (double)wt * (double)wt;
+    double a[NC];
+    a[0] = xn; a[1] = yn; a[2] = 1.0;
+    if (ORDER2) { a[3] = (double)__fmul_rn(xn, xn); a[4] = (double)__fmul_rn(xn, yn); a[5] = (double)__fmul_rn(yn, yn); }
+    int k = 0;
+#pragma unroll
+    for (int p = 0; p < NC; p++) {
+      const double wa = w2 * a[p];
+#pragma unroll
+      for (int q = p; q < NC; q++) acc[k++] += wa * a[q];
+    }
+#pragma unroll
+    for (int p = 0; p < NC; p++) acc[k++] += w2 * a[p] * (double)zz;
+    acc[k] += 1.0;
+  }
+  block_sum<NV>(acc, sh);
+  if (threadIdx.x == 0)
+    for (int i = 0; i < NV; i++)
+      if (acc[i] != 0.0) atomicAdd(&sc[b].ne[i], acc[i]);
+}
+
+// Solve the normal equations (Gaussian elimination with partial pivoting, float64), store float32 coefficients.
+template <bool ORDER2>
+__global__ void k_irls_solve(FtpScal* sc, int iter) {
+  constexpr int NC = ORDER2 ? 6 : 3, NT = NC * (NC + 1) / 2;
+  FtpScal& s = sc[blockIdx.x];
+  if (s.irls_skip) return;
+  double A[NC][NC + 1];
+  int k = 0;
+  for (int p = 0; p < NC; p++)
+    for (int q = p; q < NC; q++) { A[p][q] = s.ne[k]; A[q][p] = s.ne[k]; k++; }
+  for (int p = 0; p < NC; p++) A[p][NC] = s.ne[NT + p];
+  const int n = (int)(s.ne[NT + NC] + 0.5);
+  for (int i = 0; i < 28; i++) s.ne[i] = 0.0;
+  if (iter == 0) {
+    s.irls_n = n;
+    if (n < 200) {                                   // shape_ftp.py:1103: zero surface
+      for (int i = 0; i < 6; i++) s.coef[i] = 0.f;
+      s.irls_skip = 1;
+      s.status |= VISTAF_ST_FEW_RELIABLE;
+      return;
+    }
+  }
+  for (int c = 0; c < NC; c++) {
+    int piv = c;
+    for (int r = c + 1; r < NC; r++) if (fabs(A[r][c]) > fabs(A[piv][c])) piv = r;
+    if (piv != c) for (int q = 0; q <= NC; q++) { double t = A[c][q]; A[c][q] = A[piv][q]; A[piv][q] = t; }
+    const double d = A[c][c];
+    if (fabs(d) < 1e-300) continue;
+    for (int r = c + 1; r < NC; r++) {
+      const double f = A[r][c] / d;
+      for (int q = c; q <= NC; q++) A[r][q] -= f * A[c][q];
+    }
+  }
+  double x[NC];
+  for (int c = NC - 1; c >= 0; c--) {
+    double v = A[c][NC];
+    for (int q = c + 1; q < NC; q++) v -= A[c][q] * x[q];
+    x[c] = fabs(A[c][c]) < 1e-300 ? 0.0 : v / A[c][c];
+  }
+  for (int i = 0; i < 6; i++) s.coef[i] = i < NC ? (float)x[i] : 0.f;
+}
+__global__ void k_irls_begin(FtpScal* sc, int mode) {    // mode 0: plane on reliable, 1: quadric on reliable, 2: quadric on background
+  FtpScal& s = sc[blockIdx.x];
+  for (int i = 0; i < 28; i++) s.ne[i] = 0.0;
+  for (int i = 0; i < 6; i++) s.coef[i] = 0.f;
+  s.sigma = 1.f; s.med = 0.f;
+  s.irls_skip = 0;
+  if (mode == 0) {
+    s.detrend1 = s.n_rel >= 500 ? 1 : 0;                 // shape_ftp.py:1379
+    if (!s.detrend1) s.irls_skip = 1;
+  }
+}
+// residual stream of the current fit: r (mode 0) or |r - med| (mode 1)
+template <bool ORDER2>
+struct ResidVal {
+  const float* z; FitMask fm; const FtpScal* sc; FitGeom g; long long plane; int mode;
+  __device__ bool operator()(int b, long long i, float& v) const {
+    if (sc[b].irls_skip || !fm(b, i)) return false;
+    const float zz = z[(long long)b * plane + i];
+    if (!(fabsf(zz) <= 3.4e38f)) return false;
+    float xn, yn;
+    g.norm((int)i, xn, yn);
+    const float r = __fsub_rn(zz, poly_fit(sc[b].coef, xn, yn, ORDER2));
+    v = mode ? fabsf(__fsub_rn(r, sc[b].med)) : r;
+    return true;
+  }
+};
+__global__ void k_ftp_sub_fit1(float* __restrict__ unw, const FtpScal* sc, FitGeom g, int npix) {
+  const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npix || !sc[b].detrend1) return;
+  float xn, yn;
+  g.norm(i, xn, yn);
+  const size_t o = (size_t)b * npix + i;
+  unw[o] = __fsub_rn(unw[o], poly_fit(sc[b].coef, xn, yn, false));
+}
+
+// ------------------------------------------------------------------ F12: contact / background (shape_ftp.py:1716-1751)
+struct AbsResVal {              // |unw - fit0| over reliable & finite
+  const float* z; const uint8_t* rel; const FtpScal* sc; FitGeom g; long long plane; int need_q2;
+  __device__ bool operator()(int b, long long i, float& v) const {
+    if (need_q2 && !(sc[b].q2 == sc[b].q2)) return false;
+    if (!rel[(long long)b * plane + i]) return false;
+    const float zz = z[(long long)b * plane + i];
+    float xn, yn;
+    g.norm((int)i, xn, yn);
+    v = fabsf(__fsub_rn(zz, poly_fit(sc[b].coef, xn, yn, true)));
+    return fabsf(v) <= 3.4e38f;
+  }
+};
+__global__ void k_ftp_contact(const float* __restrict__ z, const uint8_t* __restrict__ rel, FtpScal* sc, FitGeom g,
+                              uint8_t* __restrict__ contact, int npix, int count) {
+  const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  int c = 0;
+  if (i < npix) {
+    const size_t o = (size_t)b * npix + i;
+    if (rel[o]) {
+      float xn, yn;
+      g.norm(i, xn, yn);
+      const float v = fabsf(__fsub_rn(z[o], poly_fit(sc[b].coef, xn, yn, true)));
+      c = (v >= sc[b].contact_thr && fabsf(v) <= 3.4e38f) ? 1 : 0;
+    }
+    contact[o] = (uint8_t)c;
+  }
+  if (count) {
+    c = warp_sum(c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&sc[b].n_contact, (unsigned)c);
+  }
+}
+__global__ void k_ftp_contact_frac(FtpScal* sc, float min_frac, float max_frac) {
+  FtpScal& s = sc[blockIdx.x];
+  const double frac = (double)s.n_contact / (double)(s.n_rel > 1u ? s.n_rel : 1u);
+  s.q2 = FNAN;
+  if (frac < (double)min_frac) { s.q2 = 95.f; s.status |= VISTAF_ST_CONTACT_P95; }
+  else if (frac > (double)max_frac) { s.q2 = 98.f; s.status |= VISTAF_ST_CONTACT_P95; }
+}
+__global__ void k_ftp_bg_decide(FtpScal* sc) {
+  FtpScal& s = sc[blockIdx.x];
+  const unsigned int nbg = s.n_rel - s.n_contact_d;
+  s.n_bg = nbg;
+  s.bg_is_rel = nbg < (unsigned int)(int)(0.15 * (double)s.n_rel) ? 1 : 0;     // shape_ftp.py:1744
+  if (s.bg_is_rel) s.status |= VISTAF_ST_BG_FALLBACK;
+}
+struct DetVal {                 // det = unw - fit over background (median, :1749)
+  const float* z; FitMask fm; const FtpScal* sc; FitGeom g; long long plane;
+  __device__ bool operator()(int b, long long i, float& v) const {
+    if (!fm(b, i)) return false;
+    float xn, yn;
+    g.norm((int)i, xn, yn);
+    v = __fsub_rn(z[(long long)b * plane + i], poly_fit(sc[b].coef, xn, yn, true));
+    return fabsf(v) <= 3.4e38f;
+  }
+};
+
+// ------------------------------------------------------------------ F13: smoothing, sign (shape_ftp.py:1139-1147, 1755-1768)
+__device__ __forceinline__ float hm_at(const float* z, const FtpScal& s, const FitGeom& g, long long o, int i) {
+  float xn, yn;
+  g.norm(i, xn, yn);
+  return __fsub_rn(__fsub_rn(z[o], poly_fit(s.coef, xn, yn, true)), s.bg_med);
+}
+struct HmNumLoad {              // z0 = hm where reliable & finite, else 0
+  const float* z; const uint8_t* rel; const FtpScal* sc; FitGeom g; long long plane; int w;
+  __device__ float operator()(int b, int y, int x) const {
+    const int i = y * w + x;
+    const long long o = (long long)b * plane + i;
+    if (!rel[o]) return 0.f;
+    const float v = hm_at(z, sc[b], g, o, i);
+    return fabsf(v) <= 3.4e38f ? v : 0.f;
+  }
+};
+struct HmDenLoad {
+  const float* z; const uint8_t* rel; long long plane; int w;
+  __device__ float operator()(int b, int y, int x) const {
+    const long long o = (long long)b * plane + (long long)y * w + x;
+    return (rel[o] && fabsf(z[o]) <= 3.4e38f) ? 1.f : 0.f;
+  }
+};
+struct RatioStore {             // out = num / (den + 1e-6)
+  const float* num; float* out; long long plane; int w;
+  __device__ void operator()(int b, int y, int x, float den) {
+    const long long o = (long long)b * plane + (long long)y * w + x;
+    out[o] = __fdiv_rn(num[o], __fadd_rn(den, 1e-6f));
+  }
+  __device__ void finish(int) {}
+};
+struct CoreVal {                // hm over reliable & hm <= core_thr
+  const float* hm; const uint8_t* rel; const FtpScal* sc; long long plane;
+  __device__ bool operator()(int b, long long i, float& v) const {
+    if (!rel[(long long)b * plane + i]) return false;
+    if (!(sc[b].core_thr == sc[b].core_thr)) return false;
+    v = hm[(long long)b * plane + i];
+    return v <= sc[b].core_thr;
+  }
+};
+
+// ------------------------------------------------------------------ F15: frontier, assembly (shape_ftp.py:1287-1330, 1803-1841)
+struct NotMaskZero {            // chamfer zero set = pixels outside the mask
+  const uint8_t* m; long long plane; int w;
+  __device__ bool operator()(int b, int y, int x) const { return m[(long long)b * plane + (long long)y * w + x] == 0; }
+};
+struct MaskZero {               // chamfer zero set = the mask
+  const uint8_t* m; long long plane; int w;
+  __device__ bool operator()(int b, int y, int x) const { return m[(long long)b * plane + (long long)y * w + x] != 0; }
+};
+__device__ __forceinline__ float filled_at(const float* hm, const float* dist_in, const FtpScal& s, long long o, float band) {
+  float v = hm[o];
+  if (s.flip) v = __fmul_rn(v, -1.0f);
+  const float d = dist_in[o];
+  float t = __fdiv_rn(fmaxf(__fsub_rn(d, 1.0f), 0.f), fmaxf(1e-6f, band));
+  t = fminf(fmaxf(t, 0.f), 1.f);
+  const float wgt = __fmul_rn(__fmul_rn(t, t), __fsub_rn(3.0f, __fmul_rn(2.0f, t)));
+  return __fmul_rn(v, wgt);
+}
+struct AsmLoad {                // hf_ on the ROI before the sigma-9 smoothing: reliable -> filled, else 0
+  const float* hm; const float* dist_in; const uint8_t* rel; const uint8_t* roi; const FtpScal* sc; long long plane; int w;
+  float band;
+  __device__ float operator()(int b, int y, int x) const {
+    const long long i = (long long)y * w + x, o = (long long)b * plane + i;
+    if (!roi[i] || !rel[o]) return 0.f;
+    return filled_at(hm, dist_in, sc[b], o, band);
+  }
+};
+struct Den9Store {              // sm = num / den9 (den9 = blur(roi) + 1e-6, frame independent)
+  const float* den9; float* out; long long plane; int w;
+  __device__ void operator()(int b, int y, int x, float num) {
+    const long long i = (long long)y * w + x;
+    out[(long long)b * plane + i] = __fdiv_rn(num, den9[i]);
+  }
+  __device__ void finish(int) {}
+};
+struct RoiLoad {
+  const uint8_t* roi; int w;
+  __device__ float operator()(int, int y, int x) const { return roi[(long long)y * w + x] ? 1.f : 0.f; }
+};
+struct AddEpsStore {
+  float* out; int w;
+  __device__ void operator()(int, int y, int x, float v) { out[(long long)y * w + x] = __fadd_rn(v, 1e-6f); }
+  __device__ void finish(int) {}
+};
+
+// final per-pixel assembly + phase -> mm (shape_ftp.py:1816-1851) + candidate statistics for the blob filter
+__global__ void k_ftp_assemble(const float* __restrict__ hm, const float* __restrict__ dist_in,
+                               const float* __restrict__ dist_out, const float* __restrict__ sm,
+                               const uint8_t* __restrict__ rel, const uint8_t* __restrict__ roi, FtpScal* sc,
+                               float* __restrict__ out, int npix, float band, VistafCurveModel model, int use_neg) {
+  const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  float mm = FNAN;
+  if (i < npix) {
+    const size_t o = (size_t)b * npix + i;
+    if (roi[i] && !(sc[b].status & VISTAF_ST_EMPTY_ROI)) {
+      float v;
+      if (rel[o]) v = filled_at(hm, dist_in, sc[b], o, band);
+      else {
+        v = sm[o];
+        if (fmaxf(__fsub_rn(dist_out[o], 1.0f), 0.f) <= band) v = 0.f;
+      }
+      if (fabsf(v) <= 3.4e38f) v = fminf(v, 0.f);
+      const double x = fmax((double)(use_neg ? -v : v), 0.0);
+      mm = (float)curve_eval(model, x);
+    }
+    out[o] = mm;
+  }
+  float cand = (mm > 0.f) ? mm : 0.f;
+  cand = warp_max(cand);
+  if ((threadIdx.x & 31) == 0 && cand > 0.f) atomicMax(&sc[b].gmax_bits, __float_as_uint(cand));
+}
+
+// ------------------------------------------------------------------ F17: blob filter (shape_ftp.py:1215-1281)
+struct CandFg {
+  const float* mm; long long plane; int w;
+  __device__ bool operator()(int b, int y, int x) const { return mm[(long long)b * plane + (long long)y * w + x] > 0.f; }
+};
+__global__ void k_ftp_blob_peak(const ull* __restrict__ uf, const float* __restrict__ mm, unsigned int* __restrict__ peak,
+                                int npix) {
+  const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npix) return;
+  const unsigned int root = uf_parent(uf[(size_t)b * npix + i]);
+  if (root == UF_BG) return;
+  atomicMax(peak + (size_t)b * npix + root, __float_as_uint(mm[(size_t)b * npix + i]));
+}
+__global__ void k_ftp_blob_apply(const ull* __restrict__ uf, const unsigned int* __restrict__ peak, FtpScal* sc,
+                                 float* __restrict__ mm, uint8_t* __restrict__ kept, int npix, double min_peak, double rel_frac) {
+  const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  int k = 0;
+  if (i < npix) {
+    const unsigned int root = uf_parent(uf[(size_t)b * npix + i]);
+    if (root != UF_BG) {
+      const double gmax = (double)__uint_as_float(sc[b].gmax_bits);
+      const double thr = fmax(min_peak, rel_frac * gmax);
+      k = (double)__uint_as_float(peak[(size_t)b * npix + root]) >= thr;
+      if (!k) mm[(size_t)b * npix + i] = 0.f;
+    }
+    if (kept) kept[(size_t)b * npix + i] = (uint8_t)k;
+  }
+  k = warp_sum(k);
+  if ((threadIdx.x & 31) == 0 && k) atomicAdd(&sc[b].n_kept, (unsigned)k);
+}
+
+// ------------------------------------------------------------------ P1: force reduction (force_sensor.py:93-123)
+__global__ void __launch_bounds__(256) k_depth_sign(const float* __restrict__ z, const uint8_t* roi, double* pos, double* neg,
+                                                     size_t stride, long long npix) {
+  __shared__ double sh[64];
+  const int b = blockIdx.y;
+  double v[2] = {0.0, 0.0};
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (long long)gridDim.x * blockDim.x) {
+    const float x = z[(size_t)b * npix + i];
+    if (x == x) { if (x > 0.f) v[0] += (double)x; else v[1] += (double)(-x); }   // nansum over the whole map
+  }
+  (void)roi;
+  block_sum<2>(v, sh);
+  if (threadIdx.x == 0) {
+    if (v[0] != 0.0) atomicAdd((double*)((char*)pos + (size_t)b * stride), v[0]);
+    if (v[1] != 0.0) atomicAdd((double*)((char*)neg + (size_t)b * stride), v[1]);
+  }
+}
+__global__ void __launch_bounds__(256) k_depth_reduce(const float* __restrict__ z, const uint8_t* roi, const double* pos,
+                                                       const double* neg, size_t stride, double* vsum, unsigned int* vcnt,
+                                                       unsigned int* vmax, long long npix, float eps) {
+  __shared__ double sh[32];
+  __shared__ int shc[32];
+  __shared__ float shm[32];
+  const int b = blockIdx.y;
+  const bool use_neg = *(const double*)((const char*)neg + (size_t)b * stride) > *(const double*)((const char*)pos + (size_t)b * stride);
+  double v[1] = {0.0};
+  int c = 0;
+  float mx = 0.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (long long)gridDim.x * blockDim.x) {
+    float x = z[(size_t)b * npix + i];
+    if (roi && !roi[i]) continue;
+    x = use_neg ? -x : x;
+    if (!(x > 0.f) || !(fabsf(x) <= 3.4e38f)) continue;      // clip at 0, non-finite -> 0
+    if (x > eps) { v[0] += (double)x; c++; mx = fmaxf(mx, x); }
+  }
+  block_sum<1>(v, sh);
+  c = warp_sum(c); mx = warp_max(mx);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) { shc[threadIdx.x >> 5] = c; shm[threadIdx.x >> 5] = mx; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int ct = 0; float m = 0.f;
+    for (int i = 0; i < (int)(blockDim.x >> 5); i++) { ct += shc[i]; m = fmaxf(m, shm[i]); }
+    if (v[0] != 0.0) atomicAdd((double*)((char*)vsum + (size_t)b * stride), v[0]);
+    if (ct) atomicAdd((unsigned int*)((char*)vcnt + (size_t)b * stride), (unsigned)ct);
+    if (m > 0.f) atomicMax((unsigned int*)((char*)vmax + (size_t)b * stride), __float_as_uint(m));
+  }
+}
+
+__global__ void k_ftp_records(const FtpScal* sc, VistafFtpRecord* rec, int n, int w, double period_px, double pitch_mm,
+                              VistafCurveModel force_model) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const FtpScal& s = sc[i];
+  VistafFtpRecord r;
+  memset(&r, 0, sizeof(r));
+  const double mm_per_px = pitch_mm / period_px;
+  const double a = mm_per_px * mm_per_px;
+  r.mm_per_px = mm_per_px; r.period_px = period_px;
+  if (s.vol_cnt) {
+    const float v32 = __fmul_rn((float)s.vol_sum, (float)a);        // np.sum(float32) * float -> float32 (force_sensor.py:120)
+    r.volume_cm3 = (double)v32 / 1000.0;
+    r.contact_area_mm2 = (double)s.vol_cnt * a;
+    r.max_depth_mm = (double)__uint_as_float(s.vol_max_bits);
+  }
+  r.force_N = curve_eval(force_model, r.volume_cm3);
+  r.amp_thr = s.amp_thr; r.contact_thr = s.contact_thr; r.bg_median = s.bg_med; r.core_median = s.core_med;
+  r.reliable_px = (int)s.n_rel; r.output_reliable_px = (int)s.n_rel; r.contact_dilated_px = (int)s.n_contact_d;
+  r.contact_kept_px = (int)s.n_kept; r.bad_px = (int)s.n_bad; r.residues = (int)s.residues;
+  if (s.seed_key) {
+    const unsigned int idx = 0xffffffffu - (unsigned int)(s.seed_key & 0xffffffffull);
+    r.seed_x = (int)(idx % (unsigned)w); r.seed_y = (int)(idx / (unsigned)w);
+  } else { r.seed_x = r.seed_y = -1; }
+  unsigned int st = s.status;
+  if (s.n_rel == 0) st |= VISTAF_ST_EMPTY_ROI;
+  if (s.residues || s.uf_bad) st |= VISTAF_ST_RESIDUES;
+  if (s.flip) st |= VISTAF_ST_SIGN_FLIPPED;
+  r.status = (int)st;
+  rec[i] = r;
+}
+__global__ void k_ftp_mark_empty(FtpScal* sc) {
+  FtpScal& s = sc[blockIdx.x];
+  if (s.n_rel == 0) s.status |= VISTAF_ST_EMPTY_ROI;
+}
+
+}  // namespace vftp
+using namespace vftp;
+
+// ================================================================== host side
+static void ftp_layout(const VistafFtpPlan* p, int chunk, FtpWs& L) {
+  const size_t S = (size_t)p->h * p->w, c = (size_t)chunk;
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t r = o; o += align256(bytes); return r; };
+  L.img = take(c * S * 4); L.grad = take(c * S * 4); L.bad0 = take(c * S); L.bad = take(c * S);
+  L.tmp = take(c * S * 4); L.I = take(c * S * 4); L.Iw = take(c * S * 4);
+  L.R = take(c * (size_t)p->h * p->np * 8); L.Pw = take(c * (size_t)p->np * p->np * 8);
+  L.wrapped = take(c * S * 4); L.qprod = take(c * S * 4); L.quality = take(c * S * 4);
+  L.m1 = take(c * S); L.m2 = take(c * S); L.reliable = take(c * S);
+  L.uf = take(c * S * 8); L.area = take(c * S * 4); L.unw = take(c * S * 4);
+  L.contact = take(c * S); L.contact_d = take(c * S);
+  L.hnum = take(c * S * 4); L.hm = take(c * S * 4); L.dist_in = take(c * S * 4); L.dist_out = take(c * S * 4);
+  L.dtmp = take(c * S * 4); L.snum = take(c * S * 4); L.sm = take(c * S * 4); L.peak = take(c * S * 4);
+  L.scal = take(c * sizeof(FtpScal)); L.sel = take(c * sizeof(SelectState));
+  L.telea = take(telea_ws_bytes(p->h, p->w, chunk));
+  L.total = o;
+}
+
+static MorphSE se_chamfer_ball(float margin) {       // {(dx,dy): chamfer distance <= margin} as per-row half widths
+  MorphSE s;
+  int R = (int)floorf(margin / 0.955f) + 1;
+  if (R > MORPH_MAXROWS / 2) R = MORPH_MAXROWS / 2;
+  s.rows = 2 * R + 1;
+  for (int i = 0; i < MORPH_MAXROWS; i++) s.half[i] = -1;
+  for (int i = 0; i < s.rows; i++) {
+    const int dy = abs(i - R);
+    int best = -1;
+    for (int dx = 0; dx <= R + 1; dx++) {
+      const unsigned mn = dx < dy ? dx : dy, mx = dx < dy ? dy : dx;
+      const float d = (float)(CH_HV * (mx - mn) + CH_DG * mn) * (1.0f / 65536.0f);
+      if (d <= margin) best = dx;
+    }
+    s.half[i] = best;
+  }
+  return s;
+}
+
+extern "C" int vistaf_ftp_plan_create(const VistafFtpParams* P, VistafFtpPlan** out) {
+  if (!P || !out) return vistaf_set_err("null argument", cudaErrorInvalidValue, __FILE__, __LINE__);
+  const int np = 2 * (P->patch_half < 3 ? 3 : P->patch_half) + 1;
+  if (np > NPATCH_MAX || P->crop_w > CH_THREADS * CH_MAXPT || (P->dilate_kernel | 1) > MORPH_MAXROWS ||
+      (P->close_kernel | 1) > MORPH_MAXROWS || P->edge_margin > 15 || P->bad_inpaint_radius < 1 || P->bad_inpaint_radius > 8)
+    return vistaf_set_err("unsupported FTP parameters", cudaErrorInvalidValue, __FILE__, __LINE__);
+  VistafFtpPlan* p = new (std::nothrow) VistafFtpPlan();
+  if (!p) return vistaf_set_err("out of host memory", cudaErrorMemoryAllocation, __FILE__, __LINE__);
+  memset(p, 0, sizeof(*p));
+  p->P = *P;
+  p->h = P->crop_h; p->w = P->crop_w; p->np = np;
+  p->N = P->crop_w + 2 * P->fft_pad;
+  if (P->crop_h != P->crop_w) return vistaf_set_err("FTP crop must be square", cudaErrorInvalidValue, __FILE__, __LINE__);
+  if (fft1d_create(&p->fN, p->N)) return 1;
+  p->g_illum = make_gauss(P->illum_sigma);
+  p->g_pre = make_gauss(P->pre_blur_sigma);
+  p->g_qual = make_gauss(P->quality_sigma);
+  p->g_smooth = make_gauss(P->smooth_sigma);
+  p->g_unrel = make_gauss(P->unrel_sigma);
+  p->se_bad = se_ellipse(P->bad_dilate < 3 ? 3 : (P->bad_dilate | 1));
+  p->se_close = se_ellipse(P->close_kernel < 3 ? 3 : (P->close_kernel | 1));
+  p->se_dil = se_ellipse(P->dilate_kernel);
+  p->se_edge = se_chamfer_ball((float)P->edge_margin);
+  const size_t S = (size_t)p->h * p->w;
+  CK(cudaMalloc(&p->roi, S)); CK(cudaMalloc(&p->circ, S)); CK(cudaMalloc(&p->valid, S));
+  CK(cudaMalloc(&p->apo, S * 4)); CK(cudaMalloc(&p->den9, S * 4));
+  CK(cudaMalloc(&p->cref, S * 8)); CK(cudaMalloc(&p->amp_ref, S * 4));
+  CK(cudaMalloc(&p->rampx, sizeof(float2) * p->N)); CK(cudaMalloc(&p->rampy, sizeof(float2) * p->N));
+  CK(cudaMalloc(&p->hann, sizeof(float) * np)); CK(cudaMalloc(&p->kxs, sizeof(int) * np)); CK(cudaMalloc(&p->kys, sizeof(int) * np));
+  int r_valid = P->r - P->roi_erode_px;
+  if (r_valid < 0) r_valid = 0;
+  k_ftp_geometry<<<dim3(cdiv(p->w, 256), p->h), 256>>>(p->roi, p->circ, p->valid, p->apo, p->h, p->w, P->cx, P->cy, P->r,
+                                                       r_valid, P->apod_taper);
+  CKL();
+  // den9 = GaussianBlur(roi, sigma 9) + 1e-6 (shape_ftp.py:1146 with mask = roi_eroded, :1820)
+  float* tmp = nullptr;
+  CK(cudaMalloc(&tmp, S * 4));
+  if (gauss_blur(RoiLoad{p->roi, p->w}, AddEpsStore{p->den9, p->w}, tmp, p->h, p->w, 1, p->g_unrel, p->g_unrel, 0)) return 1;
+  CK(cudaDeviceSynchronize());
+  cudaFree(tmp);
+  std::vector<float> hn(np);
+  for (int i = 0; i < np; i++) hn[i] = (float)(0.5 - 0.5 * cos(2.0 * VISTAF_PI * i / (double)(np - 1)));   // np.hanning
+  CK(cudaMemcpy(p->hann, hn.data(), sizeof(float) * np, cudaMemcpyHostToDevice));
+  CK(cudaFuncSetAttribute((const void*)k_ftp_coldft, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(p->h * 8)));
+  *out = p;
+  return 0;
+}
+
+extern "C" void vistaf_ftp_plan_destroy(VistafFtpPlan* p) {
+  if (!p) return;
+  fft1d_destroy(&p->fN);
+  cudaFree(p->roi); cudaFree(p->circ); cudaFree(p->valid); cudaFree(p->apo); cudaFree(p->den9);
+  cudaFree(p->cref); cudaFree(p->amp_ref); cudaFree(p->rampx); cudaFree(p->rampy); cudaFree(p->hann);
+  cudaFree(p->kxs); cudaFree(p->kys);
+  delete p;
+}
+
+extern "C" size_t vistaf_ftp_workspace_bytes(const VistafFtpPlan* p, int chunk) {
+  FtpWs L;
+  ftp_layout(p, chunk < 1 ? 1 : chunk, L);
+  // the reference pass additionally needs the dense padded plane + spectrum
+  size_t dense = align256((size_t)p->N * p->N * 4) + align256((size_t)p->N * p->N * 8);
+  return L.total + dense;
+}
+
+extern "C" int vistaf_ftp_masks(const VistafFtpPlan* p, uint8_t* roi, uint8_t* circ, float* apo, void* stream) {
+  const size_t S = (size_t)p->h * p->w;
+  if (roi) CK(cudaMemcpyAsync(roi, p->roi, S, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  if (circ) CK(cudaMemcpyAsync(circ, p->circ, S, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  if (apo) CK(cudaMemcpyAsync(apo, p->apo, S * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+
+extern "C" int vistaf_ftp_workspace_plane(const VistafFtpPlan* p, int chunk, const char* name, size_t* off, size_t* bytes) {
+  FtpWs L;
+  ftp_layout(p, chunk, L);
+  const size_t S = (size_t)p->h * p->w;
+  struct { const char* n; size_t o, b; } tab[] = {
+      {"img", L.img, S * 4}, {"grad", L.grad, S * 4}, {"bad", L.bad, S}, {"I", L.I, S * 4}, {"Iw", L.Iw, S * 4},
+      {"R", L.R, (size_t)p->h * p->np * 8}, {"Pw", L.Pw, (size_t)p->np * p->np * 8}, {"wrapped", L.wrapped, S * 4},
+      {"qprod", L.qprod, S * 4}, {"quality", L.quality, S * 4}, {"m1", L.m1, S}, {"m2", L.m2, S},
+      {"reliable", L.reliable, S}, {"uf", L.uf, S * 8}, {"unw", L.unw, S * 4}, {"contact", L.contact, S},
+      {"contact_d", L.contact_d, S}, {"hm", L.hm, S * 4}, {"dist_in", L.dist_in, S * 4}, {"dist_out", L.dist_out, S * 4},
+      {"sm", L.sm, S * 4}, {"scal", L.scal, sizeof(FtpScal)}};
+  for (auto& t : tab)
+    if (!strcmp(t.n, name)) { *off = t.o; *bytes = t.b; return 0; }
+  return vistaf_set_err("unknown workspace plane", cudaErrorInvalidValue, __FILE__, __LINE__);
+}
+
+// Stage A up to the apodised, normalised image Iw and its median (shared by reference and deformed frames).
+static int ftp_preprocess(VistafFtpPlan* p, const uint8_t* gray, int nb, char* ws, const FtpWs& L, cudaStream_t st) {
+  const VistafFtpParams& P = p->P;
+  const int h = p->h, w = p->w, npix = h * w;
+  const long long plane = npix;
+  float* img = (float*)(ws + L.img); float* grad = (float*)(ws + L.grad);
+  uint8_t* bad0 = (uint8_t*)(ws + L.bad0); uint8_t* bad = (uint8_t*)(ws + L.bad);
+  float* tmp = (float*)(ws + L.tmp); float* I = (float*)(ws + L.I); float* Iw = (float*)(ws + L.Iw);
+  FtpScal* sc = (FtpScal*)(ws + L.scal);
+  SelectState* sel = (SelectState*)(ws + L.sel);
+  k_ftp_init<<<cdiv(nb, 128), 128, 0, st>>>(sc, nb);
+  k_ftp_sobel<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(gray, img, grad, h, w);
+  CKL();
+  if (select_quantile(MaskedVal{img, p->valid, plane}, sel, npix, nb, P.bad_int_pct, true, st)) return 1;
+  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_HI);
+  if (select_quantile(MaskedVal{grad, p->valid, plane}, sel, npix, nb, P.bad_grad_pct, true, st)) return 1;
+  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_GRAD);
+  BadLoad bl{img, grad, p->valid, sc, plane, w};
+  if (P.bad_dilate > 1) {
+    if (morph<true>(bl, PostId(), bad, h, w, nb, p->se_bad, st)) return 1;
+  } else {
+    k_ftp_badraw<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(bl, bad, h, w);
+  }
+  (void)bad0;
+  k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(bad, sc, npix, 0);
+  CKL();
+  if (telea_inpaint(TeleaMask{bad, plane, w}, img, (size_t)npix, &sc[0].status, sizeof(FtpScal), ws + L.telea, h, w, nb,
+                    P.bad_inpaint_radius, st))
+    return 1;
+  if (gauss_blur(PlaneLoad{img, plane, w}, IllumStoreF{img, I, plane, w}, tmp, h, w, nb, p->g_illum, p->g_illum, st)) return 1;
+  if (gauss_blur(PlaneLoad{I, plane, w}, ApoStore{p->apo, Iw, plane, w}, tmp, h, w, nb, p->g_pre, p->g_pre, st)) return 1;
+  if (select_quantile(MaskedVal{Iw, p->valid, plane}, sel, npix, nb, -1.0f, true, st)) return 1;
+  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_MU);
+  CKL();
+  return 0;
+}
+
+static int ftp_patch_field(VistafFtpPlan* p, int nb, char* ws, const FtpWs& L, bool ref, cudaStream_t st) {
+  const int h = p->h, w = p->w, N = p->N, pad = p->P.fft_pad, np = p->np;
+  float* Iw = (float*)(ws + L.Iw);
+  float2* R = (float2*)(ws + L.R); float2* Pw = (float2*)(ws + L.Pw);
+  FtpScal* sc = (FtpScal*)(ws + L.scal);
+  k_ftp_rowdft<<<dim3(h, nb), 256, (size_t)N * 4, st>>>(Iw, sc, R, p->fN.tw, p->kxs, h, w, N, pad, np);
+  k_ftp_coldft<<<dim3(np, nb), 256, (size_t)h * 8, st>>>(R, Pw, p->fN.tw, p->kys, p->hann, h, N, pad, np);
+  if (ref)
+    k_ftp_field<true><<<dim3(h, nb), 256, 0, st>>>(Pw, p->fN.tw, p->rampx, p->rampy, p->cref, p->amp_ref, nullptr, nullptr, h, w, N, pad, np);
+  else
+    k_ftp_field<false><<<dim3(h, nb), 256, 0, st>>>(Pw, p->fN.tw, p->rampx, p->rampy, p->cref, p->amp_ref,
+                                                    (float*)(ws + L.wrapped), (float*)(ws + L.qprod), h, w, N, pad, np);
+  CKL();
+  return 0;
+}
+
+// find_top_peaks / choose_carrier_peak / refine_peak_parabolic_log (shape_ftp.py:420-483) on the host, once per reference
+static int ftp_pick_carrier(VistafFtpPlan* p, const std::vector<float2>& F) {
+  const int N = p->N, cy = N / 2, cx = N / 2, dc = p->P.dc_exclusion;
+  std::vector<float> mag((size_t)N * N);
+  for (int ky = 0; ky < N; ky++)
+    for (int kx = 0; kx < N; kx++) {
+      const float2 v = F[(size_t)ky * N + kx];
+      mag[(size_t)((ky + N / 2) % N) * N + (kx + N / 2) % N] = hypotf(v.x, v.y);
+    }
+  std::vector<float> ms = mag;
+  for (int y = std::max(0, cy - dc); y < std::min(N, cy + dc); y++)
+    for (int x = std::max(0, cx - dc); x < std::min(N, cx + dc); x++) ms[(size_t)y * N + x] = 0.f;
+  const int n = std::min(p->P.n_peaks, N * N);
+  std::vector<int> idx((size_t)N * N);
+  for (size_t i = 0; i < idx.size(); i++) idx[i] = (int)i;
+  std::partial_sort(idx.begin(), idx.begin() + n, idx.end(), [&](int a, int b) { return ms[a] > ms[b] || (ms[a] == ms[b] && a < b); });
+  struct Pk { int x, y; float m; };
+  std::vector<Pk> peaks, cand, cand2;
+  for (int i = 0; i < n; i++) peaks.push_back({idx[i] % N, idx[i] / N, ms[idx[i]]});
+  for (auto& q : peaks) if (q.x > cx) cand.push_back(q);
+  if (cand.empty()) cand = peaks;
+  const int md = (int)(p->P.peak_max_dy_frac * (float)N);
+  for (auto& q : cand) if (abs(q.y - cy) <= md) cand2.push_back(q);
+  if (!cand2.empty()) cand = cand2;
+  if (cand.empty()) return vistaf_set_err("no carrier peak", cudaErrorInvalidValue, __FILE__, __LINE__);
+  Pk best = cand[0];
+  for (auto& q : cand) if (q.m > best.m) best = q;
+  float pxf = (float)best.x, pyf = (float)best.y;
+  if (!(best.x <= 0 || best.x >= N - 1 || best.y <= 0 || best.y >= N - 1)) {
+    auto lm = [&](int y, int x) { return logf(mag[(size_t)y * N + x] + 1e-12f); };
+    auto parab = [](float fm, float f0, float fp) {
+      const float den = fm - 2.0f * f0 + fp;
+      return fabsf(den) < 1e-12f ? 0.0f : 0.5f * (fm - fp) / den;
+    };
+    pxf = (float)best.x + parab(lm(best.y, best.x - 1), lm(best.y, best.x), lm(best.y, best.x + 1));
+    pyf = (float)best.y + parab(lm(best.y - 1, best.x), lm(best.y, best.x), lm(best.y + 1, best.x));
+  }
+  p->peak_xf = pxf; p->peak_yf = pyf;
+  p->kx = (double)pxf - cx; p->ky = (double)pyf - cy;
+  p->pxi = (int)nearbyint((double)pxf); p->pyi = (int)nearbyint((double)pyf);
+  return 0;
+}
+
+static int ftp_set_carrier(VistafFtpPlan* p) {
+  const int N = p->N, np = p->np, bw = np / 2, cx = N / 2, cy = N / 2;
+  if (p->pxi - bw < 0 || p->pxi + bw + 1 > N || p->pyi - bw < 0 || p->pyi + bw + 1 > N)
+    return vistaf_set_err("carrier patch touches the spectrum border (unsupported)", cudaErrorInvalidValue, __FILE__, __LINE__);
+  std::vector<int> kxs(np), kys(np);
+  for (int j = 0; j < np; j++) {
+    kxs[j] = ((p->pxi - bw + j - cx) % N + N) % N;       // fftshift-ed column -> unsigned frequency index
+    kys[j] = ((p->pyi - bw + j - cy) % N + N) % N;
+  }
+  CK(cudaMemcpy(p->kxs, kxs.data(), sizeof(int) * np, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(p->kys, kys.data(), sizeof(int) * np, cudaMemcpyHostToDevice));
+  const double dpx = (double)p->peak_xf - p->pxi, dpy = (double)p->peak_yf - p->pyi;
+  const bool on = fabs(dpx) > 1e-6 || fabs(dpy) > 1e-6;
+  std::vector<float2> rx(N), ry(N);
+  for (int i = 0; i < N; i++) {
+    const double ax = on ? -2.0 * VISTAF_PI * dpx * ((double)i / N) : 0.0, ay = on ? -2.0 * VISTAF_PI * dpy * ((double)i / N) : 0.0;
+    rx[i] = make_float2((float)cos(ax), (float)sin(ax));
+    ry[i] = make_float2((float)cos(ay), (float)sin(ay));
+  }
+  CK(cudaMemcpy(p->rampx, rx.data(), sizeof(float2) * N, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(p->rampy, ry.data(), sizeof(float2) * N, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+extern "C" int vistaf_ftp_set_reference(VistafFtpPlan* p, const uint8_t* ref_gray, void* workspace, size_t ws_bytes,
+                                        VistafFtpReferenceInfo* info, void* stream) {
+  if (!p || !ref_gray || !workspace) return vistaf_set_err("vistaf_ftp_set_reference: null argument", cudaErrorInvalidValue, __FILE__, __LINE__);
+  cudaStream_t st = (cudaStream_t)stream;
+  FtpWs L;
+  ftp_layout(p, 1, L);
+  const int N = p->N;
+  const size_t dense = align256((size_t)N * N * 4) + align256((size_t)N * N * 8);
+  if (L.total + dense > ws_bytes) return vistaf_set_err("vistaf_ftp_set_reference: workspace too small", cudaErrorInvalidValue, __FILE__, __LINE__);
+  char* ws = (char*)workspace;
+  if (ftp_preprocess(p, ref_gray, 1, ws, L, st)) return 1;
+  float* Ip = (float*)(ws + L.total);
+  float2* F = (float2*)(ws + L.total + align256((size_t)N * N * 4));
+  k_ftp_pad<<<dim3(cdiv(N, 256), N), 256, 0, st>>>((float*)(ws + L.Iw), (FtpScal*)(ws + L.scal), Ip, p->h, p->w, N, p->P.fft_pad);
+  CKL();
+  if (fft2d_dense(Ip, F, p->fN, p->fN, N, N, 1, -1, true, st)) return 1;
+  std::vector<float2> hF((size_t)N * N);
+  CK(cudaMemcpyAsync(hF.data(), F, sizeof(float2) * hF.size(), cudaMemcpyDeviceToHost, st));
+  FtpScal hs;
+  CK(cudaMemcpyAsync(&hs, ws + L.scal, sizeof(FtpScal), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (ftp_pick_carrier(p, hF)) return 1;
+  if (ftp_set_carrier(p)) return 1;
+  if (ftp_patch_field(p, 1, ws, L, true, st)) return 1;
+  CK(cudaStreamSynchronize(st));
+  p->have_ref = true;
+  p->ref_bad = (int)hs.n_bad;
+  if (info) {
+    info->peak_x = p->peak_xf; info->peak_y = p->peak_yf; info->fft_h = N; info->fft_w = N;
+    info->kx = (float)p->kx; info->ky = (float)p->ky;
+    info->period_px = fabs(p->kx) > 1e-9 ? (float)((double)N / fabs(p->kx)) : 0.f;
+    info->bad_px = p->ref_bad;
+  }
+  return 0;
+}
+
+template <bool ORDER2>
+static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, SelectState* sel, int nb, int mode,
+                    cudaStream_t st) {
+  const int npix = p->h * p->w;
+  const FitGeom g{p->w, (float)((p->w - 1) / 2.0), (float)((p->h - 1) / 2.0)};
+  k_irls_begin<<<nb, 1, 0, st>>>(sc, mode);
+  for (int it = 0; it < 6; it++) {
+    k_irls_accum<ORDER2><<<dim3(64, nb), 256, 0, st>>>(z, fm, sc, g, npix, it);
+    k_irls_solve<ORDER2><<<nb, 1, 0, st>>>(sc, it);
+    if (it == 5) break;
+    ResidVal<ORDER2> rv{z, fm, sc, g, (long long)npix, 0};
+    if (select_quantile(rv, sel, npix, nb, -1.0f, true, st)) return 1;
+    k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_IRLS_MED);
+    rv.mode = 1;
+    if (select_quantile(rv, sel, npix, nb, -1.0f, false, st)) return 1;
+    k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_IRLS_MAD);
+  }
+  CKL();
+  return 0;
+}
+
+static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const VistafFtpOutputs& O, size_t f0, char* ws,
+                     const FtpWs& L, cudaStream_t st) {
+  const VistafFtpParams& P = p->P;
+  const int h = p->h, w = p->w, npix = h * w;
+  const long long plane = npix;
+  const uint8_t* gray = gray_all + f0 * (size_t)npix;
+  float* tmp = (float*)(ws + L.tmp);
+  float* wrapped = (float*)(ws + L.wrapped); float* qprod = (float*)(ws + L.qprod); float* quality = (float*)(ws + L.quality);
+  uint8_t* m1 = (uint8_t*)(ws + L.m1); uint8_t* m2 = (uint8_t*)(ws + L.m2);
+  uint8_t* rel = O.reliable ? O.reliable + f0 * (size_t)npix : (uint8_t*)(ws + L.reliable);
+  ull* uf = (ull*)(ws + L.uf); unsigned int* area = (unsigned int*)(ws + L.area);
+  float* unw = (float*)(ws + L.unw);
+  uint8_t* contact = (uint8_t*)(ws + L.contact);
+  uint8_t* contact_d = O.contact_dilated ? O.contact_dilated + f0 * (size_t)npix : (uint8_t*)(ws + L.contact_d);
+  float* hnum = (float*)(ws + L.hnum); float* hm = (float*)(ws + L.hm);
+  float* dist_in = (float*)(ws + L.dist_in); float* dist_out = (float*)(ws + L.dist_out);
+  unsigned int* dtmp = (unsigned int*)(ws + L.dtmp);
+  float* sm = (float*)(ws + L.sm);
+  unsigned int* peak = (unsigned int*)(ws + L.peak);
+  FtpScal* sc = (FtpScal*)(ws + L.scal);
+  SelectState* sel = (SelectState*)(ws + L.sel);
+  float* out = O.height_mm + f0 * (size_t)npix;
+  const FitGeom g{w, (float)((w - 1) / 2.0), (float)((h - 1) / 2.0)};
+  const dim3 gpix(cdiv(npix, 256), nb);
+
+  // ---- A: demodulation
+  if (ftp_preprocess(p, gray, nb, ws, L, st)) return 1;
+  if (ftp_patch_field(p, nb, ws, L, false, st)) return 1;
+  // ---- B: reliable mask
+  if (gauss_blur(PlaneLoad{qprod, plane, w}, PlaneStore{quality, plane, w}, tmp, h, w, nb, p->g_qual, p->g_qual, st)) return 1;
+  if (select_quantile(MaskedVal{quality, p->roi, plane}, sel, npix, nb, P.amp_percentile, true, st)) return 1;
+  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_AMP);
+  RelRawLoad rl{quality, p->roi, sc, plane, w};
+  if (morph<true>(rl, PostId(), m1, h, w, nb, p->se_close, st)) return 1;                       // close = dilate, erode
+  if (morph<false>(MaskLoad{m1, plane, w}, PostAnd{p->roi, 0, w}, m2, h, w, nb, p->se_close, st)) return 1;
+  if (uf_label(MaskFg{m2, plane, w}, EdgeZero(), uf, area, (unsigned int*)nullptr, 0, h, w, nb, st)) return 1;
+  k_uf_largest<<<gpix, 256, 0, st>>>(uf, area, &sc[0].best_cc, sizeof(FtpScal), npix);
+  LargestLoad ll{uf, p->roi, sc, plane, w};
+  if (P.edge_margin > 0) {
+    if (morph<false>(ll, PostId(), rel, h, w, nb, p->se_edge, st)) return 1;                    // chamfer distance > margin
+  } else {
+    MorphSE one = se_rect(1, 1);
+    if (morph<false>(ll, PostId(), rel, h, w, nb, one, st)) return 1;
+  }
+  k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(rel, sc, npix, 1);
+  k_ftp_mark_empty<<<nb, 1, 0, st>>>(sc);
+  k_ftp_seed<<<dim3(64, nb), 256, 0, st>>>(quality, rel, sc, npix);
+  CKL();
+  // ---- C: unwrap
+  k_ftp_residues<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(wrapped, rel, sc, h, w);
+  if (uf_label(MaskFg{rel, plane, w}, PhaseEdge{wrapped, plane}, uf, (unsigned int*)nullptr, &sc[0].uf_bad, sizeof(FtpScal), h, w, nb, st))
+    return 1;
+  k_ftp_seed_root<<<nb, 1, 0, st>>>(uf, sc, npix);
+  k_ftp_unwrap_apply<<<gpix, 256, 0, st>>>(uf, wrapped, sc, unw, npix);
+  CKL();
+  // ---- D: plane removal, two-pass quadric detrend
+  FitMask fm_rel{rel, contact_d, sc, plane, 0}, fm_bg{rel, contact_d, sc, plane, 1};
+  if (irls_fit<false>(p, unw, fm_rel, sc, sel, nb, 0, st)) return 1;
+  k_ftp_sub_fit1<<<gpix, 256, 0, st>>>(unw, sc, g, npix);
+  if (irls_fit<true>(p, unw, fm_rel, sc, sel, nb, 1, st)) return 1;
+  if (select_quantile(AbsResVal{unw, rel, sc, g, plane, 0}, sel, npix, nb, P.contact_pct, true, st)) return 1;
+  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CONTACT);
+  k_ftp_contact<<<gpix, 256, 0, st>>>(unw, rel, sc, g, contact, npix, 1);
+  k_ftp_contact_frac<<<nb, 1, 0, st>>>(sc, P.min_contact_frac, P.max_contact_frac);
+  if (select_quantile(AbsResVal{unw, rel, sc, g, plane, 1}, sel, npix, nb, 0.f, true, st, &sc[0].q2, sizeof(FtpScal))) return 1;
+  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CONTACT2);
+  k_ftp_contact<<<gpix, 256, 0, st>>>(unw, rel, sc, g, contact, npix, 0);
+  {
+    const uint8_t* src = contact;
+    for (int it = 0; it < P.dilate_iters; it++) {
+      uint8_t* dst = (it == P.dilate_iters - 1) ? contact_d : ((it & 1) ? m2 : m1);
+      if (it == P.dilate_iters - 1) { if (morph<true>(MaskLoad{src, plane, w}, PostAnd{rel, plane, w}, dst, h, w, nb, p->se_dil, st)) return 1; }
+      else if (morph<true>(MaskLoad{src, plane, w}, PostId(), dst, h, w, nb, p->se_dil, st)) return 1;
+      src = dst;
+    }
+    if (P.dilate_iters <= 0) {
+      MorphSE one = se_rect(1, 1);
+      if (morph<true>(MaskLoad{contact, plane, w}, PostAnd{rel, plane, w}, contact_d, h, w, nb, one, st)) return 1;
+    }
+  }
+  k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(contact_d, sc, npix, 3);
+  k_ftp_bg_decide<<<nb, 1, 0, st>>>(sc);
+  if (irls_fit<true>(p, unw, fm_bg, sc, sel, nb, 2, st)) return 1;
+  if (select_quantile(DetVal{unw, fm_bg, sc, g, plane}, sel, npix, nb, -1.0f, true, st)) return 1;
+  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_BGMED);
+  CKL();
+  // ---- E: masked smoothing (sigma 2.5) and sign
+  if (gauss_blur(HmNumLoad{unw, rel, sc, g, plane, w}, PlaneStore{hnum, plane, w}, tmp, h, w, nb, p->g_smooth, p->g_smooth, st)) return 1;
+  if (gauss_blur(HmDenLoad{unw, rel, plane, w}, RatioStore{hnum, hm, plane, w}, tmp, h, w, nb, p->g_smooth, p->g_smooth, st)) return 1;
+  if (select_quantile(MaskedValB{hm, rel, plane}, sel, npix, nb, P.core_pct, true, st)) return 1;
+  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CORETHR);
+  if (select_quantile(CoreVal{hm, rel, sc, plane}, sel, npix, nb, -1.0f, true, st)) return 1;
+  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_COREMED);
+  CKL();
+  // ---- F: frontier taper, assembly, sigma-9 fill of the unreliable part, phase -> mm
+  if (chamfer_dt(NotMaskZero{rel, plane, w}, dist_in, dtmp, h, w, nb, st)) return 1;
+  if (chamfer_dt(MaskZero{rel, plane, w}, dist_out, dtmp, h, w, nb, st)) return 1;
+  if (gauss_blur(AsmLoad{hm, dist_in, rel, p->roi, sc, plane, w, P.frontier_band}, Den9Store{p->den9, sm, plane, w}, tmp, h, w,
+                 nb, p->g_unrel, p->g_unrel, st))
+    return 1;
+  k_ftp_assemble<<<gpix, 256, 0, st>>>(hm, dist_in, dist_out, sm, rel, p->roi, sc, out, npix, P.frontier_band,
+                                       P.height_model, P.use_negated_height);
+  CKL();
+  // ---- G: blob filter + force reduction
+  if (uf_label(CandFg{out, plane, w}, EdgeZero(), uf, (unsigned int*)nullptr, (unsigned int*)nullptr, 0, h, w, nb, st)) return 1;
+  CK(cudaMemsetAsync(peak, 0, sizeof(unsigned int) * (size_t)npix * nb, st));
+  k_ftp_blob_peak<<<gpix, 256, 0, st>>>(uf, out, peak, npix);
+  uint8_t* kept = O.contact_kept ? O.contact_kept + f0 * (size_t)npix : nullptr;
+  k_ftp_blob_apply<<<gpix, 256, 0, st>>>(uf, peak, sc, out, kept, npix, P.blob_min_peak_mm, P.blob_rel_frac);
+  k_depth_sign<<<dim3(64, nb), 256, 0, st>>>(out, nullptr, &sc[0].pos_sum, &sc[0].neg_sum, sizeof(FtpScal), npix);
+  k_depth_reduce<<<dim3(64, nb), 256, 0, st>>>(out, nullptr, &sc[0].pos_sum, &sc[0].neg_sum, sizeof(FtpScal), &sc[0].vol_sum,
+                                               &sc[0].vol_cnt, &sc[0].vol_max_bits, npix, (float)P.depth_eps_mm);
+  if (O.output_reliable && O.output_reliable != rel)
+    CK(cudaMemcpyAsync(O.output_reliable + f0 * (size_t)npix, rel, (size_t)npix * nb, cudaMemcpyDeviceToDevice, st));
+  const double period = fabs(p->kx) > 1e-9 ? (double)p->N / fabs(p->kx) : 0.0;
+  k_ftp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, O.records + f0, nb, w, period, P.grating_pitch_mm, P.force_model);
+  CKL();
+  return 0;
+}
+
+extern "C" int vistaf_ftp_batch(VistafFtpPlan* p, const uint8_t* def_gray, int batch, const VistafFtpOutputs* out,
+                                void* workspace, size_t ws_bytes, void* stream) {
+  if (!p || !def_gray || !out || !out->height_mm || !out->records || !workspace)
+    return vistaf_set_err("vistaf_ftp_batch: null argument", cudaErrorInvalidValue, __FILE__, __LINE__);
+  if (!p->have_ref) return vistaf_set_err("vistaf_ftp_batch: call vistaf_ftp_set_reference first", cudaErrorInvalidValue, __FILE__, __LINE__);
+  FtpWs L;
+  int chunk = batch;
+  while (chunk >= 1) { ftp_layout(p, chunk, L); if (L.total <= ws_bytes) break; chunk = chunk > 8 ? chunk - chunk / 8 : chunk - 1; }
+  if (chunk < 1) return vistaf_set_err("vistaf_ftp_batch: workspace too small for one frame", cudaErrorInvalidValue, __FILE__, __LINE__);
+  for (int f0 = 0; f0 < batch; f0 += chunk) {
+    int nb = batch - f0 < chunk ? batch - f0 : chunk;
+    if (nb != chunk) ftp_layout(p, nb, L);
+    if (ftp_chunk(p, def_gray, nb, *out, (size_t)f0, (char*)workspace, L, (cudaStream_t)stream)) return 1;
+  }
+  return 0;
+}
+
+// force_sensor.depth_map_to_volume_cm3 on device maps: out3[b] = (volume_cm3, area_mm2, max_depth_mm)
+struct VolScratch { double pos, neg, vsum; unsigned int vcnt, vmax; };
+__global__ void k_vol_finish(const VolScratch* s, double* out3, int n, double mm_per_px) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double a = mm_per_px * mm_per_px;
+  double V = 0, A = 0, D = 0;
+  if (s[i].vcnt) {
+    V = (double)__fmul_rn((float)s[i].vsum, (float)a) / 1000.0;
+    A = (double)s[i].vcnt * a;
+    D = (double)__uint_as_float(s[i].vmax);
+  }
+  out3[3 * i] = V; out3[3 * i + 1] = A; out3[3 * i + 2] = D;
+}
+extern "C" int vistaf_depth_to_volume(const float* height_mm, const uint8_t* roi, int batch, long long npix, double mm_per_px,
+                                      double depth_eps_mm, double* out3, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  VolScratch* s = nullptr;
+  CK(cudaMallocAsync(&s, sizeof(VolScratch) * batch, st));
+  CK(cudaMemsetAsync(s, 0, sizeof(VolScratch) * batch, st));
+  k_depth_sign<<<dim3(64, batch), 256, 0, st>>>(height_mm, roi, &s[0].pos, &s[0].neg, sizeof(VolScratch), npix);
+  k_depth_reduce<<<dim3(64, batch), 256, 0, st>>>(height_mm, roi, &s[0].pos, &s[0].neg, sizeof(VolScratch), &s[0].vsum,
+                                                  &s[0].vcnt, &s[0].vmax, npix, (float)depth_eps_mm);
+  k_vol_finish<<<cdiv(batch, 128), 128, 0, st>>>(s, out3, batch, mm_per_px);
+  CKL();
+  CK(cudaFreeAsync(s, st));
+  return 0;
 }

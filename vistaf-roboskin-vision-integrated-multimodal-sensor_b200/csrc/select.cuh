@@ -39,8 +39,13 @@ __device__ __forceinline__ float sel_pos(unsigned int count, float q) {
   if (q < 0.f) return (float)((count - 1) >> 1);
   return (float)(count - 1) * (q / 100.0f);
 }
-static __global__ void k_sel_begin(SelectState* st, float q) {
+// qv != nullptr: per-frame quantile read from device memory (byte stride qstride); NaN = frame inactive.
+__device__ __forceinline__ float sel_q(float q, const float* qv, size_t qstride, int b) {
+  return qv ? *(const float*)((const char*)qv + (size_t)b * qstride) : q;
+}
+static __global__ void k_sel_begin(SelectState* st, float q0, const float* qv, size_t qstride) {
   SelectState& s = st[blockIdx.x];
+  const float q = sel_q(q0, qv, qstride, blockIdx.x);
   for (int i = threadIdx.x; i < 256; i += blockDim.x) s.hist[i] = 0;
   if (threadIdx.x == 0) {
     float pos = sel_pos(s.count, q);
@@ -112,9 +117,10 @@ __global__ void k_sel_neighbour(Val val, SelectState* st, long long n) {
 }
 
 // numpy _lerp in float32: a + (b-a)*t, switched to b - (b-a)*(1-t) for t >= 0.5, t = frac(pos).
-static __global__ void k_sel_finish(SelectState* st, float q) {
+static __global__ void k_sel_finish(SelectState* st, float q0, const float* qv, size_t qstride) {
   SelectState& s = st[blockIdx.x];
-  if (s.count == 0) { s.vk = s.vk1 = s.result = __int_as_float(0x7fc00000); return; }
+  const float q = sel_q(q0, qv, qstride, blockIdx.x);
+  if (s.count == 0 || q != q) { s.vk = s.vk1 = s.result = __int_as_float(0x7fc00000); return; }
   float pos = sel_pos(s.count, q);
   unsigned int k = (unsigned int)floorf(pos);
   float g = pos - floorf(pos);
@@ -132,7 +138,7 @@ static __global__ void k_sel_finish(SelectState* st, float q) {
 // Host: full selection of quantile q (percent) for `batch` frames over n candidates each.
 template <class Val>
 static int select_quantile(Val val, SelectState* st, long long n, int batch, float q, bool need_count,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0) {
   const int thr = 256;
   int gx = (int)((n + thr * 8 - 1) / (thr * 8));
   if (gx > 592) gx = 592;
@@ -142,13 +148,13 @@ static int select_quantile(Val val, SelectState* st, long long n, int batch, flo
     CK(cudaMemsetAsync(st, 0, sizeof(SelectState) * batch, stream));
     k_sel_count<Val><<<grid, thr, 0, stream>>>(val, st, n);
   }
-  k_sel_begin<<<batch, 256, 0, stream>>>(st, q);
+  k_sel_begin<<<batch, 256, 0, stream>>>(st, q, qv, qstride);
   for (int shift = 24; shift >= 0; shift -= 8) {
     k_sel_hist<Val><<<grid, thr, 0, stream>>>(val, st, n, shift);
     k_sel_pick<<<batch, 256, 0, stream>>>(st, shift);
   }
   k_sel_neighbour<Val><<<grid, thr, 0, stream>>>(val, st, n);
-  k_sel_finish<<<batch, 1, 0, stream>>>(st, q);
+  k_sel_finish<<<batch, 1, 0, stream>>>(st, q, qv, qstride);
   CKL();
   return 0;
 }
