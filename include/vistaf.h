@@ -93,6 +93,19 @@ typedef struct VistafTempPlan VistafTempPlan;
 const char* vistaf_last_error(void);
 int vistaf_version(void);
 
+/* Stage timers (measurement only; off by default).  When enabled every pipeline stage boundary records a CUDA
+ * event on the launch stream; vistaf_profile_read synchronises and returns the accumulated milliseconds, call
+ * count and kernel-launch count per stage since the previous read.  vistaf_launch_count() = kernels this
+ * process has launched through the library so far (always counted). */
+typedef struct {
+  char name[48];
+  double ms;
+  int32_t calls, launches;
+} VistafStageTime;
+int vistaf_profile_enable(int on);
+int vistaf_profile_read(VistafStageTime* out, int max_stages, int* n_out);
+long long vistaf_launch_count(void);
+
 /* Temperature path (replaces temperature_sensor.main :749 numeric body, batched). */
 int vistaf_temp_plan_create(const VistafTempParams* params, VistafTempPlan** plan);
 void vistaf_temp_plan_destroy(VistafTempPlan* plan);

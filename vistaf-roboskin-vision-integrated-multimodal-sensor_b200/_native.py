@@ -125,6 +125,26 @@ class FtpReferenceInfo(C.Structure):
                 ("kx", C.c_float), ("ky", C.c_float), ("period_px", C.c_float), ("bad_px", C.c_int32)]
 
 
+class StageTime(C.Structure):
+    _fields_ = [("name", C.c_char * 48), ("ms", C.c_double), ("calls", C.c_int32), ("launches", C.c_int32)]
+
+
+def profile_enable(on: bool) -> None:
+    check(lib().vistaf_profile_enable(int(bool(on))), "profile_enable")
+
+
+def profile_read() -> list:
+    """[(stage, ms, calls, launches)] accumulated since the last read (synchronises the last recorded event)."""
+    buf = (StageTime * 64)()
+    n = C.c_int()
+    check(lib().vistaf_profile_read(buf, 64, C.byref(n)), "profile_read")
+    return [(buf[i].name.decode(), float(buf[i].ms), int(buf[i].calls), int(buf[i].launches)) for i in range(n.value)]
+
+
+def launch_count() -> int:
+    return int(lib().vistaf_launch_count())
+
+
 _lib = None
 
 
@@ -161,6 +181,8 @@ def lib():
                                                  C.POINTER(C.c_size_t)]
         L.vistaf_depth_to_volume.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_double, C.c_double,
                                              C.c_void_p, C.c_void_p]
+        L.vistaf_profile_read.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.vistaf_launch_count.restype = C.c_longlong
         L.vistaf_curve_predict.restype = C.c_double
         L.vistaf_curve_predict.argtypes = [C.POINTER(CurveModel), C.c_double]
         _lib = L

@@ -129,7 +129,7 @@ static int gauss_blur(Load ld, Store st, float* tmp, int h, int w, int batch, co
                       const GaussKernel& gy, cudaStream_t stream) {
   const long long plane = (long long)h * w;
   dim3 g1(cdiv(w, BLUR_ROW_SEG), h, batch);
-  k_blur_rows<Load><<<g1, BLUR_ROW_THREADS, 0, stream>>>(ld, tmp, h, w, plane, gx);
+  VL(), k_blur_rows<Load><<<g1, BLUR_ROW_THREADS, 0, stream>>>(ld, tmp, h, w, plane, gx);
   CKL();
   const int tyt = gy.ksize > 100 ? 32 : 16;
   dim3 blk(32, tyt), g2(cdiv(w, 32), cdiv(h, 8 * tyt), batch);
@@ -139,7 +139,7 @@ static int gauss_blur(Load ld, Store st, float* tmp, int h, int w, int batch, co
     CK(cudaFuncSetAttribute((const void*)k_blur_cols<Store>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     attr_done = true;
   }
-  k_blur_cols<Store><<<g2, blk, sm, stream>>>(tmp, st, h, w, plane, gy);
+  VL(), k_blur_cols<Store><<<g2, blk, sm, stream>>>(tmp, st, h, w, plane, gy);
   CKL();
   return 0;
 }

@@ -17,6 +17,11 @@ int vistaf_set_err(const char* what, cudaError_t e, const char* file, int line);
   } while (0)
 #define CKL() CK(cudaGetLastError())
 
+// launch accounting + stage timers (api.cu).  Every kernel launch in the library is written `VL(), k<<<...>>>(...)`.
+extern long long g_vistaf_launches;
+#define VL() ((void)++g_vistaf_launches)
+void vistaf_stage_mark(const char* name, cudaStream_t st);      // "" closes the previous stage without opening one
+
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 static inline size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
 

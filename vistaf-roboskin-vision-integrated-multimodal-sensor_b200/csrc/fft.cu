@@ -106,20 +106,20 @@ int fft2d_dense(const void* in, float2* out, const Fft1D& pw, const Fft1D& ph, i
   if (sign < 0) {
     if (real_in) {
       if (smem_opt_in((const void*)k_fft_rows<-1, true>, sm_r)) return 1;
-      k_fft_rows<-1, true><<<gr, 256, sm_r, st>>>(in, out, pw, h, nseq_r, w, w, plane, plane, 1.f);
+      VL(), k_fft_rows<-1, true><<<gr, 256, sm_r, st>>>(in, out, pw, h, nseq_r, w, w, plane, plane, 1.f);
     } else {
       if (smem_opt_in((const void*)k_fft_rows<-1, false>, sm_r)) return 1;
-      k_fft_rows<-1, false><<<gr, 256, sm_r, st>>>(in, out, pw, h, nseq_r, w, w, plane, plane, 1.f);
+      VL(), k_fft_rows<-1, false><<<gr, 256, sm_r, st>>>(in, out, pw, h, nseq_r, w, w, plane, plane, 1.f);
     }
     CKL();
     if (smem_opt_in((const void*)k_fft_cols<-1>, sm_c)) return 1;
-    k_fft_cols<-1><<<gc, 256, sm_c, st>>>(out, out, ph, w, ncol, w, plane, sc);
+    VL(), k_fft_cols<-1><<<gc, 256, sm_c, st>>>(out, out, ph, w, ncol, w, plane, sc);
   } else {
     if (smem_opt_in((const void*)k_fft_rows<1, false>, sm_r)) return 1;
-    k_fft_rows<1, false><<<gr, 256, sm_r, st>>>(in, out, pw, h, nseq_r, w, w, plane, plane, 1.f);
+    VL(), k_fft_rows<1, false><<<gr, 256, sm_r, st>>>(in, out, pw, h, nseq_r, w, w, plane, plane, 1.f);
     CKL();
     if (smem_opt_in((const void*)k_fft_cols<1>, sm_c)) return 1;
-    k_fft_cols<1><<<gc, 256, sm_c, st>>>(out, out, ph, w, ncol, w, plane, sc);
+    VL(), k_fft_cols<1><<<gc, 256, sm_c, st>>>(out, out, ph, w, ncol, w, plane, sc);
   }
   CKL();
   return 0;

@@ -131,8 +131,10 @@ __global__ void k_crop_gray(const uint8_t* __restrict__ frames, uint8_t* __restr
 extern "C" int vistaf_crop_gray(const uint8_t* frames, int batch, int H, int W, int x1, int y1, int h, int w,
                                 uint8_t* gray, void* stream) {
   if (x1 < 0 || y1 < 0 || x1 + w > W || y1 + h > H) return vistaf_set_err("crop outside frame", cudaErrorInvalidValue, __FILE__, __LINE__);
-  vftp::k_crop_gray<<<dim3(cdiv(w, 256), h, batch), 256, 0, (cudaStream_t)stream>>>(frames, gray, H, W, x1, y1, h, w);
+  vistaf_stage_mark("F.crop_gray", (cudaStream_t)stream);
+  VL(), vftp::k_crop_gray<<<dim3(cdiv(w, 256), h, batch), 256, 0, (cudaStream_t)stream>>>(frames, gray, H, W, x1, y1, h, w);
   CKL();
+  vistaf_stage_mark("", (cudaStream_t)stream);
   return 0;
 }
 
@@ -971,7 +973,7 @@ extern "C" int vistaf_ftp_plan_create(const VistafFtpParams* P, VistafFtpPlan** 
   CK(cudaMalloc(&p->hann, sizeof(float) * np)); CK(cudaMalloc(&p->kxs, sizeof(int) * np)); CK(cudaMalloc(&p->kys, sizeof(int) * np));
   int r_valid = P->r - P->roi_erode_px;
   if (r_valid < 0) r_valid = 0;
-  k_ftp_geometry<<<dim3(cdiv(p->w, 256), p->h), 256>>>(p->roi, p->circ, p->valid, p->apo, p->h, p->w, P->cx, P->cy, P->r,
+  VL(), k_ftp_geometry<<<dim3(cdiv(p->w, 256), p->h), 256>>>(p->roi, p->circ, p->valid, p->apo, p->h, p->w, P->cx, P->cy, P->r,
                                                        r_valid, P->apod_taper);
   CKL();
   // den9 = GaussianBlur(roi, sigma 9) + 1e-6 (shape_ftp.py:1146 with mask = roi_eroded, :1820)
@@ -1039,29 +1041,33 @@ static int ftp_preprocess(VistafFtpPlan* p, const uint8_t* gray, int nb, char* w
   float* tmp = (float*)(ws + L.tmp); float* I = (float*)(ws + L.I); float* Iw = (float*)(ws + L.Iw);
   FtpScal* sc = (FtpScal*)(ws + L.scal);
   SelectState* sel = (SelectState*)(ws + L.sel);
-  k_ftp_init<<<cdiv(nb, 128), 128, 0, st>>>(sc, nb);
-  k_ftp_sobel<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(gray, img, grad, h, w);
+  vistaf_stage_mark("F.sobel_percentiles_bad", st);
+  VL(), k_ftp_init<<<cdiv(nb, 128), 128, 0, st>>>(sc, nb);
+  VL(), k_ftp_sobel<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(gray, img, grad, h, w);
   CKL();
   if (select_quantile(MaskedVal{img, p->valid, plane}, sel, npix, nb, P.bad_int_pct, true, st)) return 1;
-  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_HI);
+  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_HI);
   if (select_quantile(MaskedVal{grad, p->valid, plane}, sel, npix, nb, P.bad_grad_pct, true, st)) return 1;
-  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_GRAD);
+  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_GRAD);
   BadLoad bl{img, grad, p->valid, sc, plane, w};
   if (P.bad_dilate > 1) {
     if (morph<true>(bl, PostId(), bad, h, w, nb, p->se_bad, st)) return 1;
   } else {
-    k_ftp_badraw<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(bl, bad, h, w);
+    VL(), k_ftp_badraw<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(bl, bad, h, w);
   }
   (void)bad0;
-  k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(bad, sc, npix, 0);
+  VL(), k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(bad, sc, npix, 0);
   CKL();
+  vistaf_stage_mark("F.telea_inpaint", st);
   if (telea_inpaint(TeleaMask{bad, plane, w}, img, (size_t)npix, &sc[0].status, sizeof(FtpScal), ws + L.telea, h, w, nb,
                     P.bad_inpaint_radius, st))
     return 1;
+  vistaf_stage_mark("F.illum_blur45", st);
   if (gauss_blur(PlaneLoad{img, plane, w}, IllumStoreF{img, I, plane, w}, tmp, h, w, nb, p->g_illum, p->g_illum, st)) return 1;
+  vistaf_stage_mark("F.preblur_apo_median", st);
   if (gauss_blur(PlaneLoad{I, plane, w}, ApoStore{p->apo, Iw, plane, w}, tmp, h, w, nb, p->g_pre, p->g_pre, st)) return 1;
   if (select_quantile(MaskedVal{Iw, p->valid, plane}, sel, npix, nb, -1.0f, true, st)) return 1;
-  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_MU);
+  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_MU);
   CKL();
   return 0;
 }
@@ -1071,12 +1077,13 @@ static int ftp_patch_field(VistafFtpPlan* p, int nb, char* ws, const FtpWs& L, b
   float* Iw = (float*)(ws + L.Iw);
   float2* R = (float2*)(ws + L.R); float2* Pw = (float2*)(ws + L.Pw);
   FtpScal* sc = (FtpScal*)(ws + L.scal);
-  k_ftp_rowdft<<<dim3(h, nb), 256, (size_t)N * 4, st>>>(Iw, sc, R, p->fN.tw, p->kxs, h, w, N, pad, np);
-  k_ftp_coldft<<<dim3(np, nb), 256, (size_t)h * 8, st>>>(R, Pw, p->fN.tw, p->kys, p->hann, h, N, pad, np);
+  vistaf_stage_mark("F.carrier_dft_field", st);
+  VL(), k_ftp_rowdft<<<dim3(h, nb), 256, (size_t)N * 4, st>>>(Iw, sc, R, p->fN.tw, p->kxs, h, w, N, pad, np);
+  VL(), k_ftp_coldft<<<dim3(np, nb), 256, (size_t)h * 8, st>>>(R, Pw, p->fN.tw, p->kys, p->hann, h, N, pad, np);
   if (ref)
-    k_ftp_field<true><<<dim3(h, nb), 256, 0, st>>>(Pw, p->fN.tw, p->rampx, p->rampy, p->cref, p->amp_ref, nullptr, nullptr, h, w, N, pad, np);
+    VL(), k_ftp_field<true><<<dim3(h, nb), 256, 0, st>>>(Pw, p->fN.tw, p->rampx, p->rampy, p->cref, p->amp_ref, nullptr, nullptr, h, w, N, pad, np);
   else
-    k_ftp_field<false><<<dim3(h, nb), 256, 0, st>>>(Pw, p->fN.tw, p->rampx, p->rampy, p->cref, p->amp_ref,
+    VL(), k_ftp_field<false><<<dim3(h, nb), 256, 0, st>>>(Pw, p->fN.tw, p->rampx, p->rampy, p->cref, p->amp_ref,
                                                     (float*)(ws + L.wrapped), (float*)(ws + L.qprod), h, w, N, pad, np);
   CKL();
   return 0;
@@ -1162,7 +1169,8 @@ extern "C" int vistaf_ftp_set_reference(VistafFtpPlan* p, const uint8_t* ref_gra
   if (ftp_preprocess(p, ref_gray, 1, ws, L, st)) return 1;
   float* Ip = (float*)(ws + L.total);
   float2* F = (float2*)(ws + L.total + align256((size_t)N * N * 4));
-  k_ftp_pad<<<dim3(cdiv(N, 256), N), 256, 0, st>>>((float*)(ws + L.Iw), (FtpScal*)(ws + L.scal), Ip, p->h, p->w, N, p->P.fft_pad);
+  vistaf_stage_mark("F.reference_dense_fft", st);
+  VL(), k_ftp_pad<<<dim3(cdiv(N, 256), N), 256, 0, st>>>((float*)(ws + L.Iw), (FtpScal*)(ws + L.scal), Ip, p->h, p->w, N, p->P.fft_pad);
   CKL();
   if (fft2d_dense(Ip, F, p->fN, p->fN, N, N, 1, -1, true, st)) return 1;
   std::vector<float2> hF((size_t)N * N);
@@ -1173,6 +1181,7 @@ extern "C" int vistaf_ftp_set_reference(VistafFtpPlan* p, const uint8_t* ref_gra
   if (ftp_pick_carrier(p, hF)) return 1;
   if (ftp_set_carrier(p)) return 1;
   if (ftp_patch_field(p, 1, ws, L, true, st)) return 1;
+  vistaf_stage_mark("", st);
   CK(cudaStreamSynchronize(st));
   p->have_ref = true;
   p->ref_bad = (int)hs.n_bad;
@@ -1190,17 +1199,17 @@ static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, S
                     cudaStream_t st) {
   const int npix = p->h * p->w;
   const FitGeom g{p->w, (float)((p->w - 1) / 2.0), (float)((p->h - 1) / 2.0)};
-  k_irls_begin<<<nb, 1, 0, st>>>(sc, mode);
+  VL(), k_irls_begin<<<nb, 1, 0, st>>>(sc, mode);
   for (int it = 0; it < 6; it++) {
-    k_irls_accum<ORDER2><<<dim3(64, nb), 256, 0, st>>>(z, fm, sc, g, npix, it);
-    k_irls_solve<ORDER2><<<nb, 1, 0, st>>>(sc, it);
+    VL(), k_irls_accum<ORDER2><<<dim3(64, nb), 256, 0, st>>>(z, fm, sc, g, npix, it);
+    VL(), k_irls_solve<ORDER2><<<nb, 1, 0, st>>>(sc, it);
     if (it == 5) break;
     ResidVal<ORDER2> rv{z, fm, sc, g, (long long)npix, 0};
     if (select_quantile(rv, sel, npix, nb, -1.0f, true, st)) return 1;
-    k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_IRLS_MED);
+    VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_IRLS_MED);
     rv.mode = 1;
     if (select_quantile(rv, sel, npix, nb, -1.0f, false, st)) return 1;
-    k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_IRLS_MAD);
+    VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_IRLS_MAD);
   }
   CKL();
   return 0;
@@ -1234,15 +1243,16 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   // ---- A: demodulation
   if (ftp_preprocess(p, gray, nb, ws, L, st)) return 1;
   if (ftp_patch_field(p, nb, ws, L, false, st)) return 1;
+  vistaf_stage_mark("F.quality_reliable_mask", st);
   // ---- B: reliable mask
   if (gauss_blur(PlaneLoad{qprod, plane, w}, PlaneStore{quality, plane, w}, tmp, h, w, nb, p->g_qual, p->g_qual, st)) return 1;
   if (select_quantile(MaskedVal{quality, p->roi, plane}, sel, npix, nb, P.amp_percentile, true, st)) return 1;
-  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_AMP);
+  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_AMP);
   RelRawLoad rl{quality, p->roi, sc, plane, w};
   if (morph<true>(rl, PostId(), m1, h, w, nb, p->se_close, st)) return 1;                       // close = dilate, erode
   if (morph<false>(MaskLoad{m1, plane, w}, PostAnd{p->roi, 0, w}, m2, h, w, nb, p->se_close, st)) return 1;
   if (uf_label(MaskFg{m2, plane, w}, EdgeZero(), uf, area, (unsigned int*)nullptr, 0, h, w, nb, st)) return 1;
-  k_uf_largest<<<gpix, 256, 0, st>>>(uf, area, &sc[0].best_cc, sizeof(FtpScal), npix);
+  VL(), k_uf_largest<<<gpix, 256, 0, st>>>(uf, area, &sc[0].best_cc, sizeof(FtpScal), npix);
   LargestLoad ll{uf, p->roi, sc, plane, w};
   if (P.edge_margin > 0) {
     if (morph<false>(ll, PostId(), rel, h, w, nb, p->se_edge, st)) return 1;                    // chamfer distance > margin
@@ -1250,29 +1260,32 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
     MorphSE one = se_rect(1, 1);
     if (morph<false>(ll, PostId(), rel, h, w, nb, one, st)) return 1;
   }
-  k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(rel, sc, npix, 1);
-  k_ftp_mark_empty<<<nb, 1, 0, st>>>(sc);
-  k_ftp_seed<<<dim3(64, nb), 256, 0, st>>>(quality, rel, sc, npix);
+  VL(), k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(rel, sc, npix, 1);
+  VL(), k_ftp_mark_empty<<<nb, 1, 0, st>>>(sc);
+  VL(), k_ftp_seed<<<dim3(64, nb), 256, 0, st>>>(quality, rel, sc, npix);
   CKL();
+  vistaf_stage_mark("F.unwrap_unionfind", st);
   // ---- C: unwrap
-  k_ftp_residues<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(wrapped, rel, sc, h, w);
+  VL(), k_ftp_residues<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(wrapped, rel, sc, h, w);
   if (uf_label(MaskFg{rel, plane, w}, PhaseEdge{wrapped, plane}, uf, (unsigned int*)nullptr, &sc[0].uf_bad, sizeof(FtpScal), h, w, nb, st))
     return 1;
-  k_ftp_seed_root<<<nb, 1, 0, st>>>(uf, sc, npix);
-  k_ftp_unwrap_apply<<<gpix, 256, 0, st>>>(uf, wrapped, sc, unw, npix);
+  VL(), k_ftp_seed_root<<<nb, 1, 0, st>>>(uf, sc, npix);
+  VL(), k_ftp_unwrap_apply<<<gpix, 256, 0, st>>>(uf, wrapped, sc, unw, npix);
   CKL();
+  vistaf_stage_mark("F.irls_plane", st);
   // ---- D: plane removal, two-pass quadric detrend
   FitMask fm_rel{rel, contact_d, sc, plane, 0}, fm_bg{rel, contact_d, sc, plane, 1};
   if (irls_fit<false>(p, unw, fm_rel, sc, sel, nb, 0, st)) return 1;
-  k_ftp_sub_fit1<<<gpix, 256, 0, st>>>(unw, sc, g, npix);
+  vistaf_stage_mark("F.irls_quadric_contact", st);
+  VL(), k_ftp_sub_fit1<<<gpix, 256, 0, st>>>(unw, sc, g, npix);
   if (irls_fit<true>(p, unw, fm_rel, sc, sel, nb, 1, st)) return 1;
   if (select_quantile(AbsResVal{unw, rel, sc, g, plane, 0}, sel, npix, nb, P.contact_pct, true, st)) return 1;
-  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CONTACT);
-  k_ftp_contact<<<gpix, 256, 0, st>>>(unw, rel, sc, g, contact, npix, 1);
-  k_ftp_contact_frac<<<nb, 1, 0, st>>>(sc, P.min_contact_frac, P.max_contact_frac);
+  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CONTACT);
+  VL(), k_ftp_contact<<<gpix, 256, 0, st>>>(unw, rel, sc, g, contact, npix, 1);
+  VL(), k_ftp_contact_frac<<<nb, 1, 0, st>>>(sc, P.min_contact_frac, P.max_contact_frac);
   if (select_quantile(AbsResVal{unw, rel, sc, g, plane, 1}, sel, npix, nb, 0.f, true, st, &sc[0].q2, sizeof(FtpScal))) return 1;
-  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CONTACT2);
-  k_ftp_contact<<<gpix, 256, 0, st>>>(unw, rel, sc, g, contact, npix, 0);
+  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CONTACT2);
+  VL(), k_ftp_contact<<<gpix, 256, 0, st>>>(unw, rel, sc, g, contact, npix, 0);
   {
     const uint8_t* src = contact;
     for (int it = 0; it < P.dilate_iters; it++) {
@@ -1286,43 +1299,48 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
       if (morph<true>(MaskLoad{contact, plane, w}, PostAnd{rel, plane, w}, contact_d, h, w, nb, one, st)) return 1;
     }
   }
-  k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(contact_d, sc, npix, 3);
-  k_ftp_bg_decide<<<nb, 1, 0, st>>>(sc);
+  VL(), k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(contact_d, sc, npix, 3);
+  VL(), k_ftp_bg_decide<<<nb, 1, 0, st>>>(sc);
+  vistaf_stage_mark("F.irls_quadric_background", st);
   if (irls_fit<true>(p, unw, fm_bg, sc, sel, nb, 2, st)) return 1;
   if (select_quantile(DetVal{unw, fm_bg, sc, g, plane}, sel, npix, nb, -1.0f, true, st)) return 1;
-  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_BGMED);
+  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_BGMED);
   CKL();
+  vistaf_stage_mark("F.smooth_sign", st);
   // ---- E: masked smoothing (sigma 2.5) and sign
   if (gauss_blur(HmNumLoad{unw, rel, sc, g, plane, w}, PlaneStore{hnum, plane, w}, tmp, h, w, nb, p->g_smooth, p->g_smooth, st)) return 1;
   if (gauss_blur(HmDenLoad{unw, rel, plane, w}, RatioStore{hnum, hm, plane, w}, tmp, h, w, nb, p->g_smooth, p->g_smooth, st)) return 1;
   if (select_quantile(MaskedValB{hm, rel, plane}, sel, npix, nb, P.core_pct, true, st)) return 1;
-  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CORETHR);
+  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CORETHR);
   if (select_quantile(CoreVal{hm, rel, sc, plane}, sel, npix, nb, -1.0f, true, st)) return 1;
-  k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_COREMED);
+  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_COREMED);
   CKL();
+  vistaf_stage_mark("F.chamfer_frontier_assemble", st);
   // ---- F: frontier taper, assembly, sigma-9 fill of the unreliable part, phase -> mm
   if (chamfer_dt(NotMaskZero{rel, plane, w}, dist_in, dtmp, h, w, nb, st)) return 1;
   if (chamfer_dt(MaskZero{rel, plane, w}, dist_out, dtmp, h, w, nb, st)) return 1;
   if (gauss_blur(AsmLoad{hm, dist_in, rel, p->roi, sc, plane, w, P.frontier_band}, Den9Store{p->den9, sm, plane, w}, tmp, h, w,
                  nb, p->g_unrel, p->g_unrel, st))
     return 1;
-  k_ftp_assemble<<<gpix, 256, 0, st>>>(hm, dist_in, dist_out, sm, rel, p->roi, sc, out, npix, P.frontier_band,
+  VL(), k_ftp_assemble<<<gpix, 256, 0, st>>>(hm, dist_in, dist_out, sm, rel, p->roi, sc, out, npix, P.frontier_band,
                                        P.height_model, P.use_negated_height);
   CKL();
+  vistaf_stage_mark("F.blob_filter_force", st);
   // ---- G: blob filter + force reduction
   if (uf_label(CandFg{out, plane, w}, EdgeZero(), uf, (unsigned int*)nullptr, (unsigned int*)nullptr, 0, h, w, nb, st)) return 1;
   CK(cudaMemsetAsync(peak, 0, sizeof(unsigned int) * (size_t)npix * nb, st));
-  k_ftp_blob_peak<<<gpix, 256, 0, st>>>(uf, out, peak, npix);
+  VL(), k_ftp_blob_peak<<<gpix, 256, 0, st>>>(uf, out, peak, npix);
   uint8_t* kept = O.contact_kept ? O.contact_kept + f0 * (size_t)npix : nullptr;
-  k_ftp_blob_apply<<<gpix, 256, 0, st>>>(uf, peak, sc, out, kept, npix, P.blob_min_peak_mm, P.blob_rel_frac);
-  k_depth_sign<<<dim3(64, nb), 256, 0, st>>>(out, nullptr, &sc[0].pos_sum, &sc[0].neg_sum, sizeof(FtpScal), npix);
-  k_depth_reduce<<<dim3(64, nb), 256, 0, st>>>(out, nullptr, &sc[0].pos_sum, &sc[0].neg_sum, sizeof(FtpScal), &sc[0].vol_sum,
+  VL(), k_ftp_blob_apply<<<gpix, 256, 0, st>>>(uf, peak, sc, out, kept, npix, P.blob_min_peak_mm, P.blob_rel_frac);
+  VL(), k_depth_sign<<<dim3(64, nb), 256, 0, st>>>(out, nullptr, &sc[0].pos_sum, &sc[0].neg_sum, sizeof(FtpScal), npix);
+  VL(), k_depth_reduce<<<dim3(64, nb), 256, 0, st>>>(out, nullptr, &sc[0].pos_sum, &sc[0].neg_sum, sizeof(FtpScal), &sc[0].vol_sum,
                                                &sc[0].vol_cnt, &sc[0].vol_max_bits, npix, (float)P.depth_eps_mm);
   if (O.output_reliable && O.output_reliable != rel)
     CK(cudaMemcpyAsync(O.output_reliable + f0 * (size_t)npix, rel, (size_t)npix * nb, cudaMemcpyDeviceToDevice, st));
   const double period = fabs(p->kx) > 1e-9 ? (double)p->N / fabs(p->kx) : 0.0;
-  k_ftp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, O.records + f0, nb, w, period, P.grating_pitch_mm, P.force_model);
+  VL(), k_ftp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, O.records + f0, nb, w, period, P.grating_pitch_mm, P.force_model);
   CKL();
+  vistaf_stage_mark("", st);
   return 0;
 }
 
@@ -1363,10 +1381,10 @@ extern "C" int vistaf_depth_to_volume(const float* height_mm, const uint8_t* roi
   VolScratch* s = nullptr;
   CK(cudaMallocAsync(&s, sizeof(VolScratch) * batch, st));
   CK(cudaMemsetAsync(s, 0, sizeof(VolScratch) * batch, st));
-  k_depth_sign<<<dim3(64, batch), 256, 0, st>>>(height_mm, roi, &s[0].pos, &s[0].neg, sizeof(VolScratch), npix);
-  k_depth_reduce<<<dim3(64, batch), 256, 0, st>>>(height_mm, roi, &s[0].pos, &s[0].neg, sizeof(VolScratch), &s[0].vsum,
+  VL(), k_depth_sign<<<dim3(64, batch), 256, 0, st>>>(height_mm, roi, &s[0].pos, &s[0].neg, sizeof(VolScratch), npix);
+  VL(), k_depth_reduce<<<dim3(64, batch), 256, 0, st>>>(height_mm, roi, &s[0].pos, &s[0].neg, sizeof(VolScratch), &s[0].vsum,
                                                   &s[0].vcnt, &s[0].vmax, npix, (float)depth_eps_mm);
-  k_vol_finish<<<cdiv(batch, 128), 128, 0, st>>>(s, out3, batch, mm_per_px);
+  VL(), k_vol_finish<<<cdiv(batch, 128), 128, 0, st>>>(s, out3, batch, mm_per_px);
   CKL();
   CK(cudaFreeAsync(s, st));
   return 0;

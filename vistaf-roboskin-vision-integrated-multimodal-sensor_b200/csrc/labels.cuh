@@ -156,10 +156,10 @@ template <class Fg, class Edge>
 static int uf_label(Fg fg, Edge edge, ull* uf, unsigned int* area, unsigned int* bad, size_t bad_stride, int h, int w,
                     int batch, cudaStream_t st) {
   const int npix = h * w;
-  k_uf_init_rows<Fg, Edge><<<dim3(cdiv(h, 4), batch), 128, 0, st>>>(fg, edge, uf, h, w);
-  k_uf_merge<Fg, Edge><<<dim3(cdiv(w, 256), h, batch), 256, 0, st>>>(fg, edge, uf, bad, bad_stride, h, w);
+  VL(), k_uf_init_rows<Fg, Edge><<<dim3(cdiv(h, 4), batch), 128, 0, st>>>(fg, edge, uf, h, w);
+  VL(), k_uf_merge<Fg, Edge><<<dim3(cdiv(w, 256), h, batch), 256, 0, st>>>(fg, edge, uf, bad, bad_stride, h, w);
   if (area) CK(cudaMemsetAsync(area, 0, sizeof(unsigned int) * (size_t)npix * batch, st));
-  k_uf_flatten<<<dim3(cdiv(npix, 256), batch), 256, 0, st>>>(uf, area, npix);
+  VL(), k_uf_flatten<<<dim3(cdiv(npix, 256), batch), 256, 0, st>>>(uf, area, npix);
   CKL();
   return 0;
 }
@@ -290,7 +290,7 @@ __global__ void __launch_bounds__(CH_THREADS) k_chamfer(Zero zero, float* __rest
 template <class Zero>
 static int chamfer_dt(Zero zero, float* out, unsigned int* tmp, int h, int w, int batch, cudaStream_t st) {
   if (w > CH_THREADS * CH_MAXPT) return vistaf_set_err("chamfer_dt: row too long", cudaErrorInvalidValue, __FILE__, __LINE__);
-  k_chamfer<Zero><<<batch, CH_THREADS, sizeof(unsigned int) * 2 * (size_t)(w + 2), st>>>(zero, out, tmp, h, w);
+  VL(), k_chamfer<Zero><<<batch, CH_THREADS, sizeof(unsigned int) * 2 * (size_t)(w + 2), st>>>(zero, out, tmp, h, w);
   CKL();
   return 0;
 }

@@ -77,7 +77,7 @@ static int morph(Load ld, Post post, uint8_t* dst, int h, int w, int batch, cons
   for (int i = 0; i < se.rows; i++) rx = rx > se.half[i] ? rx : se.half[i];
   size_t sm = (size_t)(MORPH_TW + 2 * rx) * (MORPH_TH + se.rows - 1);
   dim3 grid(cdiv(w, MORPH_TW), cdiv(h, MORPH_TH), batch), blk(32, 8);
-  k_morph<DILATE, Load, Post><<<grid, blk, sm, st>>>(ld, post, dst, h, w, se);
+  VL(), k_morph<DILATE, Load, Post><<<grid, blk, sm, st>>>(ld, post, dst, h, w, se);
   CKL();
   return 0;
 }

@@ -146,15 +146,15 @@ static int select_quantile(Val val, SelectState* st, long long n, int batch, flo
   dim3 grid(gx, batch);
   if (need_count) {
     CK(cudaMemsetAsync(st, 0, sizeof(SelectState) * batch, stream));
-    k_sel_count<Val><<<grid, thr, 0, stream>>>(val, st, n);
+    VL(), k_sel_count<Val><<<grid, thr, 0, stream>>>(val, st, n);
   }
-  k_sel_begin<<<batch, 256, 0, stream>>>(st, q, qv, qstride);
+  VL(), k_sel_begin<<<batch, 256, 0, stream>>>(st, q, qv, qstride);
   for (int shift = 24; shift >= 0; shift -= 8) {
-    k_sel_hist<Val><<<grid, thr, 0, stream>>>(val, st, n, shift);
-    k_sel_pick<<<batch, 256, 0, stream>>>(st, shift);
+    VL(), k_sel_hist<Val><<<grid, thr, 0, stream>>>(val, st, n, shift);
+    VL(), k_sel_pick<<<batch, 256, 0, stream>>>(st, shift);
   }
-  k_sel_neighbour<Val><<<grid, thr, 0, stream>>>(val, st, n);
-  k_sel_finish<<<batch, 1, 0, stream>>>(st, q, qv, qstride);
+  VL(), k_sel_neighbour<Val><<<grid, thr, 0, stream>>>(val, st, n);
+  VL(), k_sel_finish<<<batch, 1, 0, stream>>>(st, q, qv, qstride);
   CKL();
   return 0;
 }

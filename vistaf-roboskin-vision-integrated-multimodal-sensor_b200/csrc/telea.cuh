@@ -386,15 +386,15 @@ static int telea_inpaint(Mask mask, float* img, size_t img_stride, unsigned int*
   telea_ws_carve(ws, h, w, batch, W);
   const int Hp = h + 2, Wp = w + 2, sp = Hp * Wp;
   const int TW = 32 + 2 * range;
-  k_telea_prep<Mask><<<dim3(cdiv(Wp, 32), cdiv(Hp, 32), batch), dim3(32, 8), (size_t)TW * TW + (size_t)TW * 32, st>>>(
+  VL(), k_telea_prep<Mask><<<dim3(cdiv(Wp, 32), cdiv(Hp, 32), batch), dim3(32, 8), (size_t)TW * TW + (size_t)TW * 32, st>>>(
       mask, W.flag, W.T, h, w, range);
   CKL();
   TeleaFg fg{W.flag, (size_t)sp, Wp};
   if (uf_label(fg, EdgeZero(), W.uf, (unsigned int*)nullptr, (unsigned int*)nullptr, 0, Hp, Wp, batch, st)) return 1;
   CK(cudaMemsetAsync(W.fr, 0, sizeof(TeleaFrame) * (size_t)batch, st));
-  k_telea_slots<<<dim3(cdiv(sp, 256), batch), 256, 0, st>>>(W.uf, W.slot, W.fr, W.cl, Hp, Wp);
-  k_telea_bbox<<<dim3(cdiv(sp, 256), batch), 256, 0, st>>>(W.uf, W.slot, W.cl, Hp, Wp);
-  k_telea_march<<<dim3(TL_GRIDX, batch), 32 * TL_WARPS, 0, st>>>(W, img, img_stride, status, status_stride, h, w, range);
+  VL(), k_telea_slots<<<dim3(cdiv(sp, 256), batch), 256, 0, st>>>(W.uf, W.slot, W.fr, W.cl, Hp, Wp);
+  VL(), k_telea_bbox<<<dim3(cdiv(sp, 256), batch), 256, 0, st>>>(W.uf, W.slot, W.cl, Hp, Wp);
+  VL(), k_telea_march<<<dim3(TL_GRIDX, batch), 32 * TL_WARPS, 0, st>>>(W, img, img_stride, status, status_stride, h, w, range);
   CKL();
   return 0;
 }

@@ -799,7 +799,7 @@ extern "C" int vistaf_temp_plan_create(const VistafTempParams* P, VistafTempPlan
   p->se_sat = se_ellipse(P->sat_dilate | 1);
   const size_t npix = (size_t)p->H * p->W;
   CK(cudaMalloc(&p->roi, npix));
-  k_roi_mask<<<dim3(cdiv(p->W, 256), p->H), 256>>>(p->roi, p->H, p->W, P->roi_cx, P->roi_cy, P->roi_r * P->roi_r);
+  VL(), k_roi_mask<<<dim3(cdiv(p->W, 256), p->H), 256>>>(p->roi, p->H, p->W, P->roi_cx, P->roi_cy, P->roi_r * P->roi_r);
   CKL();
   uint8_t* hroi = new uint8_t[npix];
   CK(cudaMemcpy(hroi, p->roi, npix, cudaMemcpyDeviceToHost));
@@ -887,32 +887,38 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   SelectState* sel = (SelectState*)(ws + L.sel);
   const uint8_t* fr = frames + f0 * (size_t)npix * 3;
 
-  k_temp_init<<<cdiv(nb, 128), 128, 0, st>>>(sc, nb);
-  k_temp_gray<<<dim3(cdiv(npix / 4, 256), nb), 256, 0, st>>>(fr, p->roi, gray8, satraw, sc, npix, P.sat_thresh);
-  k_temp_sat_dilate<<<dim3(cdiv(W, 256), H, nb), 256, 0, st>>>(satraw, p->roi, sat, sc, H, W, p->se_sat);
-  k_temp_hist<<<dim3(296, nb), 256, 0, st>>>(gray8, p->roi, sat, sc, npix);
-  k_temp_median<<<nb, 32, 0, st>>>(sc);
+  vistaf_stage_mark("T.gray_sat_median", st);
+  VL(), k_temp_init<<<cdiv(nb, 128), 128, 0, st>>>(sc, nb);
+  VL(), k_temp_gray<<<dim3(cdiv(npix / 4, 256), nb), 256, 0, st>>>(fr, p->roi, gray8, satraw, sc, npix, P.sat_thresh);
+  VL(), k_temp_sat_dilate<<<dim3(cdiv(W, 256), H, nb), 256, 0, st>>>(satraw, p->roi, sat, sc, H, W, p->se_sat);
+  VL(), k_temp_hist<<<dim3(296, nb), 256, 0, st>>>(gray8, p->roi, sat, sc, npix);
+  VL(), k_temp_median<<<nb, 32, 0, st>>>(sc);
   CKL();
+  vistaf_stage_mark("T.illum_blur20", st);
   // illumination normalisation
   IllumLoad il{gray8, p->roi, sc, plane, W};
   IllumStore is{gray8, p->roi, sat, sc, norm, plane, W, 0.0};
   if (gauss_blur(il, is, tmp, H, W, nb, p->g_illum, p->g_illum, st)) return 1;
-  k_temp_mu<<<nb, 1, 0, st>>>(sc);
+  VL(), k_temp_mu<<<nb, 1, 0, st>>>(sc);
+  vistaf_stage_mark("T.fft_rows", st);
   // forward FFT + carrier peak
-  k_temp_fft_rows<<<dim3(cdiv(H, 2), nb), 256, (size_t)W * 16, st>>>(norm, A, sc, p->fw, H, Wh);
-  k_temp_fft_cols_peaks<<<dim3(p->nblk_cols, nb), 512, (size_t)COLS_PER_BLOCK * (H + 1) * 16, st>>>(A, cand, p->fh, W, Wh,
+  VL(), k_temp_fft_rows<<<dim3(cdiv(H, 2), nb), 256, (size_t)W * 16, st>>>(norm, A, sc, p->fw, H, Wh);
+  vistaf_stage_mark("T.fft_cols_peaks", st);
+  VL(), k_temp_fft_cols_peaks<<<dim3(p->nblk_cols, nb), 512, (size_t)COLS_PER_BLOCK * (H + 1) * 16, st>>>(A, cand, p->fh, W, Wh,
                                                                                                   P.dc_exclusion);
   const int ncand = p->nblk_cols * TOPK;
-  k_temp_peak_select<<<nb, 256, (size_t)2 * ncand * 4, st>>>(cand, sc, ncand, H, W, P.dc_exclusion, P.peak_max_dy_frac);
+  VL(), k_temp_peak_select<<<nb, 256, (size_t)2 * ncand * 4, st>>>(cand, sc, ncand, H, W, P.dc_exclusion, P.peak_max_dy_frac);
   CKL();
+  vistaf_stage_mark("T.band_ifft", st);
   // band-pass + inverse
   const int R = P.band_radius, nbnd = 2 * R + 1;
-  k_temp_band<<<dim3(nbnd, nb), 256, (size_t)H * 8, st>>>(A, G, sc, p->fh, W, Wh, R);
+  VL(), k_temp_band<<<dim3(nbnd, nb), 256, (size_t)H * 8, st>>>(A, G, sc, p->fh, W, Wh, R);
   const int nrows = p->y1 - p->y0;
-  k_temp_ifft_rows<1><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R);
-  k_temp_ifft_rows<2><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R);
-  k_temp_choose_dark<<<nb, 1, 0, st>>>(sc);
+  VL(), k_temp_ifft_rows<1><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R);
+  VL(), k_temp_ifft_rows<2><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R);
+  VL(), k_temp_choose_dark<<<nb, 1, 0, st>>>(sc);
   CKL();
+  vistaf_stage_mark("T.morph_close_open", st);
   // close RECT(kx x ky) then open RECT(kx x ky), then & roi_eff  (temperature_sensor.py:390-406, 490)
   DarkLoad dl{maskA, p->roi, sat, sc, plane, W, p->y0, p->y1};
   MorphSE se_c = se_rect(P.close_kx | 1, P.close_ky | 1), se_o = se_rect(P.open_kx | 1, P.open_ky | 1);
@@ -921,6 +927,7 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   if (morph<false>(MaskLoad{m1, plane, W}, PostId(), m2, H, W, nb, se_c, st)) return 1;
   if (morph<false>(MaskLoad{m2, plane, W}, PostId(), m1, H, W, nb, se_o, st)) return 1;
   if (morph<true>(MaskLoad{m1, plane, W}, PostRoiEff{p->roi, sat, sc, plane, W}, dark, H, W, nb, se_o, st)) return 1;
+  vistaf_stage_mark("T.features_models_fuse", st);
   // features, models, fusion
   FeatArgs fa;
   fa.frames = fr; fa.roi = p->roi; fa.sat = sat; fa.dark = dark; fa.sc = sc;
@@ -936,17 +943,20 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   fa.ok_lo = P.color_t_min - P.guard_band; fa.ok_hi = P.color_t_max + P.guard_band;
   fa.blend_lo = P.color_t_max - P.switch_margin; fa.blend_hi = P.color_t_max + P.switch_margin;
   fa.final_lo = P.final_t_min; fa.final_hi = P.final_t_max; fa.chroma_min = P.chroma_min;
-  k_temp_features<<<dim3(cdiv(W, FT_W), cdiv(H, FT_H), nb), dim3(FT_W, FT_H), 0, st>>>(fa);
+  VL(), k_temp_features<<<dim3(cdiv(W, FT_W), cdiv(H, FT_H), nb), dim3(FT_W, FT_H), 0, st>>>(fa);
   CKL();
+  vistaf_stage_mark("T.final_blur", st);
   // oriented smoothing (axis aligned) + statistics
   float* fin = O.final_map + f0 * (size_t)npix;
   FusedLoad fl{fa.fused, plane, W};
   FinalStore fs{p->roi, fin, sc, plane, W, P.final_t_min, P.final_t_max, 0.0, 0.0, 3.0e38f, 0.f, 0u};
   if (gauss_blur(fl, fs, tmp, H, W, nb, p->g_across, p->g_along, st)) return 1;
+  vistaf_stage_mark("T.stats_median", st);
   FinalVal fv{fin, p->roi, plane};
   if (select_quantile(fv, sel, (long long)npix, nb, -1.0f, true, st)) return 1;
-  k_temp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, sel, O.records + f0, nb, W / 2, H / 2);
+  VL(), k_temp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, sel, O.records + f0, nb, W / 2, H / 2);
   CKL();
+  vistaf_stage_mark("", st);
   return 0;
 }
 

@@ -100,6 +100,7 @@ def bbox_from_mask(mask: np.ndarray, pad: int = 0) -> Tuple[int, int, int, int]:
 
 # ---------------------------------------------------------------- plan cache
 _PLANS = {}
+LAST_RECORD = None       # VistafTempRecord of the most recent main() (statistics reduced on the device, M1)
 MASK_NAMES = ("sat", "dark", "light", "color_support", "color_ok", "source")
 
 
@@ -206,6 +207,7 @@ def run_batch(frames_bgr, chunk: int = 8, masks: bool = True) -> dict:
 
 # ---------------------------------------------------------------- reference-compatible entry point
 def main() -> None:
+    global LAST_RECORD
     import cv2
     os.makedirs(OUTPUT_DIR, exist_ok=True)
     if not os.path.exists(INPUT_IMAGE_PATH):
@@ -218,6 +220,7 @@ def main() -> None:
     crop_bbox = bbox_from_mask(roi_outer, pad=int(CROP_PAD_PX)) if bool(CROP_OUTPUT_TO_OUTER_ROI) else (0, h, 0, w)
     out = run_batch(img[None], chunk=1, masks=True)
     rec = out["records_np"][0]
+    LAST_RECORD = rec
     if rec["status"] & N.ST_EMPTY_ROI:
         raise RuntimeError("ROI became empty after saturation exclusion. Lower SAT_THRESH_GRAY / dilation.")
     if rec["status"] & N.ST_NO_PEAK:
