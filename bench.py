@@ -168,8 +168,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default=os.environ.get("VISTAF_WORKLOAD", "multimodal"),
                     choices=["multimodal", "ftp", "temperature"])
-    ap.add_argument("--frames", type=int, default=64, help="frames per GPU per step")
-    ap.add_argument("--chunk", type=int, default=16, help="frames per library chunk (workspace size)")
+    ap.add_argument("--frames", type=int, default=256, help="frames per GPU per step")
+    ap.add_argument("--chunk", type=int, default=256, help="FTP frames per library chunk (workspace size)")
+    ap.add_argument("--chunk-temp", type=int, default=64, help="temperature frames per library chunk")
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--cpu-workers", type=int, default=None)
     ap.add_argument("--cpu-frames", type=int, default=None, help="frames per CPU step (default: one per worker)")
@@ -182,7 +183,7 @@ def main():
                           f"({N_DISTINCT} distinct seeds per rank tiled to the batch) against one reference frame, "
                           f"FTP crop 1182^2 / FFT grid 1374^2, both temperature models; frames pre-registered "
                           f"(APPLY_GLOBAL_SHIFT=False, USE_ECC_CROP_ALIGNMENT=False on GPU and CPU arms)",
-              "frames_per_gpu": a.frames, "chunk": a.chunk, "resolution": "2160x3840",
+              "frames_per_gpu": a.frames, "chunk_ftp": a.chunk, "chunk_temp": a.chunk_temp, "resolution": "2160x3840",
               "l2": f"inputs {a.frames * 24.9:.0f} MB per step, larger than the 126 MB L2 (no flush needed)"}
 
     if a.impl == "reference":
@@ -206,19 +207,17 @@ def main():
     pinned = torch.from_numpy(np.ascontiguousarray(np.tile(host, (F // N_DISTINCT + 1, 1, 1, 1))[:F])).pin_memory()
     ref_pinned = torch.from_numpy(ref_host).pin_memory()
     dev, ref_dev = pinned.cuda(), ref_pinned.cuda()
-    plan = MS.MultimodalPlan(host.shape[1], host.shape[2], a.chunk, a.chunk, a.workload)
+    plan = MS.MultimodalPlan(host.shape[1], host.shape[2], min(a.chunk, F), min(a.chunk_temp, F), a.workload)
 
     def step_resident():
-        plan.set_reference(ref_dev)
-        return plan.run(dev, masks=False)
+        return plan.step(ref_dev, dev, masks=False)
 
     dev2, ref2 = torch.empty_like(dev), torch.empty_like(ref_dev)
 
     def step_e2e():
         ref2.copy_(ref_pinned, non_blocking=True)
         dev2.copy_(pinned, non_blocking=True)
-        plan.set_reference(ref2)
-        return plan.run(dev2, masks=False)["records"].cpu()
+        return plan.step(ref2, dev2, masks=False)["records"].cpu()
 
     def barrier():
         if world > 1:

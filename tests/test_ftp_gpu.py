@@ -55,15 +55,26 @@ def _oracle(mods, syn_ref, frame):
 
 def _compare(out, i, o, fr):
     rec = out["records_np"][i]
-    for k in MASKS:
-        g = out[k][i].cpu().numpy().astype(bool)
-        assert int((g != o[k]).sum()) == 0, f"mask {k} differs"
     hm = out["height_mm"][i].cpu().numpy()
     np.testing.assert_array_equal(np.isnan(hm), np.isnan(o["height_mm"]))
     assert float(np.nanmax(np.abs(hm - o["height_mm"]))) <= TOL_MM
+    for k in MASKS:
+        g = out[k][i].cpu().numpy().astype(bool)
+        diff = g != o[k]
+        if k == "contact_kept":
+            # contact_kept is the SIGN of a float field (depth_mm > 0 inside kept blobs, shape_ftp.py:1244): along its
+            # zero contour the two sides may differ by float rounding.  Every differing pixel must be such a pixel
+            # (|depth| below the stated height tolerance on both sides), and there must be next to none of them.
+            z = np.maximum(np.abs(np.nan_to_num(hm)), np.abs(np.nan_to_num(o["height_mm"])))
+            assert not (diff & (z > TOL_MM)).any(), "contact_kept differs away from the zero contour"
+            assert int(diff.sum()) <= 1e-4 * max(1, int(o[k].sum())), f"{int(diff.sum())} sign flips on the zero contour"
+        else:
+            assert int(diff.sum()) == 0, f"mask {k} differs"
     assert float(rec["force_N"]) == pytest.approx(fr["force_N"], rel=TOL_FORCE)
     assert float(rec["volume_cm3"]) == pytest.approx(fr["volume_cm3"], rel=TOL_FORCE)
-    assert float(rec["contact_area_mm2"]) == pytest.approx(fr["contact_area_mm2"], rel=1e-9)
+    # area = (number of pixels with depth > 0.01 mm) x pixel area: pixels whose depth is within float rounding of the
+    # 0.01 mm threshold may fall either side, so the count is held to 1e-4 relative (a handful of pixels), not to 0
+    assert float(rec["contact_area_mm2"]) == pytest.approx(fr["contact_area_mm2"], rel=1e-4)
     assert float(rec["max_depth_mm"]) == pytest.approx(fr["max_depth_mm"], abs=TOL_MM)
     assert float(rec["mm_per_px"]) == pytest.approx(fr["scale_mm_per_px"], rel=1e-6)
     assert int(rec["reliable_px"]) == int(o["reliable"].sum())
@@ -187,3 +198,26 @@ def test_errors_are_loud(mods, tmp_path):
     plan = SF.FtpPlan(2160, 3840, chunk=1)
     with pytest.raises(RuntimeError):
         plan.run(torch.zeros((1, plan.h, plan.w), dtype=torch.uint8, device="cuda"))      # no reference set
+
+
+@pytest.mark.parametrize("seed", [15, 7])
+def test_telea_inpaint_bit_exact(mods, syn_ref, seed):
+    """F2/F3: the bad-pixel mask and the Telea fill (cluster march with the warp heap) equal cv2.inpaint's result bit
+    for bit — OpenCV's global (T, insertion order) processing order is reproduced inside every independent cluster."""
+    import torch
+    S, SF, FO = mods
+    import cv2
+    ref, P, geom, rg, refp = syn_ref
+    fr = S.make_frame(seed)
+    dg = cv2.cvtColor(fr[geom["y1"]:geom["y2"], geom["x1"]:geom["x2"]], cv2.COLOR_BGR2GRAY)
+    o = FO.ftp_pair(rg, dg, geom, P, ref=refp, keep=True)
+    plan = SF.FtpPlan(ref.shape[0], ref.shape[1], chunk=1)
+    plan.set_reference(torch.from_numpy(rg).cuda())
+    plan.run(torch.from_numpy(dg)[None].cuda(), masks=False)
+    torch.cuda.synchronize()
+    h, w = plan.h, plan.w
+    bad = plan.workspace_plane("bad", 1).cpu().numpy().reshape(h, w) > 0
+    img = plan.workspace_plane("img", 1).cpu().numpy().view(np.float32).reshape(h, w)
+    assert int((bad != o["bad_def"]).sum()) == 0
+    assert int(bad.sum()) > 1000
+    np.testing.assert_array_equal(img, o["img_inp_def"])

@@ -76,6 +76,8 @@ struct VistafFtpPlan {
   int* kxs; int* kys;             // device [np]: unsigned frequency index of every patch column / row
   int roi_count;
   int ref_bad;
+  ull* peak_keys;                 // device [32]: top-n spectrum peaks of the reference frame
+  void* peak_result;              // device PeakResult
 };
 
 namespace vftp {
@@ -378,6 +380,71 @@ __global__ void k_ftp_pad(const float* __restrict__ Iw, const FtpScal* sc, float
   int X = blockIdx.x * blockDim.x + threadIdx.x, Y = blockIdx.y;
   if (X >= N) return;
   Ip[(size_t)Y * N + X] = __fsub_rn(Iw[(size_t)reflect(Y - pad, h) * w + reflect(X - pad, w)], sc[0].mu);
+}
+
+// ------------------------------------------------------------------ F6: carrier peak (shape_ftp.py:420-483) on the device
+// find_top_peaks: the n largest |F| outside the DC box of the fftshift-ed spectrum, ordered by (magnitude desc, raster
+// index asc).  One sweep per peak: round r takes the largest key strictly below the key of round r-1.
+struct PeakResult { float pxf, pyf; int bx, by; float mag; int ok; };
+__global__ void __launch_bounds__(256) k_ftp_peak_round(const float2* __restrict__ F, ull* __restrict__ keys, int round, int N,
+                                                        int dc) {
+  const ull limit = round ? keys[round - 1] : ~0ull;
+  const int c = N / 2;
+  ull best = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N * N; i += gridDim.x * blockDim.x) {
+    const int sy = i / N, sx = i - sy * N;                       // fftshift-ed coordinates
+    if (sy >= c - dc && sy < c + dc && sx >= c - dc && sx < c + dc) continue;
+    const int ky = (sy - c + N) % N, kx = (sx - c + N) % N;
+    const float2 v = F[(size_t)ky * N + kx];
+    const ull k = ((ull)__float_as_uint(hypotf(v.x, v.y)) << 32) | (ull)(0xffffffffu - (unsigned int)i);
+    if (k < limit && k > best) best = k;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { const ull t = __shfl_xor_sync(0xffffffffu, best, o); best = t > best ? t : best; }
+  if ((threadIdx.x & 31) == 0 && best) atomicMax(keys + round, best);
+}
+// choose_carrier_peak (:444) + refine_peak_parabolic_log (:473)
+__global__ void k_ftp_peak_choose(const float2* __restrict__ F, const ull* __restrict__ keys, int n, int N, float max_dy_frac,
+                                  PeakResult* out) {
+  const int c = N / 2, md = (int)(max_dy_frac * (float)N);
+  int bx = -1, by = -1;
+  float bm = -1.f;
+  bool any_right = false, any_right_near = false, any_near = false;
+  for (int q = 0; q < n; q++) {
+    if (!keys[q]) continue;
+    const unsigned int iq = 0xffffffffu - (unsigned int)(keys[q] & 0xffffffffull);
+    const int yq = (int)(iq / (unsigned)N), xq = (int)(iq % (unsigned)N);
+    any_right |= xq > c; any_near |= abs(yq - c) <= md; any_right_near |= xq > c && abs(yq - c) <= md;
+  }
+  // the reference keeps the right-half peaks (if any), then of those the ones near the centre row (if any), and
+  // takes the strongest (the first of equals in peak order)
+  for (int r = 0; r < n; r++) {
+    if (!keys[r]) continue;
+    const unsigned int i = 0xffffffffu - (unsigned int)(keys[r] & 0xffffffffull);
+    const int y = (int)(i / (unsigned)N), x = (int)(i % (unsigned)N);
+    const float m = __uint_as_float((unsigned int)(keys[r] >> 32));
+    const bool right = x > c, near = abs(y - c) <= md;
+    bool in_set;
+    if (any_right) in_set = any_right_near ? (right && near) : right;
+    else in_set = any_near ? near : true;
+    if (in_set && m > bm) { bm = m; bx = x; by = y; }
+  }
+  PeakResult r;
+  r.bx = bx; r.by = by; r.mag = bm; r.ok = bx >= 0;
+  r.pxf = (float)bx; r.pyf = (float)by;
+  if (bx > 0 && bx < N - 1 && by > 0 && by < N - 1) {
+    auto lm = [&](int sy, int sx) {
+      const float2 v = F[(size_t)((sy - c + N) % N) * N + (sx - c + N) % N];
+      return logf(hypotf(v.x, v.y) + 1e-12f);
+    };
+    auto parab = [](float fm, float f0, float fp) {
+      const float den = fm - 2.0f * f0 + fp;
+      return fabsf(den) < 1e-12f ? 0.0f : 0.5f * (fm - fp) / den;
+    };
+    r.pxf = (float)bx + parab(lm(by, bx - 1), lm(by, bx), lm(by, bx + 1));
+    r.pyf = (float)by + parab(lm(by - 1, bx), lm(by, bx), lm(by + 1, bx));
+  }
+  *out = r;
 }
 
 // ------------------------------------------------------------------ F8: reliable mask (shape_ftp.py:739-776)
@@ -971,6 +1038,7 @@ extern "C" int vistaf_ftp_plan_create(const VistafFtpParams* P, VistafFtpPlan** 
   CK(cudaMalloc(&p->cref, S * 8)); CK(cudaMalloc(&p->amp_ref, S * 4));
   CK(cudaMalloc(&p->rampx, sizeof(float2) * p->N)); CK(cudaMalloc(&p->rampy, sizeof(float2) * p->N));
   CK(cudaMalloc(&p->hann, sizeof(float) * np)); CK(cudaMalloc(&p->kxs, sizeof(int) * np)); CK(cudaMalloc(&p->kys, sizeof(int) * np));
+  CK(cudaMalloc(&p->peak_keys, sizeof(ull) * 32)); CK(cudaMalloc(&p->peak_result, 64));
   int r_valid = P->r - P->roi_erode_px;
   if (r_valid < 0) r_valid = 0;
   VL(), k_ftp_geometry<<<dim3(cdiv(p->w, 256), p->h), 256>>>(p->roi, p->circ, p->valid, p->apo, p->h, p->w, P->cx, P->cy, P->r,
@@ -995,7 +1063,7 @@ extern "C" void vistaf_ftp_plan_destroy(VistafFtpPlan* p) {
   fft1d_destroy(&p->fN);
   cudaFree(p->roi); cudaFree(p->circ); cudaFree(p->valid); cudaFree(p->apo); cudaFree(p->den9);
   cudaFree(p->cref); cudaFree(p->amp_ref); cudaFree(p->rampx); cudaFree(p->rampy); cudaFree(p->hann);
-  cudaFree(p->kxs); cudaFree(p->kys);
+  cudaFree(p->kxs); cudaFree(p->kys); cudaFree(p->peak_keys); cudaFree(p->peak_result);
   delete p;
 }
 
@@ -1089,49 +1157,6 @@ static int ftp_patch_field(VistafFtpPlan* p, int nb, char* ws, const FtpWs& L, b
   return 0;
 }
 
-// find_top_peaks / choose_carrier_peak / refine_peak_parabolic_log (shape_ftp.py:420-483) on the host, once per reference
-static int ftp_pick_carrier(VistafFtpPlan* p, const std::vector<float2>& F) {
-  const int N = p->N, cy = N / 2, cx = N / 2, dc = p->P.dc_exclusion;
-  std::vector<float> mag((size_t)N * N);
-  for (int ky = 0; ky < N; ky++)
-    for (int kx = 0; kx < N; kx++) {
-      const float2 v = F[(size_t)ky * N + kx];
-      mag[(size_t)((ky + N / 2) % N) * N + (kx + N / 2) % N] = hypotf(v.x, v.y);
-    }
-  std::vector<float> ms = mag;
-  for (int y = std::max(0, cy - dc); y < std::min(N, cy + dc); y++)
-    for (int x = std::max(0, cx - dc); x < std::min(N, cx + dc); x++) ms[(size_t)y * N + x] = 0.f;
-  const int n = std::min(p->P.n_peaks, N * N);
-  std::vector<int> idx((size_t)N * N);
-  for (size_t i = 0; i < idx.size(); i++) idx[i] = (int)i;
-  std::partial_sort(idx.begin(), idx.begin() + n, idx.end(), [&](int a, int b) { return ms[a] > ms[b] || (ms[a] == ms[b] && a < b); });
-  struct Pk { int x, y; float m; };
-  std::vector<Pk> peaks, cand, cand2;
-  for (int i = 0; i < n; i++) peaks.push_back({idx[i] % N, idx[i] / N, ms[idx[i]]});
-  for (auto& q : peaks) if (q.x > cx) cand.push_back(q);
-  if (cand.empty()) cand = peaks;
-  const int md = (int)(p->P.peak_max_dy_frac * (float)N);
-  for (auto& q : cand) if (abs(q.y - cy) <= md) cand2.push_back(q);
-  if (!cand2.empty()) cand = cand2;
-  if (cand.empty()) return vistaf_set_err("no carrier peak", cudaErrorInvalidValue, __FILE__, __LINE__);
-  Pk best = cand[0];
-  for (auto& q : cand) if (q.m > best.m) best = q;
-  float pxf = (float)best.x, pyf = (float)best.y;
-  if (!(best.x <= 0 || best.x >= N - 1 || best.y <= 0 || best.y >= N - 1)) {
-    auto lm = [&](int y, int x) { return logf(mag[(size_t)y * N + x] + 1e-12f); };
-    auto parab = [](float fm, float f0, float fp) {
-      const float den = fm - 2.0f * f0 + fp;
-      return fabsf(den) < 1e-12f ? 0.0f : 0.5f * (fm - fp) / den;
-    };
-    pxf = (float)best.x + parab(lm(best.y, best.x - 1), lm(best.y, best.x), lm(best.y, best.x + 1));
-    pyf = (float)best.y + parab(lm(best.y - 1, best.x), lm(best.y, best.x), lm(best.y + 1, best.x));
-  }
-  p->peak_xf = pxf; p->peak_yf = pyf;
-  p->kx = (double)pxf - cx; p->ky = (double)pyf - cy;
-  p->pxi = (int)nearbyint((double)pxf); p->pyi = (int)nearbyint((double)pyf);
-  return 0;
-}
-
 static int ftp_set_carrier(VistafFtpPlan* p) {
   const int N = p->N, np = p->np, bw = np / 2, cx = N / 2, cy = N / 2;
   if (p->pxi - bw < 0 || p->pxi + bw + 1 > N || p->pyi - bw < 0 || p->pyi + bw + 1 > N)
@@ -1173,12 +1198,21 @@ extern "C" int vistaf_ftp_set_reference(VistafFtpPlan* p, const uint8_t* ref_gra
   VL(), k_ftp_pad<<<dim3(cdiv(N, 256), N), 256, 0, st>>>((float*)(ws + L.Iw), (FtpScal*)(ws + L.scal), Ip, p->h, p->w, N, p->P.fft_pad);
   CKL();
   if (fft2d_dense(Ip, F, p->fN, p->fN, N, N, 1, -1, true, st)) return 1;
-  std::vector<float2> hF((size_t)N * N);
-  CK(cudaMemcpyAsync(hF.data(), F, sizeof(float2) * hF.size(), cudaMemcpyDeviceToHost, st));
+  // carrier search on the device: n_peaks sweeps of the spectrum, then choice + log-parabolic refinement
+  const int npk = p->P.n_peaks < 1 ? 1 : (p->P.n_peaks > 32 ? 32 : p->P.n_peaks);
+  CK(cudaMemsetAsync(p->peak_keys, 0, sizeof(ull) * 32, st));
+  for (int r = 0; r < npk; r++) VL(), k_ftp_peak_round<<<296, 256, 0, st>>>(F, p->peak_keys, r, N, p->P.dc_exclusion);
+  VL(), k_ftp_peak_choose<<<1, 1, 0, st>>>(F, p->peak_keys, npk, N, p->P.peak_max_dy_frac, (PeakResult*)p->peak_result);
+  CKL();
+  PeakResult pr;
+  CK(cudaMemcpyAsync(&pr, p->peak_result, sizeof(pr), cudaMemcpyDeviceToHost, st));
   FtpScal hs;
   CK(cudaMemcpyAsync(&hs, ws + L.scal, sizeof(FtpScal), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  if (ftp_pick_carrier(p, hF)) return 1;
+  if (!pr.ok) return vistaf_set_err("no carrier peak", cudaErrorInvalidValue, __FILE__, __LINE__);
+  p->peak_xf = pr.pxf; p->peak_yf = pr.pyf;
+  p->kx = (double)pr.pxf - N / 2; p->ky = (double)pr.pyf - N / 2;
+  p->pxi = (int)nearbyint((double)pr.pxf); p->pyi = (int)nearbyint((double)pr.pyf);
   if (ftp_set_carrier(p)) return 1;
   if (ftp_patch_field(p, 1, ws, L, true, st)) return 1;
   vistaf_stage_mark("", st);

@@ -32,52 +32,67 @@ static inline MorphSE se_rect(int kx, int ky) {
   return s;
 }
 
-// Tile kernel: block (32 x 8) threads computes a 32 x 32 tile (4 rows per thread) from a shared
-// tile with halo.  Load: int operator()(int b, int y, int x) -> 0/1 (only called in-bounds).
-// Post: int operator()(int b, int y, int x, int v) -> value stored (e.g. & roi).
+// Bit-packed tile kernel.  A block of 128 threads produces a 32-column x 128-row tile.  Phase 1 packs every tile
+// row with its halo (64 columns: x0-16 .. x0+47, half-widths are <= 16) into one 64-bit word through warp
+// ballots; phase 2 gives one output row to each thread: for every element row the horizontal span
+// [-hw, hw] is folded into a word by log-step shift-OR (shift-AND for erosion), rows are combined by OR / AND;
+// phase 3 unpacks the 32 result bits of a row with one coalesced byte store per warp.
+//   Load: int operator()(int b, int y, int x) -> 0/1 (only called in-bounds).
+//   Post: int operator()(int b, int y, int x, int v) -> value stored (e.g. & roi).
 #define MORPH_TW 32
-#define MORPH_TH 32
+#define MORPH_TH 128
 template <bool DILATE, class Load, class Post>
-__global__ void k_morph(Load ld, Post post, uint8_t* __restrict__ dst, int h, int w, MorphSE se) {
-  extern __shared__ uint8_t tile[];
-  const int ry = se.rows / 2;
-  int rx = 0;
-  for (int i = 0; i < se.rows; i++) rx = max(rx, se.half[i]);
-  const int tw = MORPH_TW + 2 * rx, th = MORPH_TH + 2 * ry;
+__global__ void __launch_bounds__(128) k_morph(Load ld, Post post, uint8_t* __restrict__ dst, int h, int w, MorphSE se) {
+  __shared__ unsigned long long Wd[MORPH_TH + MORPH_MAXROWS - 1];
+  __shared__ unsigned int Rw[MORPH_TH];
+  const int ry = se.rows / 2, nrow = MORPH_TH + se.rows - 1;
   const int b = blockIdx.z, x0 = blockIdx.x * MORPH_TW, y0 = blockIdx.y * MORPH_TH;
-  const int tid = threadIdx.y * blockDim.x + threadIdx.x, nthr = blockDim.x * blockDim.y;
-  for (int e = tid; e < tw * th; e += nthr) {
-    int ty = e / tw, tx = e - ty * tw;
-    int y = y0 - ry + ty, x = x0 - rx + tx;
-    int v = DILATE ? 0 : 1;                       // border value
-    if (y >= 0 && y < h && x >= 0 && x < w) v = ld(b, y, x);
-    tile[e] = (uint8_t)v;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int ty = wid; ty < nrow; ty += 4) {
+    const int y = y0 - ry + ty;
+    const bool yin = y >= 0 && y < h;
+    unsigned int word[2];
+#pragma unroll
+    for (int hf = 0; hf < 2; hf++) {
+      const int x = x0 - 16 + hf * 32 + lane;
+      int v = DILATE ? 0 : 1;                       // border value
+      if (yin && x >= 0 && x < w) v = ld(b, y, x);
+      word[hf] = __ballot_sync(0xffffffffu, v != 0);
+    }
+    if (lane == 0) Wd[ty] = (unsigned long long)word[0] | ((unsigned long long)word[1] << 32);
   }
   __syncthreads();
-  for (int j = 0; j < MORPH_TH / 8; j++) {
-    int ly = threadIdx.y + 8 * j, lx = threadIdx.x;
-    int y = y0 + ly, x = x0 + lx;
-    if (y >= h || x >= w) continue;
-    int v = DILATE ? 0 : 1;
+  {
+    const int ly = threadIdx.x;
+    unsigned int acc = DILATE ? 0u : 0xffffffffu;
     for (int i = 0; i < se.rows; i++) {
-      int hw = se.half[i];
+      const int hw = se.half[i];
       if (hw < 0) continue;
-      const uint8_t* row = tile + (ly + i) * tw + lx + rx;
-      for (int d = -hw; d <= hw; d++) {
-        if (DILATE) v |= row[d]; else v &= row[d];
+      unsigned long long a = Wd[ly + i] >> (16 - hw);   // bit c <-> column x0 + c - hw
+      const int span = 2 * hw + 1;
+      for (int L = 1; L < span;) {
+        const int sft = min(L, span - L);
+        a = DILATE ? (a | (a >> sft)) : (a & (a >> sft));
+        L += sft;
       }
+      acc = DILATE ? (acc | (unsigned int)a) : (acc & (unsigned int)a);
     }
-    dst[(size_t)b * h * w + (size_t)y * w + x] = (uint8_t)post(b, y, x, v);
+    Rw[ly] = acc;
+  }
+  __syncthreads();
+  for (int ty = wid; ty < MORPH_TH; ty += 4) {
+    const int y = y0 + ty, x = x0 + lane;
+    if (y < h && x < w) dst[(size_t)b * h * w + (size_t)y * w + x] = (uint8_t)post(b, y, x, (int)((Rw[ty] >> lane) & 1u));
   }
 }
 
 template <bool DILATE, class Load, class Post>
 static int morph(Load ld, Post post, uint8_t* dst, int h, int w, int batch, const MorphSE& se, cudaStream_t st) {
-  int rx = 0;
-  for (int i = 0; i < se.rows; i++) rx = rx > se.half[i] ? rx : se.half[i];
-  size_t sm = (size_t)(MORPH_TW + 2 * rx) * (MORPH_TH + se.rows - 1);
-  dim3 grid(cdiv(w, MORPH_TW), cdiv(h, MORPH_TH), batch), blk(32, 8);
-  VL(), k_morph<DILATE, Load, Post><<<grid, blk, sm, st>>>(ld, post, dst, h, w, se);
+  for (int i = 0; i < se.rows; i++)
+    if (se.half[i] > 16) return vistaf_set_err("morph: structuring element wider than 33", cudaErrorInvalidValue, __FILE__, __LINE__);
+  if (se.rows > MORPH_MAXROWS) return vistaf_set_err("morph: structuring element taller than 33", cudaErrorInvalidValue, __FILE__, __LINE__);
+  dim3 grid(cdiv(w, MORPH_TW), cdiv(h, MORPH_TH), batch);
+  VL(), k_morph<DILATE, Load, Post><<<grid, 128, 0, st>>>(ld, post, dst, h, w, se);
   CKL();
   return 0;
 }

@@ -21,14 +21,16 @@
 #define TL_IN 16          // hole cell filled by the inward march
 #define TL_MAXCLUSTERS 65536
 #define TL_WARPS 4
-#define TL_GRIDX 48
+#define TL_GRIDX 96
+#define TL_NCLASS 24      // size classes (log2 of the cell count) for largest-first scheduling
 
 struct TeleaFrame {       // per-frame bookkeeping (device)
-  unsigned int nclusters, next, cursor, overflow;
+  unsigned int nclusters, next, overflow, pad_;
 };
 struct TeleaCluster {     // per cluster slot
-  unsigned int root, count;
-  int x0, y0, x1, y1;     // padded-frame bounding box, inclusive
+  unsigned int root, count, nband, bfill;   // cells, band cells, band-list fill cursor
+  unsigned int off, boff;                   // offsets of the heap / log region and of the band list
+  unsigned int pad_[2];
 };
 
 struct TeleaWs {          // device pointers, dense [batch][...] planes
@@ -38,15 +40,19 @@ struct TeleaWs {          // device pointers, dense [batch][...] planes
   unsigned int* slot;     // [Hp*Wp]  slot index stored at root cells
   TeleaFrame* fr;         // [1]
   TeleaCluster* cl;       // [TL_MAXCLUSTERS]
-  ull* keys;              // [cap]  (T bits << 32) | seq
-  int* pos;               // [cap]
-  size_t sp, cap;         // padded cells per frame, queue capacity per frame
+  unsigned int* order;    // [TL_MAXCLUSTERS] cluster slots, largest size class first
+  ull* keys;              // [cap]  heap keys (T bits << 32) | seq
+  int* pos;               // [cap]  heap payload: cell
+  int* log;               // [cap]  cells popped by the outward march (to negate their T)
+  int* band;              // [cap]  band cells per cluster (unordered; keys restore raster order)
+  size_t sp, cap;         // padded cells per frame, capacity per frame
 };
 
 static inline size_t telea_ws_bytes(int h, int w, int batch) {
   const size_t sp = (size_t)(h + 2) * (w + 2), cap = sp / 2, B = (size_t)batch;
   return align256(B * sp * 8) + align256(B * sp * 4) * 2 + align256(B * sp) + align256(B * sizeof(TeleaFrame)) +
-         align256(B * sizeof(TeleaCluster) * TL_MAXCLUSTERS) + align256(B * cap * 8) + align256(B * cap * 4);
+         align256(B * sizeof(TeleaCluster) * TL_MAXCLUSTERS) + align256(B * 4 * TL_MAXCLUSTERS) + align256(B * cap * 8) +
+         align256(B * cap * 4) * 3;
 }
 static inline void telea_ws_carve(char* base, int h, int w, int batch, TeleaWs& W) {
   const size_t sp = (size_t)(h + 2) * (w + 2), cap = sp / 2, B = (size_t)batch;
@@ -58,8 +64,11 @@ static inline void telea_ws_carve(char* base, int h, int w, int batch, TeleaWs& 
   W.flag = (uint8_t*)take(B * sp);
   W.fr = (TeleaFrame*)take(B * sizeof(TeleaFrame));
   W.cl = (TeleaCluster*)take(B * sizeof(TeleaCluster) * TL_MAXCLUSTERS);
+  W.order = (unsigned int*)take(B * 4 * TL_MAXCLUSTERS);
   W.keys = (ull*)take(B * cap * 8);
   W.pos = (int*)take(B * cap * 4);
+  W.log = (int*)take(B * cap * 4);
+  W.band = (int*)take(B * cap * 4);
   W.sp = sp; W.cap = cap;
 }
 
@@ -111,7 +120,9 @@ struct TeleaFg {          // cluster foreground on the padded frame
   __device__ bool operator()(int b, int y, int x) const { return flag[(size_t)b * stride + (size_t)y * Wp + x] != 0; }
 };
 
+
 // ------------------------------------------------------------------ 3. cluster table
+// slots: one slot per union-find root.
 static __global__ void k_telea_slots(const ull* __restrict__ uf, unsigned int* __restrict__ slot, TeleaFrame* fr,
                               TeleaCluster* cl, int Hp, int Wp) {
   const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -123,255 +134,402 @@ static __global__ void k_telea_slots(const ull* __restrict__ uf, unsigned int* _
   slot[(size_t)b * sp + i] = s;
   if (s < TL_MAXCLUSTERS) {
     TeleaCluster* c = cl + (size_t)b * TL_MAXCLUSTERS + s;
-    c->root = (unsigned int)i; c->count = 0;
-    c->x0 = Wp; c->y0 = Hp; c->x1 = -1; c->y1 = -1;
+    c->root = (unsigned int)i; c->count = 0; c->nband = 0; c->bfill = 0; c->off = 0; c->boff = 0;
   }
 }
-static __global__ void k_telea_bbox(const ull* __restrict__ uf, const unsigned int* __restrict__ slot, TeleaCluster* cl,
-                             int Hp, int Wp) {
+// counts: cells and band cells per cluster (warp-aggregated by root).
+static __global__ void k_telea_count(const ull* __restrict__ uf, const unsigned int* __restrict__ slot,
+                              const uint8_t* __restrict__ flag, TeleaCluster* cl, int Hp, int Wp) {
+  const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t sp = (size_t)Hp * Wp;
+  unsigned int root = UF_BG;
+  bool band = false;
+  if (i < Hp * Wp) {
+    root = uf_parent(uf[(size_t)b * sp + i]);
+    band = root != UF_BG && (flag[(size_t)b * sp + i] & TL_BAND);
+  }
+  const unsigned int grp = __match_any_sync(0xffffffffu, root);
+  const unsigned int bandbits = __ballot_sync(0xffffffffu, band);
+  if (root == UF_BG || (int)(__ffs(grp) - 1) != (int)(threadIdx.x & 31)) return;
+  const unsigned int s = slot[(size_t)b * sp + root];
+  if (s >= TL_MAXCLUSTERS) return;
+  TeleaCluster* c = cl + (size_t)b * TL_MAXCLUSTERS + s;
+  atomicAdd(&c->count, (unsigned int)__popc(grp));
+  const unsigned int nb = (unsigned int)__popc(grp & bandbits);
+  if (nb) atomicAdd(&c->nband, nb);
+}
+// schedule: order[] = cluster slots sorted by size class (largest first); off / boff = exclusive prefix sums of
+// count / nband in that order.  One block of 256 threads per frame.
+static __global__ void __launch_bounds__(256) k_telea_schedule(TeleaFrame* fr, TeleaCluster* cl, unsigned int* order,
+                                                               unsigned int cap, unsigned int* status, size_t status_stride) {
+  __shared__ unsigned int ncls[TL_NCLASS], base[TL_NCLASS], fill[TL_NCLASS];
+  __shared__ unsigned int wsum[8][2], carry[2];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  TeleaFrame* f = fr + b;
+  TeleaCluster* c = cl + (size_t)b * TL_MAXCLUSTERS;
+  unsigned int* ord = order + (size_t)b * TL_MAXCLUSTERS;
+  const unsigned int n = min(f->nclusters, (unsigned int)TL_MAXCLUSTERS);
+  if (tid < TL_NCLASS) { ncls[tid] = 0; fill[tid] = 0; }
+  if (tid < 2) carry[tid] = 0;
+  __syncthreads();
+  for (unsigned int s = tid; s < n; s += 256) atomicAdd(&ncls[min(TL_NCLASS - 1, 31 - __clz(max(1u, c[s].count)))], 1u);
+  __syncthreads();
+  if (tid == 0) {
+    unsigned int a = 0;
+    for (int k = TL_NCLASS - 1; k >= 0; k--) { base[k] = a; a += ncls[k]; }
+  }
+  __syncthreads();
+  for (unsigned int s = tid; s < n; s += 256) {
+    const int k = min(TL_NCLASS - 1, 31 - __clz(max(1u, c[s].count)));
+    ord[base[k] + atomicAdd(&fill[k], 1u)] = s;
+  }
+  __syncthreads();
+  // exclusive scans over the ordered list, 256 clusters per round
+  for (unsigned int i0 = 0; i0 < n; i0 += 256) {
+    const unsigned int i = i0 + tid;
+    const unsigned int s = i < n ? ord[i] : 0;
+    unsigned int v0 = i < n ? c[s].count : 0, v1 = i < n ? c[s].nband : 0;
+    unsigned int s0 = v0, s1 = v1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      unsigned int t0 = __shfl_up_sync(0xffffffffu, s0, o), t1 = __shfl_up_sync(0xffffffffu, s1, o);
+      if (lane >= o) { s0 += t0; s1 += t1; }
+    }
+    if (lane == 31) { wsum[wid][0] = s0; wsum[wid][1] = s1; }
+    __syncthreads();
+    unsigned int p0 = carry[0], p1 = carry[1];
+    for (int k = 0; k < wid; k++) { p0 += wsum[k][0]; p1 += wsum[k][1]; }
+    if (i < n) {
+      c[s].off = p0 + s0 - v0;
+      c[s].boff = p1 + s1 - v1;
+      if (p0 + s0 > cap || p1 + s1 > cap) {           // does not fit the workspace: skipped and reported
+        c[s].count = 0xffffffffu;
+        atomicAdd(&f->overflow, 1u);
+      }
+    }
+    __syncthreads();
+    if (tid == 255) { carry[0] = p0 + s0; carry[1] = p1 + s1; }
+    __syncthreads();
+  }
+  if (tid == 0 && (f->nclusters > TL_MAXCLUSTERS || f->overflow))
+    atomicOr((unsigned int*)((char*)status + (size_t)b * status_stride), 0x8000u);
+}
+// band lists (unordered within a cluster; the heap keys carry the raster order).
+static __global__ void k_telea_bandlist(const ull* __restrict__ uf, const unsigned int* __restrict__ slot,
+                                 const uint8_t* __restrict__ flag, TeleaCluster* cl, int* __restrict__ band, size_t cap,
+                                 int Hp, int Wp) {
   const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
   const size_t sp = (size_t)Hp * Wp;
   if (i >= Hp * Wp) return;
-  unsigned int root = uf_parent(uf[(size_t)b * sp + i]);
+  if (!(flag[(size_t)b * sp + i] & TL_BAND)) return;
+  const unsigned int root = uf_parent(uf[(size_t)b * sp + i]);
   if (root == UF_BG) return;
-  unsigned int s = slot[(size_t)b * sp + root];
+  const unsigned int s = slot[(size_t)b * sp + root];
   if (s >= TL_MAXCLUSTERS) return;
   TeleaCluster* c = cl + (size_t)b * TL_MAXCLUSTERS + s;
-  const int y = i / Wp, x = i - y * Wp;
-  atomicAdd(&c->count, 1u);
-  atomicMin(&c->x0, x); atomicMax(&c->x1, x);
-  atomicMin(&c->y0, y); atomicMax(&c->y1, y);
+  if (c->count == 0xffffffffu) return;
+  band[(size_t)b * cap + c->boff + atomicAdd(&c->bfill, 1u)] = i;
 }
 
 // ------------------------------------------------------------------ 4. the march
-// All lanes of the warp execute the scalar parts redundantly (identical stores), so no cross-lane memory
-// ordering is needed; only the queue scan and the neighbourhood taps are split across lanes.
-struct TeleaCtx {
-  uint8_t* f; float* T; float* img; ull* keys; int* pos;
-  int Hp, Wp, w, n; unsigned int seq;
-};
+// One warp per cluster; the march is a chain of dependent steps, so everything on that chain is kept at
+// shared-memory / register latency:
+//  * the priority queue is a 32-ary min-heap on (T, seq) keys whose first TL_HCAP entries (levels 0-2) live in
+//    shared memory; a sift-down step examines the 32 children of a node with one access and a warp reduction;
+//  * per popped cell ONE gather brings T and flags of the 13 cells within Manhattan distance 2 (lane k loads
+//    cell k); the four neighbours' distance solves then run in registers on lanes 0..3 (they are mutually
+//    independent: no neighbour of the popped cell is a 4-neighbour of another);
+//  * the (2r+1)^2 neighbourhood of a filled pixel is evaluated one tap per lane with all loads issued up front,
+//    and summed in raster order by lanes 0..3 (one accumulator each) from shared memory.
+// Band cells enter with seq = their raster cell index (OpenCV pushes them in raster order, all with T = 0);
+// later pushes take seq from a counter above any cell index.
+#define TL_HCAP 512
+#define TL_MAXTAPS 289        // (2 * 8 + 1)^2
 
-template <bool OUTWARD>
-__device__ __forceinline__ bool tl_inside(const TeleaCtx& c, int cell) {
-  const int v = c.f[cell];
-  return OUTWARD ? ((v & TL_RING) && !(v & TL_OUT)) : ((v & TL_MASK) && !(v & TL_IN));
+struct TeleaHeap {
+  ull* sk; int* sp;        // shared: entries [0, TL_HCAP)
+  ull* gk; int* gp;        // global: entries [TL_HCAP, ...) (indexed by the entry number)
+  int n; unsigned int seq;
+};
+__device__ __forceinline__ ull th_key(const TeleaHeap& H, int i) { return i < TL_HCAP ? H.sk[i] : H.gk[i]; }
+__device__ __forceinline__ int th_pos(const TeleaHeap& H, int i) { return i < TL_HCAP ? H.sp[i] : H.gp[i]; }
+__device__ __forceinline__ void th_set(TeleaHeap& H, int i, ull k, int p) {
+  if (i < TL_HCAP) { H.sk[i] = k; H.sp[i] = p; } else { H.gk[i] = k; H.gp[i] = p; }
 }
-template <bool OUTWARD>
-__device__ __forceinline__ float tl_solve(const TeleaCtx& c, int c1, int c2) {
-  const double a11 = (double)c.T[c1], a22 = (double)c.T[c2], m12 = a11 < a22 ? a11 : a22;
+// children of node i are 32 i + 1 .. 32 i + 32.  All lanes call these together.
+__device__ __forceinline__ void th_sift_down(TeleaHeap& H, int i, ull key, int cell, int lane) {
+  for (;;) {
+    const int first = 32 * i + 1;
+    if (first >= H.n) break;
+    const int idx = first + lane;
+    ull k = ~0ull;
+    int pp = 0;
+    if (idx < H.n) { k = th_key(H, idx); pp = th_pos(H, idx); }
+    const unsigned int hi = (unsigned int)(k >> 32), lo = (unsigned int)k;
+    const unsigned int mhi = __reduce_min_sync(0xffffffffu, hi);
+    const unsigned int mlo = __reduce_min_sync(0xffffffffu, hi == mhi ? lo : 0xffffffffu);
+    const ull kmin = ((ull)mhi << 32) | (ull)mlo;
+    if (kmin >= key) break;
+    const int src = __ffs(__ballot_sync(0xffffffffu, k == kmin)) - 1;
+    const int cpos = __shfl_sync(0xffffffffu, pp, src);
+    if (lane == 0) th_set(H, i, kmin, cpos);
+    i = first + src;
+  }
+  if (lane == 0) th_set(H, i, key, cell);
+  __syncwarp();
+}
+__device__ __forceinline__ void th_push(TeleaHeap& H, int cell, float t, int lane) {
+  const ull key = ((ull)__float_as_uint(t) << 32) | (ull)H.seq;
+  H.seq++;
+  int i = H.n++;
+  while (i > 0) {
+    const int p = (i - 1) >> 5;
+    const ull pk = th_key(H, p);
+    if (pk <= key) break;
+    const int pp = th_pos(H, p);
+    if (lane == 0) th_set(H, i, pk, pp);
+    i = p;
+  }
+  if (lane == 0) th_set(H, i, key, cell);
+  __syncwarp();
+}
+__device__ __forceinline__ int th_pop(TeleaHeap& H, int lane) {      // removes the minimum (T, seq); returns its cell
+  const int cell = th_pos(H, 0);
+  H.n--;
+  if (H.n > 0) {
+    const ull key = th_key(H, H.n);
+    const int last = th_pos(H, H.n);
+    __syncwarp();
+    th_sift_down(H, 0, key, last, lane);
+  }
+  return cell;
+}
+// initial queue: the band cells of this cluster, T = 0, ordered by raster index through the key
+__device__ __forceinline__ void th_fill_band(TeleaHeap& H, const int* band, int nband, int ncells, int lane) {
+  for (int e = lane; e < nband; e += 32) {
+    const int cell = band[e];
+    th_set(H, e, (ull)(unsigned int)cell, cell);
+  }
+  H.n = nband;
+  H.seq = (unsigned int)ncells;
+  __syncwarp();
+  for (int node = (nband - 2) >> 5; node >= 0; node--) {            // heapify: sift every internal node down
+    const ull key = th_key(H, node);
+    const int cell = th_pos(H, node);
+    __syncwarp();
+    th_sift_down(H, node, key, cell, lane);
+  }
+}
+
+// Eikonal update from two 4-neighbours (T value, "still unknown" flag each); OpenCV's FastMarching_solve.
+__device__ __forceinline__ float tl_solve2(float t1, bool in1, float t2, bool in2) {
+  const double a11 = (double)t1, a22 = (double)t2, m12 = a11 < a22 ? a11 : a22;
   double sol;
-  if (!tl_inside<OUTWARD>(c, c1)) {
-    if (!tl_inside<OUTWARD>(c, c2)) {
+  if (!in1) {
+    if (!in2) {
       if (fabs(a11 - a22) >= 1.0) sol = 1.0 + m12;
       else sol = (a11 + a22 + sqrt(2.0 - (a11 - a22) * (a11 - a22))) * 0.5;
     } else sol = 1.0 + a11;
-  } else if (!tl_inside<OUTWARD>(c, c2)) sol = 1.0 + a22;
+  } else if (!in2) sol = 1.0 + a22;
   else sol = 1.0 + m12;
   return (float)sol;
 }
 template <bool OUTWARD>
-__device__ __forceinline__ float tl_dist(const TeleaCtx& c, int i, int j) {
-  const int p = i * c.Wp + j, W = c.Wp;
-  float a = tl_solve<OUTWARD>(c, p - W, p - 1), b = tl_solve<OUTWARD>(c, p + W, p - 1);
-  float d = tl_solve<OUTWARD>(c, p - W, p + 1), e = tl_solve<OUTWARD>(c, p + W, p + 1);
-  return fminf(fminf(a, b), fminf(d, e));
+__device__ __forceinline__ bool tl_in(int v) {
+  return OUTWARD ? ((v & TL_RING) && !(v & TL_OUT)) : ((v & TL_MASK) && !(v & TL_IN));
 }
-__device__ __forceinline__ void tl_push(TeleaCtx& c, int cell, float t) {
-  c.keys[c.n] = ((ull)__float_as_uint(t) << 32) | (ull)c.seq;
-  c.pos[c.n] = cell;
-  c.n++; c.seq++;
+// The 13 cells within Manhattan distance 2 of the popped cell: index -> (dy, dx).  1..4 are the neighbours in
+// OpenCV's visiting order (up, left, down, right).
+__device__ __forceinline__ void tl_diamond(int k, int& dy, int& dx) {
+  dy = (int)((0x364a88268aull >> (3 * k)) & 7ull) - 2;
+  dx = (int)((0x32cc413452ull >> (3 * k)) & 7ull) - 2;
 }
-// pops the minimum (T, seq); returns its cell
-__device__ __forceinline__ int tl_pop(TeleaCtx& c, int lane) {
-  ull best = ~0ull;
-  int bi = -1;
-  for (int e = lane; e < c.n; e += 32) {
-    ull k = c.keys[e];
-    if (k < best) { best = k; bi = e; }
+// diamond indices of the (up, left, down, right) neighbours of neighbour q
+__device__ __forceinline__ int tl_nbr(int q, int dir) { return (int)((0x8c0ac7b00b69a095ull >> (4 * (4 * q + dir))) & 15ull); }
+
+// gather of the diamond around `cell` (lane k < 13 loads cell k; out-of-frame cells read as "known, far away")
+__device__ __forceinline__ void tl_gather(const uint8_t* f, const float* T, int ii, int jj, int Hp, int Wp, int lane,
+                                          float& t, int& v) {
+  t = 1.0e6f; v = 0;
+  if (lane < 13) {
+    int dy, dx;
+    tl_diamond(lane, dy, dx);
+    const int y = ii + dy, x = jj + dx;
+    if (y >= 0 && x >= 0 && y < Hp && x < Wp) { t = T[y * Wp + x]; v = f[y * Wp + x]; }
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    ull ok = __shfl_xor_sync(0xffffffffu, best, o);
-    int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-    if (ok < best) { best = ok; bi = oi; }            // keys are unique (seq), no tie handling needed
-  }
-  const int cell = c.pos[bi];
-  c.n--;
-  const ull lk = c.keys[c.n];
-  const int lp = c.pos[c.n];
-  __syncwarp();
-  c.keys[bi] = lk;
-  c.pos[bi] = lp;
-  __syncwarp();
-  return cell;
-}
-// initial queue: band cells of this cluster in raster order, T = 0
-__device__ __forceinline__ void tl_fill_band(TeleaCtx& c, const ull* uf, const TeleaCluster& cl, int lane) {
-  c.n = 0; c.seq = 0;
-  for (int y = cl.y0; y <= cl.y1; y++)
-    for (int xb = cl.x0; xb <= cl.x1; xb += 32) {
-      const int x = xb + lane;
-      bool is = false;
-      if (x <= cl.x1) {
-        const int cell = y * c.Wp + x;
-        is = (c.f[cell] & TL_BAND) && uf_parent(uf[cell]) == cl.root;
-      }
-      const unsigned int bits = __ballot_sync(0xffffffffu, is);
-      if (is) {
-        const int k = c.n + __popc(bits & ((1u << lane) - 1u));
-        c.keys[k] = (ull)(c.seq + (unsigned)(k - c.n));     // T = 0
-        c.pos[k] = y * c.Wp + x;
-      }
-      c.n += __popc(bits);
-      c.seq += __popc(bits);
-    }
-  __syncwarp();
 }
 
 static __global__ void __launch_bounds__(32 * TL_WARPS) k_telea_march(TeleaWs Wsp, float* __restrict__ img,
-                                                                size_t img_stride, unsigned int* status,
-                                                                size_t status_stride, int h, int w, int range) {
-  const int b = blockIdx.y, lane = threadIdx.x & 31;
+                                                                size_t img_stride, int h, int w, int range) {
+  extern __shared__ unsigned char tl_smem[];
+  const int b = blockIdx.x, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  ull* sk = (ull*)tl_smem + (size_t)wid * TL_HCAP;
+  int* sp = (int*)(tl_smem + (size_t)TL_WARPS * TL_HCAP * 8) + (size_t)wid * TL_HCAP;
+  float (*tp)[4] = (float (*)[4])(tl_smem + (size_t)TL_WARPS * TL_HCAP * 12) + (size_t)wid * 32;
+  // per-tap constants of the (2r+1)^2 neighbourhood: offsets (0x7fff = outside the radius-r disc) and 1 / |r|^3
+  short2* tapd = (short2*)(tl_smem + (size_t)TL_WARPS * (TL_HCAP * 12 + 32 * 16));
+  float* tapw = (float*)(tapd + TL_MAXTAPS);
   const int Hp = h + 2, Wp = w + 2;
   TeleaFrame* fr = Wsp.fr + b;
   const TeleaCluster* clt = Wsp.cl + (size_t)b * TL_MAXCLUSTERS;
-  const ull* uf = Wsp.uf + (size_t)b * Wsp.sp;
+  const unsigned int* ord = Wsp.order + (size_t)b * TL_MAXCLUSTERS;
   const unsigned int ncl = min(fr->nclusters, (unsigned int)TL_MAXCLUSTERS);
-  if (fr->nclusters > TL_MAXCLUSTERS && threadIdx.x == 0 && blockIdx.x == 0)
-    atomicOr((unsigned int*)((char*)status + (size_t)b * status_stride), 0x8000u);
-  TeleaCtx c;
-  c.f = Wsp.flag + (size_t)b * Wsp.sp;
-  c.T = Wsp.T + (size_t)b * Wsp.sp;
-  c.img = img + (size_t)b * img_stride;
-  c.Hp = Hp; c.Wp = Wp; c.w = w;
+  uint8_t* f = Wsp.flag + (size_t)b * Wsp.sp;
+  float* T = Wsp.T + (size_t)b * Wsp.sp;
+  float* im = img + (size_t)b * img_stride;
   const int r2 = range * range, side = 2 * range + 1, ntaps = side * side;
+  for (int tt = threadIdx.x; tt < ntaps; tt += blockDim.x) {
+    const int dk = tt / side - range, dl = tt - (tt / side) * side - range;
+    const bool in_disc = dk * dk + dl * dl <= r2 && (dk | dl) != 0;        // the centre is the pixel being filled
+    const float ry = (float)(-dk), rx = (float)(-dl);
+    const float len2 = __fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry));
+    tapd[tt] = in_disc ? make_short2((short)dk, (short)dl) : make_short2(0x7fff, 0x7fff);
+    tapw[tt] = in_disc ? (float)(1.0 / (double)__fmul_rn(len2, __fsqrt_rn(len2))) : 0.f;
+  }
+  __syncthreads();
+  const int q = lane & 3;                                   // lanes 0..3 own neighbour q; other lanes mirror them
+  int qdy, qdx;
+  tl_diamond(q + 1, qdy, qdx);
   for (;;) {
     unsigned int s = 0;
     if (lane == 0) s = atomicAdd(&fr->next, 1u);
     s = __shfl_sync(0xffffffffu, s, 0);
     if (s >= ncl) break;
-    const TeleaCluster cl = clt[s];
-    unsigned int off = 0;
-    if (lane == 0) off = atomicAdd(&fr->cursor, cl.count);
-    off = __shfl_sync(0xffffffffu, off, 0);
-    if ((size_t)off + cl.count > Wsp.cap) {
-      if (lane == 0) { atomicAdd(&fr->overflow, 1u); atomicOr((unsigned int*)((char*)status + (size_t)b * status_stride), 0x8000u); }
-      continue;
-    }
-    c.keys = Wsp.keys + (size_t)b * Wsp.cap + off;
-    c.pos = Wsp.pos + (size_t)b * Wsp.cap + off;
+    const TeleaCluster cl = clt[ord[s]];
+    if (cl.count == 0xffffffffu) continue;                  // did not fit the workspace (status bit already set)
+    TeleaHeap H;
+    H.sk = sk; H.sp = sp;
+    H.gk = Wsp.keys + (size_t)b * Wsp.cap + cl.off;
+    H.gp = Wsp.pos + (size_t)b * Wsp.cap + cl.off;
+    int* log = Wsp.log + (size_t)b * Wsp.cap + cl.off;
+    const int* band = Wsp.band + (size_t)b * Wsp.cap + cl.boff;
+    int nlog = 0;
     // ---- outward: distances over the ring
-    tl_fill_band(c, uf, cl, lane);
-    while (c.n > 0) {
-      const int cell = tl_pop(c, lane);
+    __syncwarp();
+    th_fill_band(H, band, (int)cl.nband, Hp * Wp, lane);
+    while (H.n > 0) {
+      const int cell = th_pop(H, lane);
+      if (lane == 0) log[nlog] = cell;
+      nlog++;
       const int ii = cell / Wp, jj = cell - ii * Wp;
+      float t; int v;
+      tl_gather(f, T, ii, jj, Hp, Wp, lane, t, v);
+      // lane q: neighbour q = (ii, jj) + d_q
+      const int i = ii + qdy, j = jj + qdx;
+      const int vq = __shfl_sync(0xffffffffu, v, q + 1);
+      const bool ok = i > 0 && j > 0 && i < Hp - 1 && j < Wp - 1 && tl_in<true>(vq);
+      const float tu = __shfl_sync(0xffffffffu, t, tl_nbr(q, 0)), tl_ = __shfl_sync(0xffffffffu, t, tl_nbr(q, 1));
+      const float td = __shfl_sync(0xffffffffu, t, tl_nbr(q, 2)), tr = __shfl_sync(0xffffffffu, t, tl_nbr(q, 3));
+      const bool iu = tl_in<true>(__shfl_sync(0xffffffffu, v, tl_nbr(q, 0))), il = tl_in<true>(__shfl_sync(0xffffffffu, v, tl_nbr(q, 1)));
+      const bool id = tl_in<true>(__shfl_sync(0xffffffffu, v, tl_nbr(q, 2))), ir = tl_in<true>(__shfl_sync(0xffffffffu, v, tl_nbr(q, 3)));
+      float d = 0.f;
+      if (ok) d = fminf(fminf(tl_solve2(tu, iu, tl_, il), tl_solve2(td, id, tl_, il)),
+                        fminf(tl_solve2(tu, iu, tr, ir), tl_solve2(td, id, tr, ir)));
+      if (ok && lane < 4) { T[i * Wp + j] = d; f[i * Wp + j] = (uint8_t)(vq | TL_OUT); }
+      const unsigned int okbits = __ballot_sync(0xffffffffu, ok) & 15u;
 #pragma unroll
-      for (int q = 0; q < 4; q++) {
-        const int i = ii + (q == 0 ? -1 : q == 2 ? 1 : 0), j = jj + (q == 1 ? -1 : q == 3 ? 1 : 0);
-        if (i <= 0 || j <= 0 || i >= Hp - 1 || j >= Wp - 1) continue;
-        const int p = i * Wp + j;
-        if (!tl_inside<true>(c, p)) continue;
-        const float d = tl_dist<true>(c, i, j);
-        c.T[p] = d;
-        c.f[p] = (uint8_t)(c.f[p] | TL_OUT);
-        tl_push(c, p, d);
+      for (int qq = 0; qq < 4; qq++) {
+        if (!((okbits >> qq) & 1u)) continue;
+        int dy, dx;
+        tl_diamond(qq + 1, dy, dx);
+        th_push(H, (ii + dy) * Wp + jj + dx, __shfl_sync(0xffffffffu, d, qq), lane);
       }
     }
     // negate the distances of every cell the outward march visited (band and reached ring)
-    for (int y = max(cl.y0, 1); y <= min(cl.y1, Hp - 2); y++)
-      for (int x = max(cl.x0, 1) + lane; x <= min(cl.x1, Wp - 2); x += 32) {
-        const int cell = y * Wp + x;
-        const int v = c.f[cell];
-        if (uf_parent(uf[cell]) == cl.root && ((v & TL_BAND) || ((v & TL_RING) && (v & TL_OUT)))) c.T[cell] = -c.T[cell];
-      }
+    __syncwarp();
+    for (int e = lane; e < nlog; e += 32) { const int cell = log[e]; T[cell] = -T[cell]; }
     __syncwarp();
     // ---- inward: fill the hole
-    tl_fill_band(c, uf, cl, lane);
-    while (c.n > 0) {
-      const int cell = tl_pop(c, lane);
+    th_fill_band(H, band, (int)cl.nband, Hp * Wp, lane);
+    while (H.n > 0) {
+      const int cell = th_pop(H, lane);
       const int ii = cell / Wp, jj = cell - ii * Wp;
-      for (int q = 0; q < 4; q++) {
-        const int i = ii + (q == 0 ? -1 : q == 2 ? 1 : 0), j = jj + (q == 1 ? -1 : q == 3 ? 1 : 0);
-        if (i <= 0 || j <= 0 || i >= Hp - 1 || j >= Wp - 1) continue;
-        const int p = i * Wp + j;
-        if (!tl_inside<false>(c, p)) continue;
-        const float dist = tl_dist<false>(c, i, j);
-        c.T[p] = dist;
-        float gTx, gTy;
-        if (!tl_inside<false>(c, p + 1)) {
-          if (!tl_inside<false>(c, p - 1)) gTx = __fmul_rn(__fsub_rn(c.T[p + 1], c.T[p - 1]), 0.5f);
-          else gTx = __fsub_rn(c.T[p + 1], dist);
-        } else {
-          if (!tl_inside<false>(c, p - 1)) gTx = __fsub_rn(dist, c.T[p - 1]);
-          else gTx = 0.f;
-        }
-        if (!tl_inside<false>(c, p + Wp)) {
-          if (!tl_inside<false>(c, p - Wp)) gTy = __fmul_rn(__fsub_rn(c.T[p + Wp], c.T[p - Wp]), 0.5f);
-          else gTy = __fsub_rn(c.T[p + Wp], dist);
-        } else {
-          if (!tl_inside<false>(c, p - Wp)) gTy = __fsub_rn(dist, c.T[p - Wp]);
-          else gTy = 0.f;
-        }
-        float Ia = 0.f, Jx = 0.f, Jy = 0.f, sw = 1.0e-20f;
+      float t; int v;
+      tl_gather(f, T, ii, jj, Hp, Wp, lane, t, v);
+      const int iq = ii + qdy, jq = jj + qdx;
+      const int vq = __shfl_sync(0xffffffffu, v, q + 1);
+      const bool ok = iq > 0 && jq > 0 && iq < Hp - 1 && jq < Wp - 1 && tl_in<false>(vq);
+      const float tu = __shfl_sync(0xffffffffu, t, tl_nbr(q, 0)), tl_ = __shfl_sync(0xffffffffu, t, tl_nbr(q, 1));
+      const float td = __shfl_sync(0xffffffffu, t, tl_nbr(q, 2)), tr = __shfl_sync(0xffffffffu, t, tl_nbr(q, 3));
+      const bool iu = tl_in<false>(__shfl_sync(0xffffffffu, v, tl_nbr(q, 0))), il = tl_in<false>(__shfl_sync(0xffffffffu, v, tl_nbr(q, 1)));
+      const bool id = tl_in<false>(__shfl_sync(0xffffffffu, v, tl_nbr(q, 2))), ir = tl_in<false>(__shfl_sync(0xffffffffu, v, tl_nbr(q, 3)));
+      float dq = 0.f, gxq = 0.f, gyq = 0.f;
+      if (ok) {
+        dq = fminf(fminf(tl_solve2(tu, iu, tl_, il), tl_solve2(td, id, tl_, il)),
+                   fminf(tl_solve2(tu, iu, tr, ir), tl_solve2(td, id, tr, ir)));
+        if (!ir) gxq = !il ? __fmul_rn(__fsub_rn(tr, tl_), 0.5f) : __fsub_rn(tr, dq);
+        else gxq = !il ? __fsub_rn(dq, tl_) : 0.f;
+        if (!id) gyq = !iu ? __fmul_rn(__fsub_rn(td, tu), 0.5f) : __fsub_rn(td, dq);
+        else gyq = !iu ? __fsub_rn(dq, tu) : 0.f;
+      }
+      const unsigned int okbits = __ballot_sync(0xffffffffu, ok) & 15u;
+      for (int qq = 0; qq < 4; qq++) {
+        if (!((okbits >> qq) & 1u)) continue;
+        int dy, dx;
+        tl_diamond(qq + 1, dy, dx);
+        const int i = ii + dy, j = jj + dx, p = i * Wp + j;
+        const float dist = __shfl_sync(0xffffffffu, dq, qq);
+        const float gTx = __shfl_sync(0xffffffffu, gxq, qq), gTy = __shfl_sync(0xffffffffu, gyq, qq);
+        const int vp = __shfl_sync(0xffffffffu, vq, qq);
+        float Ia = 0.f, Jx = 0.f, Jy = 0.f, sw = 1.0e-20f;        // meaningful on lanes 0..3 (one accumulator each)
         for (int t0 = 0; t0 < ntaps; t0 += 32) {
           const int tap = t0 + lane;
-          bool act = false;
           float wgt = 0.f, ta = 0.f, tx = 0.f, ty = 0.f;
-          if (tap < ntaps) {
-            const int dk = tap / side - range, dl = tap - (tap / side) * side - range;
-            const int k = i + dk, l = j + dl;
-            if (k > 0 && l > 0 && k < Hp - 1 && l < Wp - 1 && dk * dk + dl * dl <= r2) {
-              const int pk = k * Wp + l;
-              if (!tl_inside<false>(c, pk)) {
-                act = true;
-                const int km = k - 1 + (k == 1), kp = k - 1 - (k == Hp - 2);
-                const int lm = l - 1 + (l == 1), lp = l - 1 - (l == Wp - 2);
-                const float ry = (float)(i - k), rx = (float)(j - l);
-                const float len2 = __fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry));
-                const float dst = (float)(1.0 / (double)__fmul_rn(len2, __fsqrt_rn(len2)));
-                const float lev = (float)(1.0 / (1.0 + fabs((double)__fsub_rn(c.T[pk], dist))));
-                float dir = __fadd_rn(__fmul_rn(rx, gTx), __fmul_rn(ry, gTy));
-                if (fabs((double)dir) <= 0.01) dir = 0.000001f;
-                wgt = fabsf(__fmul_rn(__fmul_rn(dst, lev), dir));
-#define TL_O(a, bb) c.img[(size_t)(a) * c.w + (bb)]
-                float gIx, gIy;
-                if (!tl_inside<false>(c, pk + 1)) {
-                  if (!tl_inside<false>(c, pk - 1)) gIx = __fmul_rn(__fsub_rn(TL_O(km, lp + 1), TL_O(km, lm - 1)), 2.0f);
-                  else gIx = __fsub_rn(TL_O(km, lp + 1), TL_O(km, lm));
-                } else {
-                  if (!tl_inside<false>(c, pk - 1)) gIx = __fsub_rn(TL_O(km, lp), TL_O(km, lm - 1));
-                  else gIx = 0.f;
-                }
-                if (!tl_inside<false>(c, pk + Wp)) {
-                  if (!tl_inside<false>(c, pk - Wp)) gIy = __fmul_rn(__fsub_rn(TL_O(kp + 1, lm), TL_O(km - 1, lm)), 2.0f);
-                  else gIy = __fsub_rn(TL_O(kp + 1, lm), TL_O(km, lm));
-                } else {
-                  if (!tl_inside<false>(c, pk - Wp)) gIy = __fsub_rn(TL_O(kp, lm), TL_O(km - 1, lm));
-                  else gIy = 0.f;
-                }
-                ta = __fmul_rn(wgt, TL_O(k - 1, l - 1));
-                tx = __fmul_rn(wgt, __fmul_rn(gIx, rx));
-                ty = __fmul_rn(wgt, __fmul_rn(gIy, ry));
+          const short2 dd = tap < ntaps ? tapd[tap] : make_short2(0x7fff, 0x7fff);
+          const int dk = dd.x, dl = dd.y;
+          const int k = i + dk, l = j + dl;
+          if (dk != 0x7fff && k > 0 && l > 0 && k < Hp - 1 && l < Wp - 1) {
+            const int pk = k * Wp + l;
+            const int km = k - 1 + (k == 1), kp = k - 1 - (k == Hp - 2);
+            const int lm = l - 1 + (l == 1), lp = l - 1 - (l == Wp - 2);
+            // every load of this tap is issued before any of them is used (one memory round trip)
+            const int f0 = f[pk], fl = f[pk - 1], fr_ = f[pk + 1], fu = f[pk - Wp], fd = f[pk + Wp];
+            const float Tk = T[pk];
+#define TL_O(a, bb) im[(size_t)(a) * w + (bb)]
+            const float o_c = TL_O(k - 1, l - 1);
+            const float o_r1 = TL_O(km, lp + 1), o_l1 = TL_O(km, lm - 1), o_lm = TL_O(km, lm), o_lp = TL_O(km, lp);
+            const float o_d1 = TL_O(kp + 1, lm), o_u1 = TL_O(km - 1, lm), o_kp = TL_O(kp, lm);
 #undef TL_O
-              }
+            if (!tl_in<false>(f0)) {
+              const float ry = (float)(-dk), rx = (float)(-dl);
+              const float dst = tapw[tap];
+              const float lev = (float)(1.0 / (1.0 + fabs((double)__fsub_rn(Tk, dist))));
+              float dir = __fadd_rn(__fmul_rn(rx, gTx), __fmul_rn(ry, gTy));
+              if (fabs((double)dir) <= 0.01) dir = 0.000001f;
+              wgt = fabsf(__fmul_rn(__fmul_rn(dst, lev), dir));
+              float gIx, gIy;
+              if (!tl_in<false>(fr_)) gIx = !tl_in<false>(fl) ? __fmul_rn(__fsub_rn(o_r1, o_l1), 2.0f) : __fsub_rn(o_r1, o_lm);
+              else gIx = !tl_in<false>(fl) ? __fsub_rn(o_lp, o_l1) : 0.f;
+              if (!tl_in<false>(fd)) gIy = !tl_in<false>(fu) ? __fmul_rn(__fsub_rn(o_d1, o_u1), 2.0f) : __fsub_rn(o_d1, o_lm);
+              else gIy = !tl_in<false>(fu) ? __fsub_rn(o_kp, o_u1) : 0.f;
+              ta = __fmul_rn(wgt, o_c);
+              tx = __fmul_rn(wgt, __fmul_rn(gIx, rx));
+              ty = __fmul_rn(wgt, __fmul_rn(gIy, ry));
             }
           }
-          unsigned int bits = __ballot_sync(0xffffffffu, act);
-          while (bits) {                               // raster-order accumulation, identical on every lane
-            const int src = __ffs(bits) - 1;
-            bits &= bits - 1;
-            Ia = __fadd_rn(Ia, __shfl_sync(0xffffffffu, ta, src));
-            Jx = __fsub_rn(Jx, __shfl_sync(0xffffffffu, tx, src));
-            Jy = __fsub_rn(Jy, __shfl_sync(0xffffffffu, ty, src));
-            sw = __fadd_rn(sw, __shfl_sync(0xffffffffu, wgt, src));
+          // raster-order accumulation: lane a < 4 sums term a of the 32 taps of this round sequentially (inactive taps
+          // contribute +0, which leaves a float sum unchanged), so results do not depend on the lane count.
+          __syncwarp();
+          tp[lane][0] = ta; tp[lane][1] = -tx; tp[lane][2] = -ty; tp[lane][3] = wgt;
+          __syncwarp();
+          if (lane < 4) {
+            float acc = lane == 0 ? Ia : lane == 1 ? Jx : lane == 2 ? Jy : sw;
+#pragma unroll
+            for (int tt = 0; tt < 32; tt++) acc = __fadd_rn(acc, tp[tt][lane]);
+            if (lane == 0) Ia = acc; else if (lane == 1) Jx = acc; else if (lane == 2) Jy = acc; else sw = acc;
           }
         }
+        Ia = __shfl_sync(0xffffffffu, Ia, 0); Jx = __shfl_sync(0xffffffffu, Jx, 1);
+        Jy = __shfl_sync(0xffffffffu, Jy, 2); sw = __shfl_sync(0xffffffffu, sw, 3);
         const float nrm = __fadd_rn(__fsqrt_rn(__fadd_rn(__fmul_rn(Jx, Jx), __fmul_rn(Jy, Jy))), 1.0e-20f);
         const float val = __fadd_rn(__fdiv_rn(Ia, sw), __fdiv_rn(__fadd_rn(Jx, Jy), nrm));
-        c.img[(size_t)(i - 1) * w + (j - 1)] = val;
-        c.f[p] = (uint8_t)(c.f[p] | TL_IN);
-        tl_push(c, p, dist);
+        if (lane == 0) {
+          im[(size_t)(i - 1) * w + (j - 1)] = val;
+          T[p] = dist;
+          f[p] = (uint8_t)(vp | TL_IN);
+        }
         __syncwarp();
+        th_push(H, p, dist, lane);
       }
     }
   }
@@ -392,9 +550,19 @@ static int telea_inpaint(Mask mask, float* img, size_t img_stride, unsigned int*
   TeleaFg fg{W.flag, (size_t)sp, Wp};
   if (uf_label(fg, EdgeZero(), W.uf, (unsigned int*)nullptr, (unsigned int*)nullptr, 0, Hp, Wp, batch, st)) return 1;
   CK(cudaMemsetAsync(W.fr, 0, sizeof(TeleaFrame) * (size_t)batch, st));
-  VL(), k_telea_slots<<<dim3(cdiv(sp, 256), batch), 256, 0, st>>>(W.uf, W.slot, W.fr, W.cl, Hp, Wp);
-  VL(), k_telea_bbox<<<dim3(cdiv(sp, 256), batch), 256, 0, st>>>(W.uf, W.slot, W.cl, Hp, Wp);
-  VL(), k_telea_march<<<dim3(TL_GRIDX, batch), 32 * TL_WARPS, 0, st>>>(W, img, img_stride, status, status_stride, h, w, range);
+  const dim3 gcell(cdiv(sp, 256), batch);
+  VL(), k_telea_slots<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.fr, W.cl, Hp, Wp);
+  VL(), k_telea_count<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.flag, W.cl, Hp, Wp);
+  VL(), k_telea_schedule<<<batch, 256, 0, st>>>(W.fr, W.cl, W.order, (unsigned int)W.cap, status, status_stride);
+  VL(), k_telea_bandlist<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.flag, W.cl, W.band, W.cap, Hp, Wp);
+  const size_t march_smem = (size_t)TL_WARPS * (TL_HCAP * 12 + 32 * 16) + (size_t)TL_MAXTAPS * 8;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute((const void*)k_telea_march, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)march_smem));
+    attr_set = true;
+  }
+  // blockIdx.x = frame: the first wave of blocks starts the largest clusters of EVERY frame
+  VL(), k_telea_march<<<dim3(batch, TL_GRIDX), 32 * TL_WARPS, march_smem, st>>>(W, img, img_stride, h, w, range);
   CKL();
   return 0;
 }

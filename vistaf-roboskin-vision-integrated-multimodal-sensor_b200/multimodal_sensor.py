@@ -273,7 +273,7 @@ class MultimodalPlan:
     """FTP + force + temperature over batches of full camera frames resident on the GPU.
     mode: "multimodal" | "ftp" | "temperature" selects which halves run (BASELINE.json configs[1..3])."""
 
-    def __init__(self, H: int, W: int, chunk_ftp: int = 16, chunk_temp: int = 16, mode: str = "multimodal"):
+    def __init__(self, H: int, W: int, chunk_ftp: int = 64, chunk_temp: int = 32, mode: str = "multimodal"):
         if mode not in ("multimodal", "ftp", "temperature"):
             raise ValueError(f"unknown mode {mode}")
         self.torch = N.require_cuda()
@@ -281,6 +281,28 @@ class MultimodalPlan:
         self.ftp = shape_ftp.FtpPlan(H, W, chunk=chunk_ftp) if mode != "temperature" else None
         self.temp = temperature_sensor.TempPlan(H, W, chunk=chunk_temp) if mode != "ftp" else None
         self._out = {}
+        self._side = self.torch.cuda.Stream() if mode == "multimodal" else None
+
+    def step(self, ref_frame_dev, frames_dev, masks: bool = False, reuse_outputs: bool = True) -> dict:
+        """One batch against a (new) reference frame.  The reference-frame half (demodulation of one frame: a short,
+        latency-bound chain of kernels plus one small device->host read of the carrier peak) runs on a side stream
+        while the temperature half of the batch runs on the current stream; the FTP batch follows both."""
+        t = self.torch
+        if self._side is None:
+            self.set_reference(ref_frame_dev)
+            return self.run(frames_dev, masks, reuse_outputs)
+        main = t.cuda.current_stream()
+        B = int(frames_dev.shape[0])
+        key = (B, bool(masks))
+        cache = self._out.get(key) if reuse_outputs else None
+        self._side.wait_stream(main)              # inputs are ready; the FTP workspace is free of the previous batch
+        res = {"temp": self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None)}    # async, main stream
+        with t.cuda.stream(self._side):
+            self.set_reference(ref_frame_dev)     # host returns when the side stream has the carrier
+        main.wait_stream(self._side)
+        gray = self.ftp.crop_gray(frames_dev)
+        res["ftp"] = self.ftp.run(gray, masks=masks, out=cache["ftp"] if cache else None)
+        return self._finish(res, B, cache, key, reuse_outputs)
 
     def set_reference(self, ref_frame_dev):
         """ref_frame_dev: uint8 CUDA [H,W,3] reference (undeformed) frame."""
@@ -299,6 +321,10 @@ class MultimodalPlan:
             res["ftp"] = self.ftp.run(gray, masks=masks, out=cache["ftp"] if cache else None)
         if self.temp is not None:
             res["temp"] = self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None)
+        return self._finish(res, B, cache, key, reuse_outputs)
+
+    def _finish(self, res, B, cache, key, reuse_outputs):
+        t = self.torch
         rec = cache["records"] if cache else t.zeros((B, RECORD_BYTES), dtype=t.uint8, device="cuda")
         if "ftp" in res:
             rec[:, :104].copy_(res["ftp"]["records"])
