@@ -541,8 +541,9 @@ __device__ __forceinline__ float poly_fit(const float* c, float xn, float yn, bo
 }
 struct FitGeom {
   int w; float cx, cy;           // (w-1)/2, (h-1)/2
+  unsigned int magic;            // ceil(2^40 / w): i / w == (i * magic) >> 40 for i < 2^24, 256 <= w < 65536
   __device__ void norm(int i, float& xn, float& yn) const {
-    const int y = i / w, x = i - y * w;
+    const int y = (int)(((unsigned long long)(unsigned int)i * magic) >> 40), x = i - y * w;
     xn = __fdiv_rn(__fsub_rn((float)x, cx), cx);
     yn = __fdiv_rn(__fsub_rn((float)y, cy), cy);
   }
@@ -573,32 +574,44 @@ __global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ z,
   double acc[NV];
 #pragma unroll
   for (int i = 0; i < NV; i++) acc[i] = 0.0;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
-    if (!fm(b, i)) continue;
-    const float zz = z[(size_t)b * npix + i];
-    if (!(fabsf(zz) <= 3.4e38f)) continue;
-    float xn, yn;
-    g.norm(i, xn, yn);
-    float wt = 1.0f;
-    if (iter > 0) {
-      const float r = __fsub_rn(zz, poly_fit(coef, xn, yn, ORDER2));
-      const float u = __fdiv_rn(r, cs);
-      wt = __fdiv_rn(1.0f, __fadd_rn(1.0f, __fmul_rn(u, u)));
-    }
-    const double w2 = (double)wt * (double)wt;
-    double a[NC];
-    a[0] = xn; a[1] = yn; a[2] = 1.0;
-    if (ORDER2) { a[3] = (double)__fmul_rn(xn, xn); a[4] = (double)__fmul_rn(xn, yn); a[5] = (double)__fmul_rn(yn, yn); }
-    int k = 0;
+  // four pixels per thread and trip: the mask bytes and samples of all four are loaded before any is used
+  for (int i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4; i0 < npix; i0 += gridDim.x * blockDim.x * 4) {
+    bool in[4];
+    float z4[4];
 #pragma unroll
-    for (int p = 0; p < NC; p++) {
-      const double wa = w2 * a[p];
-#pragma unroll
-      for (int q = p; q < NC; q++) acc[k++] += wa * a[q];
+    for (int j = 0; j < 4; j++) {
+      const int i = i0 + j;
+      in[j] = i < npix && fm(b, i);
+      z4[j] = i < npix ? z[(size_t)b * npix + i] : 0.f;
     }
 #pragma unroll
-    for (int p = 0; p < NC; p++) acc[k++] += w2 * a[p] * (double)zz;
-    acc[k] += 1.0;
+    for (int j = 0; j < 4; j++) {
+      const int i = i0 + j;
+      const float zz = z4[j];
+      if (!in[j] || !(fabsf(zz) <= 3.4e38f)) continue;
+      float xn, yn;
+      g.norm(i, xn, yn);
+      float wt = 1.0f;
+      if (iter > 0) {
+        const float r = __fsub_rn(zz, poly_fit(coef, xn, yn, ORDER2));
+        const float u = __fdiv_rn(r, cs);
+        wt = __fdiv_rn(1.0f, __fadd_rn(1.0f, __fmul_rn(u, u)));
+      }
+      const double w2 = (double)wt * (double)wt;
+      double a[NC];
+      a[0] = xn; a[1] = yn; a[2] = 1.0;
+      if (ORDER2) { a[3] = (double)__fmul_rn(xn, xn); a[4] = (double)__fmul_rn(xn, yn); a[5] = (double)__fmul_rn(yn, yn); }
+      int k = 0;
+#pragma unroll
+      for (int p = 0; p < NC; p++) {
+        const double wa = w2 * a[p];
+#pragma unroll
+        for (int q = p; q < NC; q++) acc[k++] += wa * a[q];
+      }
+#pragma unroll
+      for (int p = 0; p < NC; p++) acc[k++] += w2 * a[p] * (double)zz;
+      acc[k] += 1.0;
+    }
   }
   block_sum<NV>(acc, sh);
   if (threadIdx.x == 0)
@@ -860,10 +873,15 @@ struct CandFg {
 __global__ void k_ftp_blob_peak(const ull* __restrict__ uf, const float* __restrict__ mm, unsigned int* __restrict__ peak,
                                 int npix) {
   const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= npix) return;
-  const unsigned int root = uf_parent(uf[(size_t)b * npix + i]);
-  if (root == UF_BG) return;
-  atomicMax(peak + (size_t)b * npix + root, __float_as_uint(mm[(size_t)b * npix + i]));
+  unsigned int root = UF_BG, bits = 0;
+  if (i < npix) {
+    root = uf_parent(uf[(size_t)b * npix + i]);
+    if (root != UF_BG) bits = __float_as_uint(mm[(size_t)b * npix + i]);      // depth > 0: bit order == value order
+  }
+  // lanes of one blob elect a leader that carries the group's maximum: one atomic per blob per warp
+  const unsigned int grp = __match_any_sync(0xffffffffu, root);
+  const unsigned int mx = __reduce_max_sync(grp, bits);
+  if (root != UF_BG && (int)(__ffs(grp) - 1) == (int)(threadIdx.x & 31)) atomicMax(peak + (size_t)b * npix + root, mx);
 }
 __global__ void k_ftp_blob_apply(const ull* __restrict__ uf, const unsigned int* __restrict__ peak, FtpScal* sc,
                                  float* __restrict__ mm, uint8_t* __restrict__ kept, int npix, double min_peak, double rel_frac) {
@@ -985,7 +1003,7 @@ static void ftp_layout(const VistafFtpPlan* p, int chunk, FtpWs& L) {
   L.contact = take(c * S); L.contact_d = take(c * S);
   L.hnum = take(c * S * 4); L.hm = take(c * S * 4); L.dist_in = take(c * S * 4); L.dist_out = take(c * S * 4);
   L.dtmp = take(c * S * 4); L.snum = take(c * S * 4); L.sm = take(c * S * 4); L.peak = take(c * S * 4);
-  L.scal = take(c * sizeof(FtpScal)); L.sel = take(c * sizeof(SelectState));
+  L.scal = take(c * sizeof(FtpScal)); L.sel = take(sel_ws_bytes((int)c));
   L.telea = take(telea_ws_bytes(p->h, p->w, chunk));
   L.total = o;
 }
@@ -1013,7 +1031,8 @@ extern "C" int vistaf_ftp_plan_create(const VistafFtpParams* P, VistafFtpPlan** 
   if (!P || !out) return vistaf_set_err("null argument", cudaErrorInvalidValue, __FILE__, __LINE__);
   const int np = 2 * (P->patch_half < 3 ? 3 : P->patch_half) + 1;
   if (np > NPATCH_MAX || P->crop_w > CH_THREADS * CH_MAXPT || (P->dilate_kernel | 1) > MORPH_MAXROWS ||
-      (P->close_kernel | 1) > MORPH_MAXROWS || P->edge_margin > 15 || P->bad_inpaint_radius < 1 || P->bad_inpaint_radius > 8)
+      (P->close_kernel | 1) > MORPH_MAXROWS || P->edge_margin > 15 || P->crop_w < 256 ||
+      (long long)P->crop_w * P->crop_h >= (1ll << 24) || P->bad_inpaint_radius < 1 || P->bad_inpaint_radius > 8)
     return vistaf_set_err("unsupported FTP parameters", cudaErrorInvalidValue, __FILE__, __LINE__);
   VistafFtpPlan* p = new (std::nothrow) VistafFtpPlan();
   if (!p) return vistaf_set_err("out of host memory", cudaErrorMemoryAllocation, __FILE__, __LINE__);
@@ -1232,7 +1251,7 @@ template <bool ORDER2>
 static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, SelectState* sel, int nb, int mode,
                     cudaStream_t st) {
   const int npix = p->h * p->w;
-  const FitGeom g{p->w, (float)((p->w - 1) / 2.0), (float)((p->h - 1) / 2.0)};
+  const FitGeom g{p->w, (float)((p->w - 1) / 2.0), (float)((p->h - 1) / 2.0), (unsigned int)(((1ull << 40) + p->w - 1) / p->w)};
   VL(), k_irls_begin<<<nb, 1, 0, st>>>(sc, mode);
   for (int it = 0; it < 6; it++) {
     VL(), k_irls_accum<ORDER2><<<dim3(64, nb), 256, 0, st>>>(z, fm, sc, g, npix, it);
@@ -1271,7 +1290,7 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   FtpScal* sc = (FtpScal*)(ws + L.scal);
   SelectState* sel = (SelectState*)(ws + L.sel);
   float* out = O.height_mm + f0 * (size_t)npix;
-  const FitGeom g{w, (float)((w - 1) / 2.0), (float)((h - 1) / 2.0)};
+  const FitGeom g{w, (float)((w - 1) / 2.0), (float)((h - 1) / 2.0), (unsigned int)(((1ull << 40) + w - 1) / w)};
   const dim3 gpix(cdiv(npix, 256), nb);
 
   // ---- A: demodulation

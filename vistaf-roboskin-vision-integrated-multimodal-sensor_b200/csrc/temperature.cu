@@ -749,7 +749,7 @@ static void temp_layout(const VistafTempPlan* p, int chunk, TempWs& L) {
   L.m2 = take(c * npix);
   L.cand = take(c * (size_t)p->nblk_cols * TOPK * sizeof(Cand));
   L.scal = take(c * sizeof(TempScal));
-  L.sel = take(c * sizeof(SelectState));
+  L.sel = take(sel_ws_bytes((int)c));
   L.total = o;
 }
 
