@@ -40,6 +40,7 @@ struct FtpScal {                  // per-frame scalars in the workspace
   float coef[6];
   float sigma, med;               // IRLS scale / location
   int irls_n, irls_skip;
+  unsigned int irls_ticket, nc;     // nc: samples in the compacted list of the current fit
   float hi_thr, grad_thr, mu, amp_thr, contact_thr, bg_med, core_thr, core_med, q2;
   ull seed_key;                   // (quality key << 32) | ~index
   ull best_cc;                    // (area << 32) | ~root
@@ -161,10 +162,7 @@ struct PlaneStore {
 };
 
 enum { G_HI = 0, G_GRAD, G_MU, G_AMP, G_CONTACT, G_BGMED, G_CORETHR, G_COREMED, G_IRLS_MED, G_IRLS_MAD, G_CONTACT2 };
-__global__ void k_ftp_grab(FtpScal* sc, const SelectState* sel, int which) {   // copy a finished quantile into its slot
-  FtpScal& s = sc[blockIdx.x];
-  const float r = sel[blockIdx.x].result;
-  const unsigned int cnt = sel[blockIdx.x].count;
+__device__ __forceinline__ void ftp_grab(FtpScal& s, int which, float r, unsigned int cnt) {   // a finished quantile -> its slot
   switch (which) {
     case G_HI: s.hi_thr = cnt ? r : 255.0f; break;                           // shape_ftp.py:630
     case G_GRAD: s.grad_thr = cnt ? r : 0.0f; break;                         // :640
@@ -178,6 +176,16 @@ __global__ void k_ftp_grab(FtpScal* sc, const SelectState* sel, int which) {   /
     case G_IRLS_MED: s.med = r; break;
     case G_IRLS_MAD: s.sigma = __fmul_rn(1.4826f, __fadd_rn(r, 1e-6f)); break;
   }
+}
+struct GrabOut {                 // output functor of select_quantile_out: runs on thread 0 of the finishing block
+  FtpScal* sc; int which;
+  __device__ void operator()(int b, float r, unsigned int cnt) const { ftp_grab(sc[b], which, r, cnt); }
+};
+// select + grab in one call (lists behind the `batch` states of `sel`)
+template <class Val>
+static int select_grab(Val val, FtpScal* sc, int which, SelectState* sel, long long n, int batch, float q, cudaStream_t st,
+                       const float* qv = nullptr, size_t qstride = 0) {
+  return select_quantile_out(val, GrabOut{sc, which}, sel, sel_lists(sel, batch), n, batch, q, st, qv, qstride);
 }
 
 // ------------------------------------------------------------------ F2: bad pixels (shape_ftp.py:625-649)
@@ -558,79 +566,50 @@ struct FitMask {
   }
 };
 
-template <bool ORDER2>
-__global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ z, FitMask fm, FtpScal* sc, FitGeom g,
-                                                     int npix, int iter) {
-  constexpr int NC = ORDER2 ? 6 : 3, NV = NC * (NC + 1) / 2 + NC + 1;
-  __shared__ double sh[NV * 32];
-  const int b = blockIdx.y;
+// Compacted sample list of a fit: the pixels that pass the fit's mask and are finite, as (value, pixel index) pairs
+// in arbitrary order (every consumer is order independent: float64 sums by atomics, exact order statistics).  The
+// ~30 sweeps of a fit then stream two dense arrays instead of chasing mask -> sample through a 43 % empty plane.
+__global__ void __launch_bounds__(256) k_irls_compact(const float* __restrict__ z, FitMask fm, FtpScal* sc,
+                                                       float* __restrict__ zc, unsigned int* __restrict__ pc, int npix) {
+  const int b = blockIdx.y, lane = threadIdx.x & 31;
   if (sc[b].irls_skip) return;
-  float coef[6];
-#pragma unroll
-  for (int i = 0; i < 6; i++) coef[i] = sc[b].coef[i];
-  const float med = sc[b].med;
-  const float cs = __fmul_rn(IRLS_C, sc[b].sigma);
-  (void)med;
-  double acc[NV];
-#pragma unroll
-  for (int i = 0; i < NV; i++) acc[i] = 0.0;
-  // four pixels per thread and trip: the mask bytes and samples of all four are loaded before any is used
-  for (int i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4; i0 < npix; i0 += gridDim.x * blockDim.x * 4) {
-    bool in[4];
-    float z4[4];
+  const size_t o = (size_t)b * npix;
+  const int stride = gridDim.x * 1024;
+  for (int i0 = blockIdx.x * 1024 + (threadIdx.x & ~31) * 4; i0 < npix; i0 += stride) {
+    bool ok[4];
+    float zz[4];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
-      const int i = i0 + j;
-      in[j] = i < npix && fm(b, i);
-      z4[j] = i < npix ? z[(size_t)b * npix + i] : 0.f;
+      const int i = i0 + j * 32 + lane;
+      zz[j] = i < npix ? z[o + i] : 0.f;
+      ok[j] = i < npix && fm(b, i) && fabsf(zz[j]) <= 3.4e38f;
     }
 #pragma unroll
     for (int j = 0; j < 4; j++) {
-      const int i = i0 + j;
-      const float zz = z4[j];
-      if (!in[j] || !(fabsf(zz) <= 3.4e38f)) continue;
-      float xn, yn;
-      g.norm(i, xn, yn);
-      float wt = 1.0f;
-      if (iter > 0) {
-        const float r = __fsub_rn(zz, poly_fit(coef, xn, yn, ORDER2));
-        const float u = __fdiv_rn(r, cs);
-        wt = __fdiv_rn(1.0f, __fadd_rn(1.0f, __fmul_rn(u, u)));
+      const unsigned int bits = __ballot_sync(0xffffffffu, ok[j]);
+      if (!bits) continue;
+      unsigned int base = 0;
+      if (lane == 0) base = atomicAdd(&sc[b].nc, (unsigned int)__popc(bits));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (ok[j]) {
+        const unsigned int at = base + (unsigned int)__popc(bits & ((1u << lane) - 1u));
+        zc[o + at] = zz[j];
+        pc[o + at] = (unsigned int)(i0 + j * 32 + lane);
       }
-      const double w2 = (double)wt * (double)wt;
-      double a[NC];
-      a[0] = xn; a[1] = yn; a[2] = 1.0;
-      if (ORDER2) { a[3] = (double)__fmul_rn(xn, xn); a[4] = (double)__fmul_rn(xn, yn); a[5] = (double)__fmul_rn(yn, yn); }
-      int k = 0;
-#pragma unroll
-      for (int p = 0; p < NC; p++) {
-        const double wa = w2 * a[p];
-#pragma unroll
-        for (int q = p; q < NC; q++) acc[k++] += wa * a[q];
-      }
-#pragma unroll
-      for (int p = 0; p < NC; p++) acc[k++] += w2 * a[p] * (double)zz;
-      acc[k] += 1.0;
     }
   }
-  block_sum<NV>(acc, sh);
-  if (threadIdx.x == 0)
-    for (int i = 0; i < NV; i++)
-      if (acc[i] != 0.0) atomicAdd(&sc[b].ne[i], acc[i]);
 }
 
 // Solve the normal equations (Gaussian elimination with partial pivoting, float64), store float32 coefficients.
 template <bool ORDER2>
-__global__ void k_irls_solve(FtpScal* sc, int iter) {
+__device__ void irls_solve_dev(FtpScal& s, int iter) {
   constexpr int NC = ORDER2 ? 6 : 3, NT = NC * (NC + 1) / 2;
-  FtpScal& s = sc[blockIdx.x];
-  if (s.irls_skip) return;
   double A[NC][NC + 1];
   int k = 0;
   for (int p = 0; p < NC; p++)
-    for (int q = p; q < NC; q++) { A[p][q] = s.ne[k]; A[q][p] = s.ne[k]; k++; }
-  for (int p = 0; p < NC; p++) A[p][NC] = s.ne[NT + p];
-  const int n = (int)(s.ne[NT + NC] + 0.5);
+    for (int q = p; q < NC; q++) { const double v = __ldcg(&s.ne[k]); A[p][q] = v; A[q][p] = v; k++; }
+  for (int p = 0; p < NC; p++) A[p][NC] = __ldcg(&s.ne[NT + p]);
+  const int n = (int)(__ldcg(&s.ne[NT + NC]) + 0.5);
   for (int i = 0; i < 28; i++) s.ne[i] = 0.0;
   if (iter == 0) {
     s.irls_n = n;
@@ -660,27 +639,96 @@ __global__ void k_irls_solve(FtpScal* sc, int iter) {
   }
   for (int i = 0; i < 6; i++) s.coef[i] = i < NC ? (float)x[i] : 0.f;
 }
+
+template <bool ORDER2>
+__global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ zc, const unsigned int* __restrict__ pc, FtpScal* sc,
+                                                     FitGeom g, int npix, int iter) {
+  constexpr int NC = ORDER2 ? 6 : 3, NV = NC * (NC + 1) / 2 + NC + 1;
+  __shared__ double sh[NV * 32];
+  const int b = blockIdx.y;
+  if (sc[b].irls_skip) return;
+  float coef[6];
+#pragma unroll
+  for (int i = 0; i < 6; i++) coef[i] = sc[b].coef[i];
+  const float cs = __fmul_rn(IRLS_C, sc[b].sigma);
+  const int n = (int)sc[b].nc;
+  const size_t o = (size_t)b * npix;
+  double acc[NV];
+#pragma unroll
+  for (int i = 0; i < NV; i++) acc[i] = 0.0;
+  // four samples per thread and trip, all eight loads issued before any is used
+  for (int j0 = blockIdx.x * 1024 + threadIdx.x; j0 < n; j0 += gridDim.x * 1024) {
+    float z4[4];
+    unsigned int p4[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int jj = j0 + j * 256;
+      z4[j] = jj < n ? zc[o + jj] : 0.f;
+      p4[j] = jj < n ? pc[o + jj] : 0u;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      if (j0 + j * 256 >= n) continue;
+      const float zz = z4[j];
+      float xn, yn;
+      g.norm((int)p4[j], xn, yn);
+      float wt = 1.0f;
+      if (iter > 0) {
+        const float r = __fsub_rn(zz, poly_fit(coef, xn, yn, ORDER2));
+        const float u = __fdiv_rn(r, cs);
+        wt = __fdiv_rn(1.0f, __fadd_rn(1.0f, __fmul_rn(u, u)));
+      }
+      const double w2 = (double)wt * (double)wt;
+      double a[NC];
+      a[0] = xn; a[1] = yn; a[2] = 1.0;
+      if (ORDER2) { a[3] = (double)__fmul_rn(xn, xn); a[4] = (double)__fmul_rn(xn, yn); a[5] = (double)__fmul_rn(yn, yn); }
+      int k = 0;
+#pragma unroll
+      for (int p = 0; p < NC; p++) {
+        const double wa = w2 * a[p];
+#pragma unroll
+        for (int q = p; q < NC; q++) acc[k++] += wa * a[q];
+      }
+#pragma unroll
+      for (int p = 0; p < NC; p++) acc[k++] += w2 * a[p] * (double)zz;
+      acc[k] += 1.0;
+    }
+  }
+  block_sum<NV>(acc, sh);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < NV; i++)
+      if (acc[i] != 0.0) atomicAdd(&sc[b].ne[i], acc[i]);
+    __threadfence();
+    if (atomicAdd(&sc[b].irls_ticket, 1u) == gridDim.x - 1) {      // last block of this frame: solve
+      __threadfence();
+      sc[b].irls_ticket = 0;
+      irls_solve_dev<ORDER2>(sc[b], iter);
+    }
+  }
+}
+
 __global__ void k_irls_begin(FtpScal* sc, int mode) {    // mode 0: plane on reliable, 1: quadric on reliable, 2: quadric on background
   FtpScal& s = sc[blockIdx.x];
   for (int i = 0; i < 28; i++) s.ne[i] = 0.0;
   for (int i = 0; i < 6; i++) s.coef[i] = 0.f;
   s.sigma = 1.f; s.med = 0.f;
   s.irls_skip = 0;
+  s.irls_ticket = 0;
+  s.nc = 0;
   if (mode == 0) {
     s.detrend1 = s.n_rel >= 500 ? 1 : 0;                 // shape_ftp.py:1379
     if (!s.detrend1) s.irls_skip = 1;
   }
 }
-// residual stream of the current fit: r (mode 0) or |r - med| (mode 1)
+// residual stream of the current fit over its compacted samples: r (mode 0) or |r - med| (mode 1)
 template <bool ORDER2>
 struct ResidVal {
-  const float* z; FitMask fm; const FtpScal* sc; FitGeom g; long long plane; int mode;
-  __device__ bool operator()(int b, long long i, float& v) const {
-    if (sc[b].irls_skip || !fm(b, i)) return false;
-    const float zz = z[(long long)b * plane + i];
-    if (!(fabsf(zz) <= 3.4e38f)) return false;
+  const float* zc; const unsigned int* pc; const FtpScal* sc; FitGeom g; long long plane; int mode;
+  __device__ long long limit(int b) const { return (long long)sc[b].nc; }
+  __device__ bool operator()(int b, long long j, float& v) const {
+    const float zz = zc[(long long)b * plane + j];
     float xn, yn;
-    g.norm((int)i, xn, yn);
+    g.norm((int)pc[(long long)b * plane + j], xn, yn);
     const float r = __fsub_rn(zz, poly_fit(sc[b].coef, xn, yn, ORDER2));
     v = mode ? fabsf(__fsub_rn(r, sc[b].med)) : r;
     return true;
@@ -1128,14 +1176,13 @@ static int ftp_preprocess(VistafFtpPlan* p, const uint8_t* gray, int nb, char* w
   float* tmp = (float*)(ws + L.tmp); float* I = (float*)(ws + L.I); float* Iw = (float*)(ws + L.Iw);
   FtpScal* sc = (FtpScal*)(ws + L.scal);
   SelectState* sel = (SelectState*)(ws + L.sel);
+  if (sel_reset(sel, nb, st)) return 1;
   vistaf_stage_mark("F.sobel_percentiles_bad", st);
   VL(), k_ftp_init<<<cdiv(nb, 128), 128, 0, st>>>(sc, nb);
   VL(), k_ftp_sobel<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(gray, img, grad, h, w);
   CKL();
-  if (select_quantile(MaskedVal{img, p->valid, plane}, sel, npix, nb, P.bad_int_pct, true, st)) return 1;
-  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_HI);
-  if (select_quantile(MaskedVal{grad, p->valid, plane}, sel, npix, nb, P.bad_grad_pct, true, st)) return 1;
-  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_GRAD);
+  if (select_grab(MaskedVal{img, p->valid, plane}, sc, G_HI, sel, npix, nb, P.bad_int_pct, st)) return 1;
+  if (select_grab(MaskedVal{grad, p->valid, plane}, sc, G_GRAD, sel, npix, nb, P.bad_grad_pct, st)) return 1;
   BadLoad bl{img, grad, p->valid, sc, plane, w};
   if (P.bad_dilate > 1) {
     if (morph<true>(bl, PostId(), bad, h, w, nb, p->se_bad, st)) return 1;
@@ -1153,8 +1200,7 @@ static int ftp_preprocess(VistafFtpPlan* p, const uint8_t* gray, int nb, char* w
   if (gauss_blur(PlaneLoad{img, plane, w}, IllumStoreF{img, I, plane, w}, tmp, h, w, nb, p->g_illum, p->g_illum, st)) return 1;
   vistaf_stage_mark("F.preblur_apo_median", st);
   if (gauss_blur(PlaneLoad{I, plane, w}, ApoStore{p->apo, Iw, plane, w}, tmp, h, w, nb, p->g_pre, p->g_pre, st)) return 1;
-  if (select_quantile(MaskedVal{Iw, p->valid, plane}, sel, npix, nb, -1.0f, true, st)) return 1;
-  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_MU);
+  if (select_grab(MaskedVal{Iw, p->valid, plane}, sc, G_MU, sel, npix, nb, -1.0f, st)) return 1;
   CKL();
   return 0;
 }
@@ -1247,22 +1293,38 @@ extern "C" int vistaf_ftp_set_reference(VistafFtpPlan* p, const uint8_t* ref_gra
   return 0;
 }
 
+// The fit runs over groups of IRLS_GROUP frames: one group's samples and masks (7 MB per frame) stay resident in the
+// 126 MB L2 across the ~30 sweeps of the six iterations, so only the first sweep of a group reads HBM.  Per
+// iteration: accumulate (+ solve in the last block), median of the residuals, median of |r - med| (3 launches each).
+#define IRLS_GROUP 8
 template <bool ORDER2>
-static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, SelectState* sel, int nb, int mode,
-                    cudaStream_t st) {
+static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, SelectState* sel, float* zc, unsigned int* pc,
+                    int nb, int mode, cudaStream_t st) {
   const int npix = p->h * p->w;
   const FitGeom g{p->w, (float)((p->w - 1) / 2.0), (float)((p->h - 1) / 2.0), (unsigned int)(((1ull << 40) + p->w - 1) / p->w)};
+  unsigned int* lists = sel_lists(sel, nb);
   VL(), k_irls_begin<<<nb, 1, 0, st>>>(sc, mode);
-  for (int it = 0; it < 6; it++) {
-    VL(), k_irls_accum<ORDER2><<<dim3(64, nb), 256, 0, st>>>(z, fm, sc, g, npix, it);
-    VL(), k_irls_solve<ORDER2><<<nb, 1, 0, st>>>(sc, it);
-    if (it == 5) break;
-    ResidVal<ORDER2> rv{z, fm, sc, g, (long long)npix, 0};
-    if (select_quantile(rv, sel, npix, nb, -1.0f, true, st)) return 1;
-    VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_IRLS_MED);
-    rv.mode = 1;
-    if (select_quantile(rv, sel, npix, nb, -1.0f, false, st)) return 1;
-    VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_IRLS_MAD);
+  for (int g0 = 0; g0 < nb; g0 += IRLS_GROUP) {
+    const int ng = nb - g0 < IRLS_GROUP ? nb - g0 : IRLS_GROUP;
+    const float* zg = z + (size_t)g0 * npix;
+    float* zcg = zc + (size_t)g0 * npix;
+    unsigned int* pcg = pc + (size_t)g0 * npix;
+    FtpScal* scg = sc + g0;
+    SelectState* selg = sel + g0;
+    unsigned int* listg = lists + (size_t)g0 * SEL_CAP;
+    FitMask fmg = fm;
+    fmg.rel += (size_t)g0 * fm.plane; fmg.contact_d += (size_t)g0 * fm.plane; fmg.sc = scg;
+    int gx = (148 * 4 + ng - 1) / ng;
+    if (gx > 128) gx = 128;
+    VL(), k_irls_compact<<<dim3(gx, ng), 256, 0, st>>>(zg, fmg, scg, zcg, pcg, npix);
+    for (int it = 0; it < 6; it++) {
+      VL(), k_irls_accum<ORDER2><<<dim3(gx, ng), 256, 0, st>>>(zcg, pcg, scg, g, npix, it);
+      if (it == 5) break;
+      ResidVal<ORDER2> rv{zcg, pcg, scg, g, (long long)npix, 0};
+      if (select_quantile_out(rv, GrabOut{scg, G_IRLS_MED}, selg, listg, npix, ng, -1.0f, st)) return 1;
+      rv.mode = 1;
+      if (select_quantile_out(rv, GrabOut{scg, G_IRLS_MAD}, selg, listg, npix, ng, -1.0f, st)) return 1;
+    }
   }
   CKL();
   return 0;
@@ -1299,8 +1361,7 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   vistaf_stage_mark("F.quality_reliable_mask", st);
   // ---- B: reliable mask
   if (gauss_blur(PlaneLoad{qprod, plane, w}, PlaneStore{quality, plane, w}, tmp, h, w, nb, p->g_qual, p->g_qual, st)) return 1;
-  if (select_quantile(MaskedVal{quality, p->roi, plane}, sel, npix, nb, P.amp_percentile, true, st)) return 1;
-  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_AMP);
+  if (select_grab(MaskedVal{quality, p->roi, plane}, sc, G_AMP, sel, npix, nb, P.amp_percentile, st)) return 1;
   RelRawLoad rl{quality, p->roi, sc, plane, w};
   if (morph<true>(rl, PostId(), m1, h, w, nb, p->se_close, st)) return 1;                       // close = dilate, erode
   if (morph<false>(MaskLoad{m1, plane, w}, PostAnd{p->roi, 0, w}, m2, h, w, nb, p->se_close, st)) return 1;
@@ -1328,16 +1389,14 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   vistaf_stage_mark("F.irls_plane", st);
   // ---- D: plane removal, two-pass quadric detrend
   FitMask fm_rel{rel, contact_d, sc, plane, 0}, fm_bg{rel, contact_d, sc, plane, 1};
-  if (irls_fit<false>(p, unw, fm_rel, sc, sel, nb, 0, st)) return 1;
+  if (irls_fit<false>(p, unw, fm_rel, sc, sel, hnum, (unsigned int*)hm, nb, 0, st)) return 1;
   vistaf_stage_mark("F.irls_quadric_contact", st);
   VL(), k_ftp_sub_fit1<<<gpix, 256, 0, st>>>(unw, sc, g, npix);
-  if (irls_fit<true>(p, unw, fm_rel, sc, sel, nb, 1, st)) return 1;
-  if (select_quantile(AbsResVal{unw, rel, sc, g, plane, 0}, sel, npix, nb, P.contact_pct, true, st)) return 1;
-  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CONTACT);
+  if (irls_fit<true>(p, unw, fm_rel, sc, sel, hnum, (unsigned int*)hm, nb, 1, st)) return 1;
+  if (select_grab(AbsResVal{unw, rel, sc, g, plane, 0}, sc, G_CONTACT, sel, npix, nb, P.contact_pct, st)) return 1;
   VL(), k_ftp_contact<<<gpix, 256, 0, st>>>(unw, rel, sc, g, contact, npix, 1);
   VL(), k_ftp_contact_frac<<<nb, 1, 0, st>>>(sc, P.min_contact_frac, P.max_contact_frac);
-  if (select_quantile(AbsResVal{unw, rel, sc, g, plane, 1}, sel, npix, nb, 0.f, true, st, &sc[0].q2, sizeof(FtpScal))) return 1;
-  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CONTACT2);
+  if (select_grab(AbsResVal{unw, rel, sc, g, plane, 1}, sc, G_CONTACT2, sel, npix, nb, 0.f, st, &sc[0].q2, sizeof(FtpScal))) return 1;
   VL(), k_ftp_contact<<<gpix, 256, 0, st>>>(unw, rel, sc, g, contact, npix, 0);
   {
     const uint8_t* src = contact;
@@ -1355,18 +1414,15 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   VL(), k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(contact_d, sc, npix, 3);
   VL(), k_ftp_bg_decide<<<nb, 1, 0, st>>>(sc);
   vistaf_stage_mark("F.irls_quadric_background", st);
-  if (irls_fit<true>(p, unw, fm_bg, sc, sel, nb, 2, st)) return 1;
-  if (select_quantile(DetVal{unw, fm_bg, sc, g, plane}, sel, npix, nb, -1.0f, true, st)) return 1;
-  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_BGMED);
+  if (irls_fit<true>(p, unw, fm_bg, sc, sel, hnum, (unsigned int*)hm, nb, 2, st)) return 1;
+  if (select_grab(DetVal{unw, fm_bg, sc, g, plane}, sc, G_BGMED, sel, npix, nb, -1.0f, st)) return 1;
   CKL();
   vistaf_stage_mark("F.smooth_sign", st);
   // ---- E: masked smoothing (sigma 2.5) and sign
   if (gauss_blur(HmNumLoad{unw, rel, sc, g, plane, w}, PlaneStore{hnum, plane, w}, tmp, h, w, nb, p->g_smooth, p->g_smooth, st)) return 1;
   if (gauss_blur(HmDenLoad{unw, rel, plane, w}, RatioStore{hnum, hm, plane, w}, tmp, h, w, nb, p->g_smooth, p->g_smooth, st)) return 1;
-  if (select_quantile(MaskedValB{hm, rel, plane}, sel, npix, nb, P.core_pct, true, st)) return 1;
-  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_CORETHR);
-  if (select_quantile(CoreVal{hm, rel, sc, plane}, sel, npix, nb, -1.0f, true, st)) return 1;
-  VL(), k_ftp_grab<<<nb, 1, 0, st>>>(sc, sel, G_COREMED);
+  if (select_grab(MaskedValB{hm, rel, plane}, sc, G_CORETHR, sel, npix, nb, P.core_pct, st)) return 1;
+  if (select_grab(CoreVal{hm, rel, sc, plane}, sc, G_COREMED, sel, npix, nb, -1.0f, st)) return 1;
   CKL();
   vistaf_stage_mark("F.chamfer_frontier_assemble", st);
   // ---- F: frontier taper, assembly, sigma-9 fill of the unreliable part, phase -> mm

@@ -3,14 +3,16 @@
 // residuals / masked planes are never materialised:
 //     struct Val { __device__ bool operator()(int b, long long i, float& v) const; };   // false = skip
 //
-// Two sweeps of the data in the common case:
-//   S1  2048-bin histogram of the top 11 key bits (also yields the element count);
-//   P1  locate the bin of rank k and the bin of rank k+1 (numpy interpolates between the two);
-//   S2  gather the keys of those one or two bins into a per-frame list (warp-aggregated append);
-//   P2  one block per frame selects ranks k, k+1 inside the list exactly and interpolates.
-// If the bins hold more keys than the list can take (heavily duplicated data), the same launches fall through to
-// MSB radix selection: S2 / S3 become 11- and 10-bit histogram sweeps under the fixed prefix and S4 is a
-// neighbour sweep for rank k+1; on the gather path S3 / S4 exit at once.
+// Three launches, two sweeps of the data:
+//   S1  2048-bin histogram of the top 11 key bits; the LAST block of a frame to finish (ticket counter) counts
+//       the elements, locates the bin b1 of rank k and decides gather (bin fits the list) or radix;
+//   S2  keys of bin b1: 2048-bin histogram of key bits [20:10] and (gather mode) warp-aggregated append to the
+//       per-frame list; when rank k+1 lies above bin b1, the smallest key above the bin is tracked by atomicMin;
+//   P2  one block of 1024 threads per frame: sub-bin of rank k, then the last 10 key bits from one pass over the
+//       list (gather) or over the frame's values (radix mode: heavily duplicated data), rank k+1 from the same
+//       histograms, numpy's float32 interpolation, result handed to an output functor, state cleaned.
+// Invariant between selections: hist = 0, nlist = 0, ticket = 0, min_next = ~0 (sel_reset establishes it once per
+// workspace; P2 restores it).
 #pragma once
 #include "common.cuh"
 
@@ -21,15 +23,17 @@ struct SelectState {           // one per frame, device memory
   unsigned int hist[SEL_BINS];
   unsigned int count;          // number of valid elements
   unsigned int k;              // rank of the lower neighbour (0-based)
-  unsigned int mode;           // 0 = done / empty, 1 = gather, 2 = radix
-  unsigned int b1, b1n;        // level-1 bin of rank k and of rank k+1
+  unsigned int mode;           // 0 = empty / inactive, 1 = gather, 2 = radix
+  unsigned int b1;             // level-1 bin of rank k
   unsigned int below;          // elements in bins below b1
+  unsigned int inbin;          // elements in bin b1
   unsigned int nlist;          // keys gathered
-  unsigned int prefix, krem;   // radix path: key bits fixed so far, rank inside the current bucket
-  unsigned int cnt_le, min_gt; // radix path, neighbour sweep
+  unsigned int ticket;         // blocks of S1 that have flushed
+  unsigned int min_next;       // smallest key in bins above b1 (tracked when rank k+1 is not in b1)
+  unsigned int need_next;
   float vk, vk1;               // k-th and (k+1)-th smallest
   float result;                // interpolated quantile (float32, numpy lerp)
-  unsigned int pad_[2];
+  unsigned int pad_[3];
 };
 
 static inline size_t sel_ws_bytes(int chunk) { return (size_t)chunk * (sizeof(SelectState) + (size_t)SEL_CAP * 4); }
@@ -61,44 +65,38 @@ __device__ __forceinline__ void sel_interpolate(SelectState& s, float q) {
   s.result = r;
 }
 
+
+// Optional per-frame element count of a value functor (`long long limit(int b) const`): sweeps stop there.
+template <class V>
+__device__ __forceinline__ auto sel_limit(const V& v, int b, long long n, int) -> decltype(v.limit(b)) {
+  const long long l = v.limit(b);
+  return l < n ? l : n;
+}
+template <class V>
+__device__ __forceinline__ long long sel_limit(const V&, int, long long n, long) { return n; }
+
 static __global__ void k_sel_zero(SelectState* st) {
   SelectState& s = st[blockIdx.x];
   for (int i = threadIdx.x; i < SEL_BINS; i += blockDim.x) s.hist[i] = 0;
   if (threadIdx.x == 0) {
-    s.count = 0; s.k = 0; s.mode = 0; s.b1 = s.b1n = 0; s.below = 0; s.nlist = 0; s.prefix = 0; s.krem = 0;
-    s.cnt_le = 0; s.min_gt = 0xffffffffu;
+    s.count = 0; s.k = 0; s.mode = 0; s.b1 = 0; s.below = 0; s.inbin = 0; s.nlist = 0; s.ticket = 0;
+    s.min_next = 0xffffffffu; s.need_next = 0;
   }
 }
-
-// ---- S1: level-1 histogram (top 11 bits).  Consecutive lanes often fall into the same bin; shared-memory atomics
-// serialise only on equal addresses, and the per-block histogram is flushed once.
-template <class Val>
-__global__ void __launch_bounds__(256) k_sel_s1(Val val, SelectState* st, long long n) {
-  __shared__ unsigned int h[SEL_BINS];
-  const int b = blockIdx.y;
-  for (int i = threadIdx.x; i < SEL_BINS; i += blockDim.x) h[i] = 0;
-  __syncthreads();
-  // four independent element fetches are in flight before the first histogram update (the value functors are
-  // chains of dependent loads: mask byte, then sample)
-  for (long long i0 = (long long)blockIdx.x * blockDim.x * 4 + threadIdx.x; i0 < n; i0 += (long long)gridDim.x * blockDim.x * 4) {
-    float v[4];
-    bool ok[4];
-#pragma unroll
-    for (int j = 0; j < 4; j++) { const long long i = i0 + (long long)j * blockDim.x; ok[j] = i < n && val(b, i, v[j]); }
-#pragma unroll
-    for (int j = 0; j < 4; j++) if (ok[j]) atomicAdd(&h[f2key(v[j]) >> 21], 1u);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < SEL_BINS; i += blockDim.x)
-    if (h[i]) atomicAdd(&st[b].hist[i], h[i]);
+// establishes the between-selections invariant for `batch` states (once per workspace use)
+static inline int sel_reset(SelectState* st, int batch, cudaStream_t stream) {
+  VL(), k_sel_zero<<<batch, 256, 0, stream>>>(st);
+  CKL();
+  return 0;
 }
 
-// Block-wide search of the bin holding 0-based rank `r` in hist[0..SEL_BINS): returns (bin, elements below it)
-// to every thread.  NT threads, NT | SEL_BINS, NT a multiple of 32 and <= 1024.  sh: >= 34 unsigned ints.
-template <int NT>
+// Block-wide search of the bin holding 0-based rank `r` in hist[0..NB): returns (bin, elements below it)
+// to every thread.  NT threads, NT | NB, NT a multiple of 32 and <= 1024.  sh: >= 34 unsigned ints.
+// If r >= total, bin = 0xffffffff.
+template <int NT, int NB>
 __device__ __forceinline__ void sel_find_bin(const unsigned int* hist, unsigned int r, unsigned int* sh, unsigned int& bin,
                                              unsigned int& below) {
-  constexpr int PER = SEL_BINS / NT;
+  constexpr int PER = NB / NT;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   unsigned int loc[PER], sum = 0;
 #pragma unroll
@@ -108,6 +106,7 @@ __device__ __forceinline__ void sel_find_bin(const unsigned int* hist, unsigned 
   for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
   __syncthreads();
   if (lane == 31) sh[wid] = inc;
+  if (tid == 0) { sh[32] = 0xffffffffu; sh[33] = 0; }
   __syncthreads();
   unsigned int wbase = 0;
   for (int w = 0; w < wid; w++) wbase += sh[w];
@@ -124,215 +123,236 @@ __device__ __forceinline__ void sel_find_bin(const unsigned int* hist, unsigned 
   bin = sh[32]; below = sh[33];
   __syncthreads();
 }
+// first non-empty bin strictly above `after` (0xffffffff if none).  sh: >= 1 unsigned int.
+template <int NT, int NB>
+__device__ __forceinline__ unsigned int sel_next_bin(const unsigned int* hist, unsigned int after, unsigned int* sh) {
+  __syncthreads();
+  if (threadIdx.x == 0) sh[0] = 0xffffffffu;
+  __syncthreads();
+  unsigned int best = 0xffffffffu;
+  for (unsigned int i = threadIdx.x; i < NB; i += NT)
+    if (i > after && hist[i] && i < best) best = i;
+  best = __reduce_min_sync(0xffffffffu, best);
+  if ((threadIdx.x & 31) == 0 && best != 0xffffffffu) atomicMin(&sh[0], best);
+  __syncthreads();
+  const unsigned int r = sh[0];
+  __syncthreads();
+  return r;
+}
 
-// ---- P1: count, ranks, level-1 bins; chooses gather or radix.
-static __global__ void __launch_bounds__(256) k_sel_p1(SelectState* st, float q0, const float* qv, size_t qstride) {
+// ---- S1: level-1 histogram (top 11 key bits) + rank location by the last block of each frame.
+template <class Val>
+__global__ void __launch_bounds__(256) k_sel_s1(Val val, SelectState* st, long long n, float q0, const float* qv,
+                                                size_t qstride) {
+  __shared__ unsigned int h[SEL_BINS];
   __shared__ unsigned int sh[34];
-  __shared__ unsigned int tot;
-  SelectState& s = st[blockIdx.x];
-  const float q = sel_q(q0, qv, qstride, blockIdx.x);
+  __shared__ unsigned int s_last;
+  const int b = blockIdx.y;
+  SelectState& s = st[b];
+  for (int i = threadIdx.x; i < SEL_BINS; i += 256) h[i] = 0;
+  __syncthreads();
+  n = sel_limit(val, b, n, 0);
+  // four independent element fetches are in flight before the first histogram update (the value functors are
+  // chains of dependent loads: mask byte, then sample)
+  for (long long i0 = (long long)blockIdx.x * 1024 + threadIdx.x; i0 < n; i0 += (long long)gridDim.x * 1024) {
+    float v[4];
+    bool ok[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) { const long long i = i0 + (long long)j * 256; ok[j] = i < n && val(b, i, v[j]); }
+#pragma unroll
+    for (int j = 0; j < 4; j++) if (ok[j]) atomicAdd(&h[f2key(v[j]) >> 21], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < SEL_BINS; i += 256)
+    if (h[i]) atomicAdd(&s.hist[i], h[i]);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(&s.ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+  __syncthreads();
+  if (!s_last) return;
+  // ---- last block of this frame: every other block's histogram is visible (fence + ticket)
+  __threadfence();
   unsigned int c = 0;
-  for (int i = threadIdx.x; i < SEL_BINS; i += 256) c += s.hist[i];
+  for (int i = threadIdx.x; i < SEL_BINS; i += 256) { const unsigned int x = __ldcg(&s.hist[i]); h[i] = x; c += x; s.hist[i] = 0; }
   c = (unsigned int)warp_sum((int)c);
-  if (threadIdx.x == 0) tot = 0;
+  if (threadIdx.x == 0) sh[0] = 0;
   __syncthreads();
-  if ((threadIdx.x & 31) == 0) atomicAdd(&tot, c);
+  if ((threadIdx.x & 31) == 0) atomicAdd(&sh[0], c);
   __syncthreads();
-  const unsigned int count = tot;
+  const unsigned int count = sh[0];
+  __syncthreads();
+  const float q = sel_q(q0, qv, qstride, b);
   if (count == 0 || q != q) {
-    if (threadIdx.x == 0) { s.count = count; s.mode = 0; }
+    if (threadIdx.x == 0) { s.count = count; s.mode = 0; s.ticket = 0; }
     return;
   }
   const unsigned int k = (unsigned int)floorf(sel_pos(count, q));
-  const unsigned int k1 = k + 1 < count ? k + 1 : k;
-  unsigned int b1, below, b1n, below_n;
-  sel_find_bin<256>(s.hist, k, sh, b1, below);
-  sel_find_bin<256>(s.hist, k1, sh, b1n, below_n);
-  const unsigned int need = s.hist[b1] + (b1n != b1 ? s.hist[b1n] : 0u);
-  const unsigned int mode = need <= (unsigned int)SEL_CAP ? 1u : 2u;
-  __syncthreads();
+  unsigned int b1, below;
+  sel_find_bin<256, SEL_BINS>(h, k, sh, b1, below);
   if (threadIdx.x == 0) {
-    s.count = count; s.k = k; s.b1 = b1; s.b1n = b1n; s.below = below; s.nlist = 0; s.mode = mode;
-    s.prefix = b1 << 21; s.krem = k - below;
+    const unsigned int inbin = h[b1];
+    s.count = count; s.k = k; s.b1 = b1; s.below = below; s.inbin = inbin; s.nlist = 0; s.ticket = 0;
+    s.mode = inbin <= (unsigned int)SEL_CAP ? 1u : 2u;
+    s.need_next = (k + 1 < count && k + 1 - below >= inbin) ? 1u : 0u;
+    s.min_next = 0xffffffffu;
   }
-  if (mode == 2) for (int i = threadIdx.x; i < SEL_BINS; i += 256) s.hist[i] = 0;
 }
 
-// ---- S2: gather the keys of bins b1 / b1n (mode 1), or histogram key bits [20:10] under the prefix (mode 2).
+// ---- S2: keys of bin b1 -> level-2 histogram (bits [20:10]) and, in gather mode, the per-frame list.
 template <class Val>
 __global__ void __launch_bounds__(256) k_sel_s2(Val val, SelectState* st, unsigned int* lists, long long n) {
   __shared__ unsigned int h[SEL_BINS];
   const int b = blockIdx.y, lane = threadIdx.x & 31;
-  const unsigned int mode = st[b].mode;
-  if (mode == 0) return;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  const long long start = (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31);
-  if (mode == 1) {
-    const unsigned int b1 = st[b].b1, b1n = st[b].b1n;
-    unsigned int* list = lists + (size_t)b * SEL_CAP;
-    for (long long i0 = start; i0 < n; i0 += 4 * stride) {
-      float v[4];
-      bool ok[4];
-#pragma unroll
-      for (int j = 0; j < 4; j++) { const long long i = i0 + j * stride + lane; ok[j] = i < n && val(b, i, v[j]); }
-#pragma unroll
-      for (int j = 0; j < 4; j++) {
-        unsigned int key = 0;
-        bool take = false;
-        if (ok[j]) { key = f2key(v[j]); const unsigned int bin = key >> 21; take = bin == b1 || bin == b1n; }
-        const unsigned int bits = __ballot_sync(0xffffffffu, take);
-        if (!bits) continue;
-        unsigned int base = 0;
-        if (lane == 0) base = atomicAdd(&st[b].nlist, (unsigned int)__popc(bits));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (take) {
-          const unsigned int at = base + (unsigned int)__popc(bits & ((1u << lane) - 1u));
-          if (at < (unsigned int)SEL_CAP) list[at] = key;
-        }
-      }
-    }
-    return;
-  }
-  for (int i = threadIdx.x; i < SEL_BINS; i += blockDim.x) h[i] = 0;
-  __syncthreads();
-  const unsigned int top = st[b].prefix >> 21;
-  for (long long i = start + lane; i < n; i += stride) {
-    float v;
-    if (val(b, i, v)) { const unsigned int key = f2key(v); if ((key >> 21) == top) atomicAdd(&h[(key >> 10) & 2047u], 1u); }
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < SEL_BINS; i += blockDim.x)
-    if (h[i]) atomicAdd(&st[b].hist[i], h[i]);
-}
-
-// exact key of 0-based rank r inside list[0..n) by three histogram levels (11 / 11 / 10 bits), one block of 1024
-__device__ __forceinline__ unsigned int sel_list_rank(const unsigned int* __restrict__ list, unsigned int n, unsigned int r,
-                                                      unsigned int* h, unsigned int* sh) {
-  unsigned int prefix = 0, himask = 0;
-  const int shifts[3] = {21, 10, 0};
-  const unsigned int masks[3] = {2047u, 2047u, 1023u};
-#pragma unroll
-  for (int lv = 0; lv < 3; lv++) {
-    for (int i = threadIdx.x; i < SEL_BINS; i += 1024) h[i] = 0;
-    __syncthreads();
-    for (unsigned int i = threadIdx.x; i < n; i += 1024) {
-      const unsigned int key = list[i];
-      if ((key & himask) == prefix) atomicAdd(&h[(key >> shifts[lv]) & masks[lv]], 1u);
-    }
-    __syncthreads();
-    unsigned int bin, below;
-    sel_find_bin<1024>(h, r, sh, bin, below);
-    r -= below;
-    prefix |= bin << shifts[lv];
-    himask |= masks[lv] << shifts[lv];
-  }
-  return prefix;
-}
-
-// ---- P2: mode 1: exact ranks k, k+1 inside the gathered list, interpolation (done).  mode 2: level-2 digit.
-static __global__ void __launch_bounds__(1024) k_sel_p2(SelectState* st, unsigned int* lists, float q0, const float* qv,
-                                                        size_t qstride) {
-  __shared__ unsigned int h[SEL_BINS];
-  __shared__ unsigned int sh[34];
-  SelectState& s = st[blockIdx.x];
+  SelectState& s = st[b];
   const unsigned int mode = s.mode;
   if (mode == 0) return;
-  if (mode == 1) {
-    const unsigned int* list = lists + (size_t)blockIdx.x * SEL_CAP;
-    const unsigned int n = min(s.nlist, (unsigned int)SEL_CAP);
-    const unsigned int r0 = s.k - s.below;
-    const unsigned int r1 = s.k + 1 < s.count ? r0 + 1 : r0;
-    const unsigned int k0 = sel_list_rank(list, n, r0, h, sh);
-    const unsigned int k1 = r1 == r0 ? k0 : sel_list_rank(list, n, r1, h, sh);
-    if (threadIdx.x == 0) {
-      s.vk = key2f(k0); s.vk1 = key2f(k1);
-      sel_interpolate(s, sel_q(q0, qv, qstride, blockIdx.x));
-      s.mode = 0;
+  const unsigned int b1 = s.b1;
+  const bool need_next = s.need_next != 0, gather = mode == 1;
+  unsigned int* list = lists + (size_t)b * SEL_CAP;
+  for (int i = threadIdx.x; i < SEL_BINS; i += 256) h[i] = 0;
+  __syncthreads();
+  unsigned int mn = 0xffffffffu;
+  n = sel_limit(val, b, n, 0);
+  // warp-uniform trip count (ballots inside): lanes of a warp walk consecutive elements
+  const long long stride = (long long)gridDim.x * 1024;
+  const long long start = (long long)blockIdx.x * 1024 + (threadIdx.x & ~31) * 4;
+  for (long long i0 = start; i0 < n; i0 += stride) {
+    float v[4];
+    bool ok[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) { const long long i = i0 + j * 32 + lane; ok[j] = i < n && val(b, i, v[j]); }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      unsigned int key = 0;
+      bool take = false;
+      if (ok[j]) {
+        key = f2key(v[j]);
+        const unsigned int bin = key >> 21;
+        take = bin == b1;
+        if (need_next && bin > b1) mn = min(mn, key);
+      }
+      if (take) atomicAdd(&h[(key >> 10) & 2047u], 1u);
+      if (!gather) continue;
+      const unsigned int bits = __ballot_sync(0xffffffffu, take);
+      if (!bits) continue;
+      unsigned int base = 0;
+      if (lane == 0) base = atomicAdd(&s.nlist, (unsigned int)__popc(bits));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (take) {
+        const unsigned int at = base + (unsigned int)__popc(bits & ((1u << lane) - 1u));
+        if (at < (unsigned int)SEL_CAP) list[at] = key;
+      }
     }
-    return;
   }
-  unsigned int bin, below;
-  sel_find_bin<1024>(s.hist, s.krem, sh, bin, below);
+  if (need_next) {
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    if (lane == 0 && mn != 0xffffffffu) atomicMin(&s.min_next, mn);
+  }
   __syncthreads();
-  if (threadIdx.x == 0) { s.krem -= below; s.prefix |= bin << 10; }
-  for (int i = threadIdx.x; i < SEL_BINS; i += 1024) s.hist[i] = 0;
+  for (int i = threadIdx.x; i < SEL_BINS; i += 256)
+    if (h[i]) atomicAdd(&s.hist[i], h[i]);
 }
 
-// ---- S3 (mode 2 only): histogram of the low 10 key bits under the 22-bit prefix.
-template <class Val>
-__global__ void __launch_bounds__(256) k_sel_s3(Val val, SelectState* st, long long n) {
-  __shared__ unsigned int h[1024];
-  const int b = blockIdx.y;
-  if (st[b].mode != 2) return;
-  for (int i = threadIdx.x; i < 1024; i += blockDim.x) h[i] = 0;
-  __syncthreads();
-  const unsigned int top = st[b].prefix >> 10;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    float v;
-    if (val(b, i, v)) { const unsigned int key = f2key(v); if ((key >> 10) == top) atomicAdd(&h[key & 1023u], 1u); }
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < 1024; i += blockDim.x)
-    if (h[i]) atomicAdd(&st[b].hist[i], h[i]);
-}
-// ---- P3 (mode 2 only): final digit -> v_k; rank k+1 is the same key when the final bin holds it too.
-static __global__ void __launch_bounds__(1024) k_sel_p3(SelectState* st) {
+struct SelNoOut { __device__ void operator()(int, float, unsigned int) const {} };
+
+// ---- P2: one block per frame finishes the selection (see the header).  Out: void operator()(int b, float result,
+// unsigned int count), called by thread 0.
+template <class Val, class Out>
+__global__ void __launch_bounds__(1024) k_sel_p2(Val val, Out out, SelectState* st, unsigned int* lists, long long n, float q0,
+                                                 const float* qv, size_t qstride) {
+  __shared__ unsigned int h3[1024];
   __shared__ unsigned int sh[34];
-  SelectState& s = st[blockIdx.x];
-  if (s.mode != 2) return;
-  unsigned int bin, below;
-  sel_find_bin<1024>(s.hist, s.krem, sh, bin, below);
+  __shared__ unsigned int s_min;
+  const int b = blockIdx.x;
+  SelectState& s = st[b];
+  const unsigned int mode = s.mode;
+  const float q = sel_q(q0, qv, qstride, b);
+  if (mode == 0) {
+    if (threadIdx.x == 0) { sel_interpolate(s, q); out(b, s.result, s.count); s.min_next = 0xffffffffu; s.need_next = 0; }
+    return;                                             // S1 left hist / nlist / ticket clean
+  }
+  n = sel_limit(val, b, n, 0);
+  const unsigned int* list = lists + (size_t)b * SEL_CAP;
+  const unsigned int nl = min(s.nlist, (unsigned int)SEL_CAP);
+  const unsigned int count = s.count, k = s.k, b1 = s.b1, inbin = s.inbin;
+  const unsigned int r0 = k - s.below;                  // rank inside bin b1
+  unsigned int sb, below2;
+  sel_find_bin<1024, SEL_BINS>(s.hist, r0, sh, sb, below2);
+  const unsigned int p22 = (b1 << 11) | sb;
+  h3[threadIdx.x] = 0;
+  __syncthreads();
+  if (mode == 1) {
+    for (unsigned int i = threadIdx.x; i < nl; i += 1024) {
+      const unsigned int key = list[i];
+      if ((key >> 10) == p22) atomicAdd(&h3[key & 1023u], 1u);
+    }
+  } else {
+    for (long long i = threadIdx.x; i < n; i += 1024) {
+      float v;
+      if (val(b, i, v)) { const unsigned int key = f2key(v); if ((key >> 10) == p22) atomicAdd(&h3[key & 1023u], 1u); }
+    }
+  }
+  __syncthreads();
+  const unsigned int r = r0 - below2;                   // rank inside the sub-bin
+  unsigned int lo, below3;
+  sel_find_bin<1024, 1024>(h3, r, sh, lo, below3);
+  const unsigned int key0 = (p22 << 10) | lo;
+  unsigned int key1 = key0;
+  if (k + 1 < count) {
+    const unsigned int insub = s.hist[sb];
+    if (r + 1 - below3 < h3[lo]) key1 = key0;                                   // duplicate of the same key
+    else if (r + 1 < insub) key1 = (p22 << 10) | sel_next_bin<1024, 1024>(h3, lo, sh);
+    else if (r0 + 1 < inbin) {                                                  // first key of the next sub-bin of b1
+      const unsigned int sb2 = sel_next_bin<1024, SEL_BINS>(s.hist, sb, sh);
+      const unsigned int p2 = (b1 << 11) | sb2;
+      if (threadIdx.x == 0) s_min = 0xffffffffu;
+      __syncthreads();
+      unsigned int mn = 0xffffffffu;
+      if (mode == 1) {
+        for (unsigned int i = threadIdx.x; i < nl; i += 1024) { const unsigned int key = list[i]; if ((key >> 10) == p2) mn = min(mn, key); }
+      } else {
+        for (long long i = threadIdx.x; i < n; i += 1024) {
+          float v;
+          if (val(b, i, v)) { const unsigned int key = f2key(v); if ((key >> 10) == p2) mn = min(mn, key); }
+        }
+      }
+      mn = __reduce_min_sync(0xffffffffu, mn);
+      if ((threadIdx.x & 31) == 0 && mn != 0xffffffffu) atomicMin(&s_min, mn);
+      __syncthreads();
+      key1 = s_min;
+    } else key1 = s.min_next;                                                   // first key above bin b1
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < SEL_BINS; i += 1024) s.hist[i] = 0;
   if (threadIdx.x == 0) {
-    s.prefix |= bin;
-    s.vk = key2f(s.prefix);
-    const unsigned int inbin = s.hist[bin], r = s.krem - below;
-    if (r + 1 < inbin || s.k + 1 >= s.count) { s.vk1 = s.vk; s.mode = 3; }      // 3 = radix path, neighbour known
+    s.vk = key2f(key0); s.vk1 = key2f(key1);
+    sel_interpolate(s, q);
+    out(b, s.result, count);
+    s.mode = 0; s.nlist = 0; s.min_next = 0xffffffffu; s.need_next = 0;
   }
-}
-// ---- S4 (mode 2 only): smallest key above v_k.
-template <class Val>
-__global__ void __launch_bounds__(256) k_sel_s4(Val val, SelectState* st, long long n) {
-  const int b = blockIdx.y;
-  if (st[b].mode != 2) return;
-  const unsigned int kk = st[b].prefix;
-  unsigned int mg = 0xffffffffu;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    float v;
-    if (val(b, i, v)) { const unsigned int key = f2key(v); if (key > kk) mg = min(mg, key); }
-  }
-  mg = __reduce_min_sync(0xffffffffu, mg);
-  if ((threadIdx.x & 31) == 0 && mg != 0xffffffffu) atomicMin(&st[b].min_gt, mg);
-}
-static __global__ void k_sel_finish(SelectState* st, float q0, const float* qv, size_t qstride) {
-  SelectState& s = st[blockIdx.x];
-  const float q = sel_q(q0, qv, qstride, blockIdx.x);
-  if (s.count == 0 || q != q) { sel_interpolate(s, q); return; }
-  if (s.mode == 2) s.vk1 = s.min_gt == 0xffffffffu ? s.vk : key2f(s.min_gt);
-  if (s.mode == 2 || s.mode == 3) { sel_interpolate(s, q); s.mode = 0; }
 }
 
-// Host: full selection of quantile q (percent; q < 0 = median) for `batch` frames over n candidates each.  The
-// per-frame key lists live right behind the `batch` states (sel_ws_bytes).  `need_count` is kept for call-site
-// compatibility: the count always comes from the first sweep.
+// Host: selection of quantile q (percent; q < 0 = median) for `batch` frames over n candidates each.
+// `lists`: batch * SEL_CAP keys.  The result lands in st[b].result / st[b].count and in `out`.
+template <class Val, class Out>
+static int select_quantile_out(Val val, Out out, SelectState* st, unsigned int* lists, long long n, int batch, float q,
+                               cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0) {
+  int gx = (148 * 6 + batch - 1) / batch;
+  const int gmax = (int)((n + 1023) / 1024);
+  if (gx > gmax) gx = gmax;
+  if (gx > 592) gx = 592;
+  if (gx < 1) gx = 1;
+  dim3 grid(gx, batch);
+  VL(), k_sel_s1<Val><<<grid, 256, 0, stream>>>(val, st, n, q, qv, qstride);
+  VL(), k_sel_s2<Val><<<grid, 256, 0, stream>>>(val, st, lists, n);
+  VL(), k_sel_p2<Val, Out><<<batch, 1024, 0, stream>>>(val, out, st, lists, n, q, qv, qstride);
+  CKL();
+  return 0;
+}
+// call-site compatible form: the key lists live right behind the `batch` states (sel_ws_bytes)
 template <class Val>
 static int select_quantile(Val val, SelectState* st, long long n, int batch, float q, bool need_count,
                            cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0) {
   (void)need_count;
-  const int thr = 256;
-  int gx = (int)((n + thr * 8 - 1) / (thr * 8));
-  if (gx > 592) gx = 592;
-  if (gx < 1) gx = 1;
-  dim3 grid(gx, batch);
-  unsigned int* lists = sel_lists(st, batch);
-  VL(), k_sel_zero<<<batch, 256, 0, stream>>>(st);
-  VL(), k_sel_s1<Val><<<grid, thr, 0, stream>>>(val, st, n);
-  VL(), k_sel_p1<<<batch, 256, 0, stream>>>(st, q, qv, qstride);
-  VL(), k_sel_s2<Val><<<grid, thr, 0, stream>>>(val, st, lists, n);
-  VL(), k_sel_p2<<<batch, 1024, 0, stream>>>(st, lists, q, qv, qstride);
-  VL(), k_sel_s3<Val><<<grid, thr, 0, stream>>>(val, st, n);
-  VL(), k_sel_p3<<<batch, 1024, 0, stream>>>(st);
-  VL(), k_sel_s4<Val><<<grid, thr, 0, stream>>>(val, st, n);
-  VL(), k_sel_finish<<<batch, 1, 0, stream>>>(st, q, qv, qstride);
-  CKL();
-  return 0;
+  return select_quantile_out(val, SelNoOut(), st, sel_lists(st, batch), n, batch, q, stream, qv, qstride);
 }

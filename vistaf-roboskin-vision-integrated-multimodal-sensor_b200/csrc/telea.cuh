@@ -13,6 +13,7 @@
 #pragma once
 #include "common.cuh"
 #include "labels.cuh"
+#include <stdlib.h>
 
 #define TL_MASK 1
 #define TL_BAND 2
@@ -243,7 +244,7 @@ static __global__ void k_telea_bandlist(const ull* __restrict__ uf, const unsign
 //    and summed in raster order by lanes 0..3 (one accumulator each) from shared memory.
 // Band cells enter with seq = their raster cell index (OpenCV pushes them in raster order, all with T = 0);
 // later pushes take seq from a counter above any cell index.
-#define TL_HCAP 512
+#define TL_HCAP 1056      // 1 + 32 + 1024 - 1: heap levels 0-2 of the 32-ary heap live in shared memory
 #define TL_MAXTAPS 289        // (2 * 8 + 1)^2
 
 struct TeleaHeap {
@@ -555,7 +556,18 @@ static int telea_inpaint(Mask mask, float* img, size_t img_stride, unsigned int*
   VL(), k_telea_count<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.flag, W.cl, Hp, Wp);
   VL(), k_telea_schedule<<<batch, 256, 0, st>>>(W.fr, W.cl, W.order, (unsigned int)W.cap, status, status_stride);
   VL(), k_telea_bandlist<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.flag, W.cl, W.band, W.cap, Hp, Wp);
-  const size_t march_smem = (size_t)TL_WARPS * (TL_HCAP * 12 + 32 * 16) + (size_t)TL_MAXTAPS * 8;
+  size_t march_smem = (size_t)TL_WARPS * (TL_HCAP * 12 + 32 * 16) + (size_t)TL_MAXTAPS * 8;
+  // A marching warp alone issues on ~1/3 of its scheduler's cycles (ncu: 0.35 IPC per warp), so three warps per
+  // scheduler already saturate issue and more only stretch the critical path (the largest cluster of a frame).
+  // The dynamic shared-memory request is padded so that exactly TL_BLOCKS_PER_SM blocks fit an SM.
+  static int blocks_per_sm = -1;
+  if (blocks_per_sm < 0) {
+    const char* e = getenv("VISTAF_TELEA_BLOCKS_PER_SM");
+    blocks_per_sm = e ? atoi(e) : 3;
+    if (blocks_per_sm < 1) blocks_per_sm = 1;
+  }
+  const size_t sm_budget = 227 * 1024 - 1024 * (size_t)blocks_per_sm;        // 1 KB per block reserved by the driver
+  if (march_smem * (size_t)(blocks_per_sm + 1) <= sm_budget) march_smem = sm_budget / (size_t)(blocks_per_sm + 1) + 256;
   static bool attr_set = false;
   if (!attr_set) {
     CK(cudaFuncSetAttribute((const void*)k_telea_march, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)march_smem));

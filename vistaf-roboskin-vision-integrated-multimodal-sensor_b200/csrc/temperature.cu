@@ -953,6 +953,7 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   if (gauss_blur(fl, fs, tmp, H, W, nb, p->g_across, p->g_along, st)) return 1;
   vistaf_stage_mark("T.stats_median", st);
   FinalVal fv{fin, p->roi, plane};
+  if (sel_reset(sel, nb, st)) return 1;
   if (select_quantile(fv, sel, (long long)npix, nb, -1.0f, true, st)) return 1;
   VL(), k_temp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, sel, O.records + f0, nb, W / 2, H / 2);
   CKL();

@@ -273,15 +273,18 @@ class MultimodalPlan:
     """FTP + force + temperature over batches of full camera frames resident on the GPU.
     mode: "multimodal" | "ftp" | "temperature" selects which halves run (BASELINE.json configs[1..3])."""
 
-    def __init__(self, H: int, W: int, chunk_ftp: int = 64, chunk_temp: int = 32, mode: str = "multimodal"):
+    def __init__(self, H: int, W: int, chunk_ftp: int = 64, chunk_temp: int = 32, mode: str = "multimodal",
+                 lanes_ftp: int = 1, lanes_temp: int = 1):
         if mode not in ("multimodal", "ftp", "temperature"):
             raise ValueError(f"unknown mode {mode}")
         self.torch = N.require_cuda()
         self.H, self.W, self.mode = int(H), int(W), mode
-        self.ftp = shape_ftp.FtpPlan(H, W, chunk=chunk_ftp) if mode != "temperature" else None
-        self.temp = temperature_sensor.TempPlan(H, W, chunk=chunk_temp) if mode != "ftp" else None
+        self.ftp = shape_ftp.FtpPlan(H, W, chunk=chunk_ftp, lanes=lanes_ftp) if mode != "temperature" else None
+        self.temp = temperature_sensor.TempPlan(H, W, chunk=chunk_temp, lanes=lanes_temp) if mode != "ftp" else None
         self._out = {}
         self._side = self.torch.cuda.Stream() if mode == "multimodal" else None
+        self._tstream = self.torch.cuda.Stream() if mode == "multimodal" else None
+        self.concurrent = True                # False: temperature half, then FTP half, on the current stream (stage timing)
 
     def step(self, ref_frame_dev, frames_dev, masks: bool = False, reuse_outputs: bool = True) -> dict:
         """One batch against a (new) reference frame.  The reference-frame half (demodulation of one frame: a short,
@@ -295,13 +298,18 @@ class MultimodalPlan:
         B = int(frames_dev.shape[0])
         key = (B, bool(masks))
         cache = self._out.get(key) if reuse_outputs else None
+        # the temperature half runs on its own stream (and lanes) beside the FTP half: neither reads the other's data
         self._side.wait_stream(main)              # inputs are ready; the FTP workspace is free of the previous batch
-        res = {"temp": self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None)}    # async, main stream
+        tstream = self._tstream if self.concurrent else main
+        tstream.wait_stream(main)
+        with t.cuda.stream(tstream):
+            res = {"temp": self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None)}    # async
         with t.cuda.stream(self._side):
             self.set_reference(ref_frame_dev)     # host returns when the side stream has the carrier
         main.wait_stream(self._side)
         gray = self.ftp.crop_gray(frames_dev)
         res["ftp"] = self.ftp.run(gray, masks=masks, out=cache["ftp"] if cache else None)
+        main.wait_stream(tstream)
         return self._finish(res, B, cache, key, reuse_outputs)
 
     def set_reference(self, ref_frame_dev):
@@ -316,11 +324,20 @@ class MultimodalPlan:
         key = (B, bool(masks))
         cache = self._out.get(key) if reuse_outputs else None
         res = {}
+        cur = t.cuda.current_stream()
+        forked = self.temp is not None and self.ftp is not None and self._tstream is not None and self.concurrent
+        if self.temp is not None:
+            if forked:                            # temperature half beside the FTP half
+                self._tstream.wait_stream(cur)
+                with t.cuda.stream(self._tstream):
+                    res["temp"] = self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None)
+            else:
+                res["temp"] = self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None)
         if self.ftp is not None:
             gray = self.ftp.crop_gray(frames_dev)
             res["ftp"] = self.ftp.run(gray, masks=masks, out=cache["ftp"] if cache else None)
-        if self.temp is not None:
-            res["temp"] = self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None)
+        if forked:
+            cur.wait_stream(self._tstream)
         return self._finish(res, B, cache, key, reuse_outputs)
 
     def _finish(self, res, B, cache, key, reuse_outputs):

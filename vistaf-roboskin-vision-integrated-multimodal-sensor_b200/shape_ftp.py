@@ -165,7 +165,7 @@ class FtpPlan:
     """Owns the opaque library plan, its torch workspace for `chunk` frames and the cached reference frame."""
 
     def __init__(self, H: int, W: int, chunk: int = 8, calibration_json: Optional[str] = None,
-                 force_json: Optional[str] = None):
+                 force_json: Optional[str] = None, lanes: int = 1):
         self.torch = N.require_cuda()
         self.H, self.W, self.chunk = int(H), int(W), int(chunk)
         self.geom = crop_geometry(H, W)
@@ -173,8 +173,16 @@ class FtpPlan:
         self.params = _params(self.geom, calibration_json or CALIBRATION_JSON, force_json or FORCE_CALIBRATION_JSON)
         self.handle = C.c_void_p()
         N.check(N.lib().vistaf_ftp_plan_create(C.byref(self.params), C.byref(self.handle)), "ftp_plan_create")
-        self.ws_bytes = int(N.lib().vistaf_ftp_workspace_bytes(self.handle, self.chunk))
-        self.ws = self.torch.empty(self.ws_bytes, dtype=self.torch.uint8, device="cuda")
+        # `lanes` > 1: a batch is cut into that many contiguous slices, each marched through the library on its own
+        # stream with its own workspace, so one slice's latency-bound stages (Telea march, selection tails, small
+        # per-frame kernels) overlap the other slices' bandwidth-bound sweeps.  The plan itself is read-only there.
+        self.lanes = max(1, int(lanes))
+        self.lane_frames = -(-self.chunk // self.lanes)
+        self.ws_bytes = int(N.lib().vistaf_ftp_workspace_bytes(self.handle, self.lane_frames))
+        self.lane_ws = [self.torch.empty(self.ws_bytes, dtype=self.torch.uint8, device="cuda") for _ in range(self.lanes)]
+        self.lane_streams = [self.torch.cuda.Stream() for _ in range(self.lanes)] if self.lanes > 1 else []
+        self.ws = self.lane_ws[0]
+        self.active_lanes = self.lanes        # set to 1 to serialise a batch on the current stream (stage timing)
         self.ref_info = None
 
     def __del__(self):
@@ -216,7 +224,7 @@ class FtpPlan:
 
     def workspace_plane(self, name: str, chunk: Optional[int] = None):
         off, nb = C.c_size_t(), C.c_size_t()
-        N.check(N.lib().vistaf_ftp_workspace_plane(self.handle, chunk or self.chunk, name.encode(), C.byref(off), C.byref(nb)))
+        N.check(N.lib().vistaf_ftp_workspace_plane(self.handle, chunk or self.lane_frames, name.encode(), C.byref(off), C.byref(nb)))
         return self.ws[off.value:off.value + nb.value]
 
     def run(self, def_gray_dev, masks: bool = True, out: Optional[dict] = None) -> dict:
@@ -233,12 +241,31 @@ class FtpPlan:
             if masks:
                 for k in MASK_NAMES:
                     out[k] = t.empty((B, self.h, self.w), dtype=t.uint8, device="cuda")
-        O = N.FtpOutputs()
-        O.height_mm, O.records = out["height_mm"].data_ptr(), out["records"].data_ptr()
-        for k in MASK_NAMES:
-            setattr(O, k, out[k].data_ptr() if k in out else None)
-        N.check(N.lib().vistaf_ftp_batch(self.handle, def_gray_dev.data_ptr(), B, C.byref(O), self.ws.data_ptr(),
-                                         self.ws_bytes, self._stream()), "ftp_batch")
+        def call(lo, hi, ws, stream):
+            O = N.FtpOutputs()
+            O.height_mm, O.records = out["height_mm"][lo:].data_ptr(), out["records"][lo:].data_ptr()
+            for k in MASK_NAMES:
+                setattr(O, k, out[k][lo:].data_ptr() if k in out else None)
+            N.check(N.lib().vistaf_ftp_batch(self.handle, def_gray_dev[lo:].data_ptr(), hi - lo, C.byref(O), ws.data_ptr(),
+                                             self.ws_bytes, C.c_void_p(stream.cuda_stream)), "ftp_batch")
+
+        cur = t.cuda.current_stream()
+        L = min(self.lanes, max(1, int(self.active_lanes)))
+        if L == 1 or B < 2 * L:
+            call(0, B, self.ws, cur)
+            return out
+        per = -(-B // L)
+        used = []
+        for k in range(L):
+            lo, hi = k * per, min(B, (k + 1) * per)
+            if lo >= hi:
+                break
+            s = self.lane_streams[k]
+            s.wait_stream(cur)
+            call(lo, hi, self.lane_ws[k], s)
+            used.append(s)
+        for s in used:
+            cur.wait_stream(s)
         return out
 
 

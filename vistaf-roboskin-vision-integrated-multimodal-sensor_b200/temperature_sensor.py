@@ -135,14 +135,19 @@ def _params(h: int, w: int) -> N.TempParams:
 class TempPlan:
     """Owns the opaque library plan + a torch workspace for `chunk` frames."""
 
-    def __init__(self, h: int, w: int, chunk: int = 8):
+    def __init__(self, h: int, w: int, chunk: int = 8, lanes: int = 1):
         self.torch = N.require_cuda()
         self.h, self.w, self.chunk = h, w, int(chunk)
         self.params = _params(h, w)
         self.handle = C.c_void_p()
         N.check(N.lib().vistaf_temp_plan_create(C.byref(self.params), C.byref(self.handle)), "temp_plan_create")
-        self.ws_bytes = int(N.lib().vistaf_temp_workspace_bytes(self.handle, self.chunk))
-        self.ws = self.torch.empty(self.ws_bytes, dtype=self.torch.uint8, device="cuda")
+        self.lanes = max(1, int(lanes))               # see shape_ftp.FtpPlan: slices of a batch on concurrent streams
+        self.lane_frames = -(-self.chunk // self.lanes)
+        self.ws_bytes = int(N.lib().vistaf_temp_workspace_bytes(self.handle, self.lane_frames))
+        self.lane_ws = [self.torch.empty(self.ws_bytes, dtype=self.torch.uint8, device="cuda") for _ in range(self.lanes)]
+        self.lane_streams = [self.torch.cuda.Stream() for _ in range(self.lanes)] if self.lanes > 1 else []
+        self.ws = self.lane_ws[0]
+        self.active_lanes = self.lanes        # set to 1 to serialise a batch on the current stream (stage timing)
 
     def __del__(self):
         try:
@@ -153,7 +158,7 @@ class TempPlan:
 
     def workspace_plane(self, name: str):
         off, nb = C.c_size_t(), C.c_size_t()
-        N.check(N.lib().vistaf_temp_workspace_plane(self.handle, self.chunk, name.encode(), C.byref(off), C.byref(nb)))
+        N.check(N.lib().vistaf_temp_workspace_plane(self.handle, self.lane_frames, name.encode(), C.byref(off), C.byref(nb)))
         return self.ws[off.value:off.value + nb.value]
 
     def run(self, frames_dev, masks: bool = True, out: Optional[dict] = None) -> dict:
@@ -169,13 +174,31 @@ class TempPlan:
             if masks:
                 for k in MASK_NAMES:
                     out[k] = t.empty((B, self.h, self.w), dtype=t.uint8, device="cuda")
-        O = N.TempOutputs()
-        O.fused, O.final_map, O.records = out["fused"].data_ptr(), out["final"].data_ptr(), out["records"].data_ptr()
-        for k in MASK_NAMES:
-            setattr(O, k, out[k].data_ptr() if k in out else None)
-        stream = t.cuda.current_stream().cuda_stream
-        N.check(N.lib().vistaf_temp_batch(self.handle, frames_dev.data_ptr(), B, C.byref(O), self.ws.data_ptr(),
-                                          self.ws_bytes, C.c_void_p(stream)), "temp_batch")
+        def call(lo, hi, ws, stream):
+            O = N.TempOutputs()
+            O.fused, O.final_map, O.records = out["fused"][lo:].data_ptr(), out["final"][lo:].data_ptr(), out["records"][lo:].data_ptr()
+            for k in MASK_NAMES:
+                setattr(O, k, out[k][lo:].data_ptr() if k in out else None)
+            N.check(N.lib().vistaf_temp_batch(self.handle, frames_dev[lo:].data_ptr(), hi - lo, C.byref(O), ws.data_ptr(),
+                                              self.ws_bytes, C.c_void_p(stream.cuda_stream)), "temp_batch")
+
+        cur = t.cuda.current_stream()
+        L = min(self.lanes, max(1, int(self.active_lanes)))
+        if L == 1 or B < 2 * L:
+            call(0, B, self.ws, cur)
+            return out
+        per = -(-B // L)
+        used = []
+        for k in range(L):
+            lo, hi = k * per, min(B, (k + 1) * per)
+            if lo >= hi:
+                break
+            s = self.lane_streams[k]
+            s.wait_stream(cur)
+            call(lo, hi, self.lane_ws[k], s)
+            used.append(s)
+        for s in used:
+            cur.wait_stream(s)
         return out
 
 
