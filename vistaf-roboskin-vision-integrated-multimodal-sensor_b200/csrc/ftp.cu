@@ -641,15 +641,12 @@ __device__ void irls_solve_dev(FtpScal& s, int iter) {
 }
 
 template <bool ORDER2>
-__global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ zc, const unsigned int* __restrict__ pc, FtpScal* sc,
-                                                     FitGeom g, int npix, int iter) {
+__global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ zc, const unsigned int* __restrict__ pc,
+                                                     const float* __restrict__ rc, FtpScal* sc, FitGeom g, int npix, int iter) {
   constexpr int NC = ORDER2 ? 6 : 3, NV = NC * (NC + 1) / 2 + NC + 1;
   __shared__ double sh[NV * 32];
   const int b = blockIdx.y;
   if (sc[b].irls_skip) return;
-  float coef[6];
-#pragma unroll
-  for (int i = 0; i < 6; i++) coef[i] = sc[b].coef[i];
   const float cs = __fmul_rn(IRLS_C, sc[b].sigma);
   const int n = (int)sc[b].nc;
   const size_t o = (size_t)b * npix;
@@ -658,13 +655,14 @@ __global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ zc
   for (int i = 0; i < NV; i++) acc[i] = 0.0;
   // four samples per thread and trip, all eight loads issued before any is used
   for (int j0 = blockIdx.x * 1024 + threadIdx.x; j0 < n; j0 += gridDim.x * 1024) {
-    float z4[4];
+    float z4[4], r4[4];
     unsigned int p4[4];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       const int jj = j0 + j * 256;
       z4[j] = jj < n ? zc[o + jj] : 0.f;
       p4[j] = jj < n ? pc[o + jj] : 0u;
+      r4[j] = (jj < n && iter > 0) ? rc[o + jj] : 0.f;       // residuals of the previous solve (RFirst)
     }
 #pragma unroll
     for (int j = 0; j < 4; j++) {
@@ -674,8 +672,7 @@ __global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ zc
       g.norm((int)p4[j], xn, yn);
       float wt = 1.0f;
       if (iter > 0) {
-        const float r = __fsub_rn(zz, poly_fit(coef, xn, yn, ORDER2));
-        const float u = __fdiv_rn(r, cs);
+        const float u = __fdiv_rn(r4[j], cs);
         wt = __fdiv_rn(1.0f, __fadd_rn(1.0f, __fmul_rn(u, u)));
       }
       const double w2 = (double)wt * (double)wt;
@@ -720,17 +717,32 @@ __global__ void k_irls_begin(FtpScal* sc, int mode) {    // mode 0: plane on rel
     if (!s.detrend1) s.irls_skip = 1;
   }
 }
-// residual stream of the current fit over its compacted samples: r (mode 0) or |r - med| (mode 1)
+// Residual streams of the current fit over its compacted samples.  RFirst evaluates r = z - fit once per solve (first
+// sweep of the median selection) and stores it; the other sweeps of the iteration (RPlain: r, RAbs: |r - med|, and the
+// next accumulate) re-read the 4-byte residual instead of the sample, its pixel index and the polynomial.
 template <bool ORDER2>
-struct ResidVal {
-  const float* zc; const unsigned int* pc; const FtpScal* sc; FitGeom g; long long plane; int mode;
+struct RFirst {
+  const float* zc; const unsigned int* pc; float* rc; const FtpScal* sc; FitGeom g; long long plane;
   __device__ long long limit(int b) const { return (long long)sc[b].nc; }
   __device__ bool operator()(int b, long long j, float& v) const {
-    const float zz = zc[(long long)b * plane + j];
+    const long long o = (long long)b * plane + j;
     float xn, yn;
-    g.norm((int)pc[(long long)b * plane + j], xn, yn);
-    const float r = __fsub_rn(zz, poly_fit(sc[b].coef, xn, yn, ORDER2));
-    v = mode ? fabsf(__fsub_rn(r, sc[b].med)) : r;
+    g.norm((int)pc[o], xn, yn);
+    v = __fsub_rn(zc[o], poly_fit(sc[b].coef, xn, yn, ORDER2));
+    rc[o] = v;
+    return true;
+  }
+};
+struct RPlain {
+  const float* rc; const FtpScal* sc; long long plane;
+  __device__ long long limit(int b) const { return (long long)sc[b].nc; }
+  __device__ bool operator()(int b, long long j, float& v) const { v = rc[(long long)b * plane + j]; return true; }
+};
+struct RAbs {
+  const float* rc; const FtpScal* sc; long long plane;
+  __device__ long long limit(int b) const { return (long long)sc[b].nc; }
+  __device__ bool operator()(int b, long long j, float& v) const {
+    v = fabsf(__fsub_rn(rc[(long long)b * plane + j], sc[b].med));
     return true;
   }
 };
@@ -1299,7 +1311,7 @@ extern "C" int vistaf_ftp_set_reference(VistafFtpPlan* p, const uint8_t* ref_gra
 #define IRLS_GROUP 8
 template <bool ORDER2>
 static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, SelectState* sel, float* zc, unsigned int* pc,
-                    int nb, int mode, cudaStream_t st) {
+                    float* rc, int nb, int mode, cudaStream_t st) {
   const int npix = p->h * p->w;
   const FitGeom g{p->w, (float)((p->w - 1) / 2.0), (float)((p->h - 1) / 2.0), (unsigned int)(((1ull << 40) + p->w - 1) / p->w)};
   unsigned int* lists = sel_lists(sel, nb);
@@ -1309,6 +1321,7 @@ static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, S
     const float* zg = z + (size_t)g0 * npix;
     float* zcg = zc + (size_t)g0 * npix;
     unsigned int* pcg = pc + (size_t)g0 * npix;
+    float* rcg = rc + (size_t)g0 * npix;
     FtpScal* scg = sc + g0;
     SelectState* selg = sel + g0;
     unsigned int* listg = lists + (size_t)g0 * SEL_CAP;
@@ -1318,12 +1331,13 @@ static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, S
     if (gx > 128) gx = 128;
     VL(), k_irls_compact<<<dim3(gx, ng), 256, 0, st>>>(zg, fmg, scg, zcg, pcg, npix);
     for (int it = 0; it < 6; it++) {
-      VL(), k_irls_accum<ORDER2><<<dim3(gx, ng), 256, 0, st>>>(zcg, pcg, scg, g, npix, it);
+      VL(), k_irls_accum<ORDER2><<<dim3(gx, ng), 256, 0, st>>>(zcg, pcg, rcg, scg, g, npix, it);
       if (it == 5) break;
-      ResidVal<ORDER2> rv{zcg, pcg, scg, g, (long long)npix, 0};
-      if (select_quantile_out(rv, GrabOut{scg, G_IRLS_MED}, selg, listg, npix, ng, -1.0f, st)) return 1;
-      rv.mode = 1;
-      if (select_quantile_out(rv, GrabOut{scg, G_IRLS_MAD}, selg, listg, npix, ng, -1.0f, st)) return 1;
+      RFirst<ORDER2> r1{zcg, pcg, rcg, scg, g, (long long)npix};
+      RPlain r2{rcg, scg, (long long)npix};
+      RAbs r3{rcg, scg, (long long)npix};
+      if (select_quantile_out2(r1, r2, GrabOut{scg, G_IRLS_MED}, selg, listg, npix, ng, -1.0f, st)) return 1;
+      if (select_quantile_out(r3, GrabOut{scg, G_IRLS_MAD}, selg, listg, npix, ng, -1.0f, st)) return 1;
     }
   }
   CKL();
@@ -1389,10 +1403,10 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   vistaf_stage_mark("F.irls_plane", st);
   // ---- D: plane removal, two-pass quadric detrend
   FitMask fm_rel{rel, contact_d, sc, plane, 0}, fm_bg{rel, contact_d, sc, plane, 1};
-  if (irls_fit<false>(p, unw, fm_rel, sc, sel, hnum, (unsigned int*)hm, nb, 0, st)) return 1;
+  if (irls_fit<false>(p, unw, fm_rel, sc, sel, hnum, (unsigned int*)hm, dist_in, nb, 0, st)) return 1;
   vistaf_stage_mark("F.irls_quadric_contact", st);
   VL(), k_ftp_sub_fit1<<<gpix, 256, 0, st>>>(unw, sc, g, npix);
-  if (irls_fit<true>(p, unw, fm_rel, sc, sel, hnum, (unsigned int*)hm, nb, 1, st)) return 1;
+  if (irls_fit<true>(p, unw, fm_rel, sc, sel, hnum, (unsigned int*)hm, dist_in, nb, 1, st)) return 1;
   if (select_grab(AbsResVal{unw, rel, sc, g, plane, 0}, sc, G_CONTACT, sel, npix, nb, P.contact_pct, st)) return 1;
   VL(), k_ftp_contact<<<gpix, 256, 0, st>>>(unw, rel, sc, g, contact, npix, 1);
   VL(), k_ftp_contact_frac<<<nb, 1, 0, st>>>(sc, P.min_contact_frac, P.max_contact_frac);
@@ -1414,7 +1428,7 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   VL(), k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(contact_d, sc, npix, 3);
   VL(), k_ftp_bg_decide<<<nb, 1, 0, st>>>(sc);
   vistaf_stage_mark("F.irls_quadric_background", st);
-  if (irls_fit<true>(p, unw, fm_bg, sc, sel, hnum, (unsigned int*)hm, nb, 2, st)) return 1;
+  if (irls_fit<true>(p, unw, fm_bg, sc, sel, hnum, (unsigned int*)hm, dist_in, nb, 2, st)) return 1;
   if (select_grab(DetVal{unw, fm_bg, sc, g, plane}, sc, G_BGMED, sel, npix, nb, -1.0f, st)) return 1;
   CKL();
   vistaf_stage_mark("F.smooth_sign", st);

@@ -334,20 +334,27 @@ __global__ void __launch_bounds__(1024) k_sel_p2(Val val, Out out, SelectState* 
 
 // Host: selection of quantile q (percent; q < 0 = median) for `batch` frames over n candidates each.
 // `lists`: batch * SEL_CAP keys.  The result lands in st[b].result / st[b].count and in `out`.
-template <class Val, class Out>
-static int select_quantile_out(Val val, Out out, SelectState* st, unsigned int* lists, long long n, int batch, float q,
-                               cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0) {
+// val1 feeds the first sweep, val2 the second sweep and the finishing block: they must describe the same value
+// stream (a first-sweep functor may materialise the values it computes for the second to re-read).
+template <class Val1, class Val2, class Out>
+static int select_quantile_out2(Val1 val1, Val2 val2, Out out, SelectState* st, unsigned int* lists, long long n, int batch,
+                                float q, cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0) {
   int gx = (148 * 6 + batch - 1) / batch;
   const int gmax = (int)((n + 1023) / 1024);
   if (gx > gmax) gx = gmax;
   if (gx > 592) gx = 592;
   if (gx < 1) gx = 1;
   dim3 grid(gx, batch);
-  VL(), k_sel_s1<Val><<<grid, 256, 0, stream>>>(val, st, n, q, qv, qstride);
-  VL(), k_sel_s2<Val><<<grid, 256, 0, stream>>>(val, st, lists, n);
-  VL(), k_sel_p2<Val, Out><<<batch, 1024, 0, stream>>>(val, out, st, lists, n, q, qv, qstride);
+  VL(), k_sel_s1<Val1><<<grid, 256, 0, stream>>>(val1, st, n, q, qv, qstride);
+  VL(), k_sel_s2<Val2><<<grid, 256, 0, stream>>>(val2, st, lists, n);
+  VL(), k_sel_p2<Val2, Out><<<batch, 1024, 0, stream>>>(val2, out, st, lists, n, q, qv, qstride);
   CKL();
   return 0;
+}
+template <class Val, class Out>
+static int select_quantile_out(Val val, Out out, SelectState* st, unsigned int* lists, long long n, int batch, float q,
+                               cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0) {
+  return select_quantile_out2(val, val, out, st, lists, n, batch, q, stream, qv, qstride);
 }
 // call-site compatible form: the key lists live right behind the `batch` states (sel_ws_bytes)
 template <class Val>

@@ -22,7 +22,7 @@
 #define TL_IN 16          // hole cell filled by the inward march
 #define TL_MAXCLUSTERS 65536
 #define TL_WARPS 4
-#define TL_GRIDX 96
+#define TL_BLOCKS_PER_SM 2  // resident march blocks per SM (persistent grid): leaves the SM to co-running kernels
 #define TL_NCLASS 24      // size classes (log2 of the cell count) for largest-first scheduling
 
 struct TeleaFrame {       // per-frame bookkeeping (device)
@@ -244,7 +244,7 @@ static __global__ void k_telea_bandlist(const ull* __restrict__ uf, const unsign
 //    and summed in raster order by lanes 0..3 (one accumulator each) from shared memory.
 // Band cells enter with seq = their raster cell index (OpenCV pushes them in raster order, all with T = 0);
 // later pushes take seq from a counter above any cell index.
-#define TL_HCAP 1056      // 1 + 32 + 1024 - 1: heap levels 0-2 of the 32-ary heap live in shared memory
+#define TL_HCAP 512
 #define TL_MAXTAPS 289        // (2 * 8 + 1)^2
 
 struct TeleaHeap {
@@ -361,9 +361,9 @@ __device__ __forceinline__ void tl_gather(const uint8_t* f, const float* T, int 
 }
 
 static __global__ void __launch_bounds__(32 * TL_WARPS) k_telea_march(TeleaWs Wsp, float* __restrict__ img,
-                                                                size_t img_stride, int h, int w, int range) {
+                                                                size_t img_stride, int h, int w, int range, int batch) {
   extern __shared__ unsigned char tl_smem[];
-  const int b = blockIdx.x, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   ull* sk = (ull*)tl_smem + (size_t)wid * TL_HCAP;
   int* sp = (int*)(tl_smem + (size_t)TL_WARPS * TL_HCAP * 8) + (size_t)wid * TL_HCAP;
   float (*tp)[4] = (float (*)[4])(tl_smem + (size_t)TL_WARPS * TL_HCAP * 12) + (size_t)wid * 32;
@@ -371,13 +371,6 @@ static __global__ void __launch_bounds__(32 * TL_WARPS) k_telea_march(TeleaWs Ws
   short2* tapd = (short2*)(tl_smem + (size_t)TL_WARPS * (TL_HCAP * 12 + 32 * 16));
   float* tapw = (float*)(tapd + TL_MAXTAPS);
   const int Hp = h + 2, Wp = w + 2;
-  TeleaFrame* fr = Wsp.fr + b;
-  const TeleaCluster* clt = Wsp.cl + (size_t)b * TL_MAXCLUSTERS;
-  const unsigned int* ord = Wsp.order + (size_t)b * TL_MAXCLUSTERS;
-  const unsigned int ncl = min(fr->nclusters, (unsigned int)TL_MAXCLUSTERS);
-  uint8_t* f = Wsp.flag + (size_t)b * Wsp.sp;
-  float* T = Wsp.T + (size_t)b * Wsp.sp;
-  float* im = img + (size_t)b * img_stride;
   const int r2 = range * range, side = 2 * range + 1, ntaps = side * side;
   for (int tt = threadIdx.x; tt < ntaps; tt += blockDim.x) {
     const int dk = tt / side - range, dl = tt - (tt / side) * side - range;
@@ -391,11 +384,28 @@ static __global__ void __launch_bounds__(32 * TL_WARPS) k_telea_march(TeleaWs Ws
   const int q = lane & 3;                                   // lanes 0..3 own neighbour q; other lanes mirror them
   int qdy, qdx;
   tl_diamond(q + 1, qdy, qdx);
+  // Persistent grid: every warp serves one frame's largest-first cluster queue until it runs dry, then moves on to
+  // the next frame.  Warps start spread over the frames, so the few giant clusters of EVERY frame (the critical
+  // path: a serial march of 10^4 cells) begin at once.
+  int b = (int)((blockIdx.x * TL_WARPS + wid) % (unsigned int)batch);
+  int dry = 0;
   for (;;) {
-    unsigned int s = 0;
-    if (lane == 0) s = atomicAdd(&fr->next, 1u);
+    TeleaFrame* fr = Wsp.fr + b;
+    const unsigned int ncl = min(fr->nclusters, (unsigned int)TL_MAXCLUSTERS);
+    unsigned int s = 0xffffffffu;
+    if (lane == 0 && *(volatile unsigned int*)&fr->next < ncl) s = atomicAdd(&fr->next, 1u);
     s = __shfl_sync(0xffffffffu, s, 0);
-    if (s >= ncl) break;
+    if (s >= ncl) {
+      if (++dry >= batch) break;
+      b = b + 1 == batch ? 0 : b + 1;
+      continue;
+    }
+    dry = 0;
+    const TeleaCluster* clt = Wsp.cl + (size_t)b * TL_MAXCLUSTERS;
+    const unsigned int* ord = Wsp.order + (size_t)b * TL_MAXCLUSTERS;
+    uint8_t* f = Wsp.flag + (size_t)b * Wsp.sp;
+    float* T = Wsp.T + (size_t)b * Wsp.sp;
+    float* im = img + (size_t)b * img_stride;
     const TeleaCluster cl = clt[ord[s]];
     if (cl.count == 0xffffffffu) continue;                  // did not fit the workspace (status bit already set)
     TeleaHeap H;
@@ -556,25 +566,15 @@ static int telea_inpaint(Mask mask, float* img, size_t img_stride, unsigned int*
   VL(), k_telea_count<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.flag, W.cl, Hp, Wp);
   VL(), k_telea_schedule<<<batch, 256, 0, st>>>(W.fr, W.cl, W.order, (unsigned int)W.cap, status, status_stride);
   VL(), k_telea_bandlist<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.flag, W.cl, W.band, W.cap, Hp, Wp);
-  size_t march_smem = (size_t)TL_WARPS * (TL_HCAP * 12 + 32 * 16) + (size_t)TL_MAXTAPS * 8;
-  // A marching warp alone issues on ~1/3 of its scheduler's cycles (ncu: 0.35 IPC per warp), so three warps per
-  // scheduler already saturate issue and more only stretch the critical path (the largest cluster of a frame).
-  // The dynamic shared-memory request is padded so that exactly TL_BLOCKS_PER_SM blocks fit an SM.
-  static int blocks_per_sm = -1;
-  if (blocks_per_sm < 0) {
-    const char* e = getenv("VISTAF_TELEA_BLOCKS_PER_SM");
-    blocks_per_sm = e ? atoi(e) : 3;
-    if (blocks_per_sm < 1) blocks_per_sm = 1;
-  }
-  const size_t sm_budget = 227 * 1024 - 1024 * (size_t)blocks_per_sm;        // 1 KB per block reserved by the driver
-  if (march_smem * (size_t)(blocks_per_sm + 1) <= sm_budget) march_smem = sm_budget / (size_t)(blocks_per_sm + 1) + 256;
-  static bool attr_set = false;
-  if (!attr_set) {
+  const size_t march_smem = (size_t)TL_WARPS * (TL_HCAP * 12 + 32 * 16) + (size_t)TL_MAXTAPS * 8;
+  static int n_sm = 0;
+  if (!n_sm) {
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
     CK(cudaFuncSetAttribute((const void*)k_telea_march, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)march_smem));
-    attr_set = true;
   }
-  // blockIdx.x = frame: the first wave of blocks starts the largest clusters of EVERY frame
-  VL(), k_telea_march<<<dim3(batch, TL_GRIDX), 32 * TL_WARPS, march_smem, st>>>(W, img, img_stride, h, w, range);
+  VL(), k_telea_march<<<n_sm * TL_BLOCKS_PER_SM, 32 * TL_WARPS, march_smem, st>>>(W, img, img_stride, h, w, range, batch);
   CKL();
   return 0;
 }

@@ -204,8 +204,20 @@ __global__ void __launch_bounds__(256) k_temp_fft_rows(const float* __restrict__
   const float* r0 = norm + ((size_t)b * h + r) * n;
   const float* r1 = r0 + n;
   const bool has1 = r + 1 < h;
-  for (int x = threadIdx.x; x < n; x += blockDim.x)
-    a[x] = make_float2(__fdiv_rn(r0[x], mu), has1 ? __fdiv_rn(r1[x], mu) : 0.f);
+  for (int x0 = threadIdx.x; x0 < n; x0 += blockDim.x * 4) {       // all loads of four trips issued before use
+    float u0[4], u1[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int x = x0 + j * blockDim.x;
+      u0[j] = x < n ? r0[x] : 0.f;
+      u1[j] = (x < n && has1) ? r1[x] : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int x = x0 + j * blockDim.x;
+      if (x < n) a[x] = make_float2(__fdiv_rn(u0[j], mu), has1 ? __fdiv_rn(u1[j], mu) : 0.f);
+    }
+  }
   float2* z = fft_smem<-1>(a, bb, p, 1, n);
   float2* o0 = A + ((size_t)b * h + r) * wh;
   float2* o1 = o0 + wh;
@@ -232,9 +244,19 @@ __global__ void __launch_bounds__(512) k_temp_fft_cols_peaks(const float2* __res
   float2* a = sm;
   float2* bb = sm + (size_t)COLS_PER_BLOCK * lds;
   const float2* src = A + (size_t)b * n * wh;
-  for (int t = threadIdx.x; t < nc * n; t += blockDim.x) {
-    int y = t / nc, c = t - y * nc;
-    a[c * lds + y] = src[(size_t)y * wh + c0 + c];
+  // eight independent 8-byte loads per thread in flight (the staging loop is latency bound: one block per SM)
+  for (int t0 = threadIdx.x; t0 < nc * n; t0 += blockDim.x * 8) {
+    float2 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const int t = t0 + j * blockDim.x;
+      if (t < nc * n) { const int y = t / nc, c = t - y * nc; v[j] = src[(size_t)y * wh + c0 + c]; }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const int t = t0 + j * blockDim.x;
+      if (t < nc * n) { const int y = t / nc, c = t - y * nc; a[c * lds + y] = v[j]; }
+    }
   }
   float2* F = fft_smem<-1>(a, bb, p, nc, lds);
   float* mag = (float*)(F == a ? bb : a);          // scratch buffer is free now
