@@ -197,6 +197,13 @@ int vistaf_ftp_set_reference(VistafFtpPlan* plan, const uint8_t* ref_gray, void*
 /* deformed frames: gray DEVICE uint8 [B][h][w] (already aligned); shape_ftp.py:1641-1865 + force_sensor.py:93-167 */
 int vistaf_ftp_batch(VistafFtpPlan* plan, const uint8_t* def_gray, int batch, const VistafFtpOutputs* out, void* workspace,
                      size_t workspace_bytes, void* cuda_stream);
+/* vistaf_ftp_batch for ONE chunk in two calls on the same workspace (batch must fit it whole): _begin runs the stages
+ * that do not read the reference frame (shape_ftp.py:625-666, :821-848: bad pixels, Telea fill, illumination
+ * normalisation, apodisation, median) and may be issued before vistaf_ftp_set_reference; _finish runs the rest. */
+int vistaf_ftp_batch_begin(VistafFtpPlan* plan, const uint8_t* def_gray, int batch, void* workspace, size_t workspace_bytes,
+                           void* cuda_stream);
+int vistaf_ftp_batch_finish(VistafFtpPlan* plan, const uint8_t* def_gray, int batch, const VistafFtpOutputs* out,
+                            void* workspace, size_t workspace_bytes, void* cuda_stream);
 int vistaf_ftp_masks(const VistafFtpPlan* plan, uint8_t* roi_dev, uint8_t* circ_dev, float* apo_dev, void* cuda_stream);
 int vistaf_ftp_workspace_plane(const VistafFtpPlan* plan, int chunk, const char* name, size_t* offset, size_t* bytes);
 /* force_sensor.depth_map_to_volume_cm3 (:93-123) on DEVICE maps: out3 = DEVICE float64 [B][3] (volume_cm3, area_mm2, max_depth_mm) */

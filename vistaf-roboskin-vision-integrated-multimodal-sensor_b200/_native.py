@@ -176,6 +176,9 @@ def lib():
                                                C.POINTER(FtpReferenceInfo), C.c_void_p]
         L.vistaf_ftp_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(FtpOutputs), C.c_void_p, C.c_size_t,
                                        C.c_void_p]
+        L.vistaf_ftp_batch_begin.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.vistaf_ftp_batch_finish.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(FtpOutputs), C.c_void_p, C.c_size_t,
+                                              C.c_void_p]
         L.vistaf_ftp_masks.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.vistaf_ftp_workspace_plane.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.POINTER(C.c_size_t),
                                                  C.POINTER(C.c_size_t)]

@@ -34,13 +34,21 @@ static inline GaussKernel make_gauss(double sigma, int ksize_override = 0) {
   return g;
 }
 
+// Optional active window [x0,x1) x [y0,y1): outputs outside it are not computed -- the column pass hands the Store a
+// 0 there (for Stores whose result does not depend on the value outside the window, e.g. NaN outside a ROI) and the
+// row pass skips rows / segments no active column block reads.
+struct BlurWindow { int x0, x1, y0, y1; };
+
 // Row pass.  grid = (ceil(w/1280), h, batch), block = 160.  Load: float operator()(int b,int y,int x).
 template <class Load>
 __global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* __restrict__ tmp, int h, int w,
-                                                                 long long plane, GaussKernel g) {
+                                                                 long long plane, GaussKernel g, BlurWindow win, int rady) {   // rady: column radius + column block height
   __shared__ float s[8 * BLUR_ROW_PITCH];
   __shared__ float wk[BLUR_MAXK];
   const int b = blockIdx.z, y = blockIdx.y, x0 = blockIdx.x * BLUR_ROW_SEG;
+  // rows the active column blocks read: the window widened by the column radius and one block height (blocks are
+  // aligned to their own grid); border reflection maps into that same range
+  if (y < win.y0 - rady || y >= win.y1 + rady || x0 >= win.x1 + 32 || x0 + BLUR_ROW_SEG <= win.x0 - 32) return;
   const int rad = g.ksize >> 1;
   const int need = BLUR_ROW_SEG + g.kpad + 8;
   for (int e = threadIdx.x; e < need; e += BLUR_ROW_THREADS) {
@@ -52,21 +60,21 @@ __global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* 
   for (int e = threadIdx.x; e < g.kpad; e += BLUR_ROW_THREADS) wk[e] = g.w[e];
   __syncthreads();
   const int t = threadIdx.x;
-  float acc[8], win[16];
+  float acc[8], wreg[16];
 #pragma unroll
-  for (int j = 0; j < 8; j++) { acc[j] = 0.f; win[j] = s[j * BLUR_ROW_PITCH + t]; }
+  for (int j = 0; j < 8; j++) { acc[j] = 0.f; wreg[j] = s[j * BLUR_ROW_PITCH + t]; }
   for (int kb = 0; kb < g.kpad; kb += 8) {
     const int c = t + (kb >> 3) + 1;
 #pragma unroll
-    for (int j = 0; j < 8; j++) win[8 + j] = s[j * BLUR_ROW_PITCH + c];
+    for (int j = 0; j < 8; j++) wreg[8 + j] = s[j * BLUR_ROW_PITCH + c];
 #pragma unroll
     for (int kk = 0; kk < 8; kk++) {
       const float wv = wk[kb + kk];
 #pragma unroll
-      for (int j = 0; j < 8; j++) acc[j] = fmaf(wv, win[kk + j], acc[j]);
+      for (int j = 0; j < 8; j++) acc[j] = fmaf(wv, wreg[kk + j], acc[j]);
     }
 #pragma unroll
-    for (int j = 0; j < 8; j++) win[j] = win[8 + j];
+    for (int j = 0; j < 8; j++) wreg[j] = wreg[8 + j];
   }
   float* o = tmp + (long long)b * plane + (long long)y * w;
 #pragma unroll
@@ -79,11 +87,22 @@ __global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* 
 // Column pass.  grid = (ceil(w/32), ceil(h/(8*TYT)), batch), block = (32, TYT).
 // dynamic smem = (8*TYT + kpad + 8) * 32 floats.  Store: void operator()(int b,int y,int x,float v); void finish(int b).
 template <class Store>
-__global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int w, long long plane, GaussKernel g) {
+__global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int w, long long plane, GaussKernel g,
+                            BlurWindow win) {
   extern __shared__ float sc[];
   __shared__ float wk[BLUR_MAXK];
   const int TY = 8 * blockDim.y;
   const int b = blockIdx.z, x = blockIdx.x * 32 + threadIdx.x, y0 = blockIdx.y * TY;
+  if ((int)blockIdx.x * 32 >= win.x1 || (int)blockIdx.x * 32 + 32 <= win.x0 || y0 >= win.y1 || y0 + TY <= win.y0) {
+    Store sto = st;                // block outside the window: nothing computed
+    if (x < w) {
+      const int r0o = threadIdx.y * 8;
+#pragma unroll
+      for (int j = 0; j < 8; j++) { const int y = y0 + r0o + j; if (y < h) sto(b, y, x, 0.f); }
+    }
+    sto.finish(b);
+    return;
+  }
   const int rad = g.ksize >> 1;
   const int need = TY + g.kpad + 8;
   const float* src = tmp + (long long)b * plane;
@@ -97,20 +116,20 @@ __global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int 
   for (int e = tid; e < g.kpad; e += 32 * blockDim.y) wk[e] = g.w[e];
   __syncthreads();
   const int r0 = threadIdx.y * 8;
-  float acc[8], win[16];
+  float acc[8], wreg[16];
 #pragma unroll
-  for (int j = 0; j < 8; j++) { acc[j] = 0.f; win[j] = sc[(r0 + j) * 32 + threadIdx.x]; }
+  for (int j = 0; j < 8; j++) { acc[j] = 0.f; wreg[j] = sc[(r0 + j) * 32 + threadIdx.x]; }
   for (int kb = 0; kb < g.kpad; kb += 8) {
 #pragma unroll
-    for (int j = 0; j < 8; j++) win[8 + j] = sc[(r0 + kb + 8 + j) * 32 + threadIdx.x];
+    for (int j = 0; j < 8; j++) wreg[8 + j] = sc[(r0 + kb + 8 + j) * 32 + threadIdx.x];
 #pragma unroll
     for (int kk = 0; kk < 8; kk++) {
       const float wv = wk[kb + kk];
 #pragma unroll
-      for (int j = 0; j < 8; j++) acc[j] = fmaf(wv, win[kk + j], acc[j]);
+      for (int j = 0; j < 8; j++) acc[j] = fmaf(wv, wreg[kk + j], acc[j]);
     }
 #pragma unroll
-    for (int j = 0; j < 8; j++) win[j] = win[8 + j];
+    for (int j = 0; j < 8; j++) wreg[j] = wreg[8 + j];
   }
   Store stl = st;                 // per-thread copy: stores may accumulate (reductions fused in the epilogue)
   if (x < w) {
@@ -126,10 +145,11 @@ __global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int 
 // Host launcher: dst/epilogue through Store, source/prologue through Load, tmp = scratch plane(s).
 template <class Load, class Store>
 static int gauss_blur(Load ld, Store st, float* tmp, int h, int w, int batch, const GaussKernel& gx,
-                      const GaussKernel& gy, cudaStream_t stream) {
+                      const GaussKernel& gy, cudaStream_t stream, const BlurWindow* window = nullptr) {
   const long long plane = (long long)h * w;
+  const BlurWindow win = window ? *window : BlurWindow{0, w, 0, h};
   dim3 g1(cdiv(w, BLUR_ROW_SEG), h, batch);
-  VL(), k_blur_rows<Load><<<g1, BLUR_ROW_THREADS, 0, stream>>>(ld, tmp, h, w, plane, gx);
+  VL(), k_blur_rows<Load><<<g1, BLUR_ROW_THREADS, 0, stream>>>(ld, tmp, h, w, plane, gx, win, (gy.ksize >> 1) + 8 * (gy.ksize > 100 ? 32 : 16));
   CKL();
   const int tyt = gy.ksize > 100 ? 32 : 16;
   dim3 blk(32, tyt), g2(cdiv(w, 32), cdiv(h, 8 * tyt), batch);
@@ -139,7 +159,7 @@ static int gauss_blur(Load ld, Store st, float* tmp, int h, int w, int batch, co
     CK(cudaFuncSetAttribute((const void*)k_blur_cols<Store>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     attr_done = true;
   }
-  VL(), k_blur_cols<Store><<<g2, blk, sm, stream>>>(tmp, st, h, w, plane, gy);
+  VL(), k_blur_cols<Store><<<g2, blk, sm, stream>>>(tmp, st, h, w, plane, gy, win);
   CKL();
   return 0;
 }

@@ -63,6 +63,7 @@ struct VistafFtpPlan {
   int h, w, N, np;                // crop size, padded FFT size, patch size
   uint8_t *roi, *circ, *valid;    // device [h][w]
   float *apo, *den9;              // device [h][w]
+  float *xnt, *ynt;               // device [w], [h]: normalised fit coordinates (x - cx) / cx, float32 (shape_ftp.py:1107)
   Fft1D fN;
   GaussKernel g_illum, g_pre, g_qual, g_smooth, g_unrel;
   MorphSE se_bad, se_close, se_dil, se_edge;
@@ -550,12 +551,25 @@ __device__ __forceinline__ float poly_fit(const float* c, float xn, float yn, bo
 struct FitGeom {
   int w; float cx, cy;           // (w-1)/2, (h-1)/2
   unsigned int magic;            // ceil(2^40 / w): i / w == (i * magic) >> 40 for i < 2^24, 256 <= w < 65536
+  const float* xnt; const float* ynt;   // tables of (x - cx) / cx and (y - cy) / cy, rounded like the float32 division
   __device__ void norm(int i, float& xn, float& yn) const {
     const int y = (int)(((unsigned long long)(unsigned int)i * magic) >> 40), x = i - y * w;
-    xn = __fdiv_rn(__fsub_rn((float)x, cx), cx);
-    yn = __fdiv_rn(__fsub_rn((float)y, cy), cy);
+    xn = __ldg(xnt + x);
+    yn = __ldg(ynt + y);
+  }
+  __device__ unsigned int pack(int i) const {                     // (y << 16) | x
+    const unsigned int y = (unsigned int)(((unsigned long long)(unsigned int)i * magic) >> 40);
+    return (y << 16) | ((unsigned int)i - y * (unsigned int)w);
+  }
+  __device__ void norm_packed(unsigned int pk, float& xn, float& yn) const {
+    xn = __ldg(xnt + (pk & 0xffffu));
+    yn = __ldg(ynt + (pk >> 16));
   }
 };
+static FitGeom make_fitgeom(const VistafFtpPlan* p) {
+  return FitGeom{p->w, (float)((p->w - 1) / 2.0), (float)((p->h - 1) / 2.0), (unsigned int)(((1ull << 40) + p->w - 1) / p->w),
+                 p->xnt, p->ynt};
+}
 // mask selector for the three fits: 0 = reliable, 1 = background (reliable & ~contact_dilated, or reliable)
 struct FitMask {
   const uint8_t* rel; const uint8_t* contact_d; const FtpScal* sc; long long plane; int use_bg;
@@ -569,7 +583,7 @@ struct FitMask {
 // Compacted sample list of a fit: the pixels that pass the fit's mask and are finite, as (value, pixel index) pairs
 // in arbitrary order (every consumer is order independent: float64 sums by atomics, exact order statistics).  The
 // ~30 sweeps of a fit then stream two dense arrays instead of chasing mask -> sample through a 43 % empty plane.
-__global__ void __launch_bounds__(256) k_irls_compact(const float* __restrict__ z, FitMask fm, FtpScal* sc,
+__global__ void __launch_bounds__(256) k_irls_compact(const float* __restrict__ z, FitMask fm, FtpScal* sc, FitGeom g,
                                                        float* __restrict__ zc, unsigned int* __restrict__ pc, int npix) {
   const int b = blockIdx.y, lane = threadIdx.x & 31;
   if (sc[b].irls_skip) return;
@@ -594,7 +608,7 @@ __global__ void __launch_bounds__(256) k_irls_compact(const float* __restrict__ 
       if (ok[j]) {
         const unsigned int at = base + (unsigned int)__popc(bits & ((1u << lane) - 1u));
         zc[o + at] = zz[j];
-        pc[o + at] = (unsigned int)(i0 + j * 32 + lane);
+        pc[o + at] = g.pack(i0 + j * 32 + lane);
       }
     }
   }
@@ -669,7 +683,7 @@ __global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ zc
       if (j0 + j * 256 >= n) continue;
       const float zz = z4[j];
       float xn, yn;
-      g.norm((int)p4[j], xn, yn);
+      g.norm_packed(p4[j], xn, yn);
       float wt = 1.0f;
       if (iter > 0) {
         const float u = __fdiv_rn(r4[j], cs);
@@ -727,7 +741,7 @@ struct RFirst {
   __device__ bool operator()(int b, long long j, float& v) const {
     const long long o = (long long)b * plane + j;
     float xn, yn;
-    g.norm((int)pc[o], xn, yn);
+    g.norm_packed(pc[o], xn, yn);
     v = __fsub_rn(zc[o], poly_fit(sc[b].coef, xn, yn, ORDER2));
     rc[o] = v;
     return true;
@@ -1102,6 +1116,16 @@ extern "C" int vistaf_ftp_plan_create(const VistafFtpParams* P, VistafFtpPlan** 
   p->N = P->crop_w + 2 * P->fft_pad;
   if (P->crop_h != P->crop_w) return vistaf_set_err("FTP crop must be square", cudaErrorInvalidValue, __FILE__, __LINE__);
   if (fft1d_create(&p->fN, p->N)) return 1;
+  {
+    std::vector<float> tx(p->w), ty(p->h);
+    volatile float cxv = (float)((p->w - 1) / 2.0), cyv = (float)((p->h - 1) / 2.0);
+    for (int x = 0; x < p->w; x++) { volatile float d = (float)x - cxv; volatile float q = d / cxv; tx[x] = q; }
+    for (int y = 0; y < p->h; y++) { volatile float d = (float)y - cyv; volatile float q = d / cyv; ty[y] = q; }
+    CK(cudaMalloc(&p->xnt, sizeof(float) * p->w));
+    CK(cudaMalloc(&p->ynt, sizeof(float) * p->h));
+    CK(cudaMemcpy(p->xnt, tx.data(), sizeof(float) * p->w, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(p->ynt, ty.data(), sizeof(float) * p->h, cudaMemcpyHostToDevice));
+  }
   p->g_illum = make_gauss(P->illum_sigma);
   p->g_pre = make_gauss(P->pre_blur_sigma);
   p->g_qual = make_gauss(P->quality_sigma);
@@ -1142,6 +1166,7 @@ extern "C" void vistaf_ftp_plan_destroy(VistafFtpPlan* p) {
   fft1d_destroy(&p->fN);
   cudaFree(p->roi); cudaFree(p->circ); cudaFree(p->valid); cudaFree(p->apo); cudaFree(p->den9);
   cudaFree(p->cref); cudaFree(p->amp_ref); cudaFree(p->rampx); cudaFree(p->rampy); cudaFree(p->hann);
+  cudaFree(p->xnt); cudaFree(p->ynt);
   cudaFree(p->kxs); cudaFree(p->kys); cudaFree(p->peak_keys); cudaFree(p->peak_result);
   delete p;
 }
@@ -1179,7 +1204,8 @@ extern "C" int vistaf_ftp_workspace_plane(const VistafFtpPlan* p, int chunk, con
 }
 
 // Stage A up to the apodised, normalised image Iw and its median (shared by reference and deformed frames).
-static int ftp_preprocess(VistafFtpPlan* p, const uint8_t* gray, int nb, char* ws, const FtpWs& L, cudaStream_t st) {
+static int ftp_preprocess(VistafFtpPlan* p, const uint8_t* gray, int nb, char* ws, const FtpWs& L, cudaStream_t st,
+                          bool ref = false) {       // ref: the reference frame's pass reports under R.* stage names
   const VistafFtpParams& P = p->P;
   const int h = p->h, w = p->w, npix = h * w;
   const long long plane = npix;
@@ -1189,7 +1215,7 @@ static int ftp_preprocess(VistafFtpPlan* p, const uint8_t* gray, int nb, char* w
   FtpScal* sc = (FtpScal*)(ws + L.scal);
   SelectState* sel = (SelectState*)(ws + L.sel);
   if (sel_reset(sel, nb, st)) return 1;
-  vistaf_stage_mark("F.sobel_percentiles_bad", st);
+  vistaf_stage_mark(ref ? "R.sobel_percentiles_bad" : "F.sobel_percentiles_bad", st);
   VL(), k_ftp_init<<<cdiv(nb, 128), 128, 0, st>>>(sc, nb);
   VL(), k_ftp_sobel<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(gray, img, grad, h, w);
   CKL();
@@ -1204,13 +1230,13 @@ static int ftp_preprocess(VistafFtpPlan* p, const uint8_t* gray, int nb, char* w
   (void)bad0;
   VL(), k_ftp_count_mask<<<dim3(64, nb), 256, 0, st>>>(bad, sc, npix, 0);
   CKL();
-  vistaf_stage_mark("F.telea_inpaint", st);
+  vistaf_stage_mark(ref ? "R.telea_inpaint" : "F.telea_inpaint", st);
   if (telea_inpaint(TeleaMask{bad, plane, w}, img, (size_t)npix, &sc[0].status, sizeof(FtpScal), ws + L.telea, h, w, nb,
                     P.bad_inpaint_radius, st))
     return 1;
-  vistaf_stage_mark("F.illum_blur45", st);
+  vistaf_stage_mark(ref ? "R.illum_blur45" : "F.illum_blur45", st);
   if (gauss_blur(PlaneLoad{img, plane, w}, IllumStoreF{img, I, plane, w}, tmp, h, w, nb, p->g_illum, p->g_illum, st)) return 1;
-  vistaf_stage_mark("F.preblur_apo_median", st);
+  vistaf_stage_mark(ref ? "R.preblur_apo_median" : "F.preblur_apo_median", st);
   if (gauss_blur(PlaneLoad{I, plane, w}, ApoStore{p->apo, Iw, plane, w}, tmp, h, w, nb, p->g_pre, p->g_pre, st)) return 1;
   if (select_grab(MaskedVal{Iw, p->valid, plane}, sc, G_MU, sel, npix, nb, -1.0f, st)) return 1;
   CKL();
@@ -1222,7 +1248,7 @@ static int ftp_patch_field(VistafFtpPlan* p, int nb, char* ws, const FtpWs& L, b
   float* Iw = (float*)(ws + L.Iw);
   float2* R = (float2*)(ws + L.R); float2* Pw = (float2*)(ws + L.Pw);
   FtpScal* sc = (FtpScal*)(ws + L.scal);
-  vistaf_stage_mark("F.carrier_dft_field", st);
+  vistaf_stage_mark(ref ? "R.carrier_dft_field" : "F.carrier_dft_field", st);
   VL(), k_ftp_rowdft<<<dim3(h, nb), 256, (size_t)N * 4, st>>>(Iw, sc, R, p->fN.tw, p->kxs, h, w, N, pad, np);
   VL(), k_ftp_coldft<<<dim3(np, nb), 256, (size_t)h * 8, st>>>(R, Pw, p->fN.tw, p->kys, p->hann, h, N, pad, np);
   if (ref)
@@ -1268,10 +1294,10 @@ extern "C" int vistaf_ftp_set_reference(VistafFtpPlan* p, const uint8_t* ref_gra
   const size_t dense = align256((size_t)N * N * 4) + align256((size_t)N * N * 8);
   if (L.total + dense > ws_bytes) return vistaf_set_err("vistaf_ftp_set_reference: workspace too small", cudaErrorInvalidValue, __FILE__, __LINE__);
   char* ws = (char*)workspace;
-  if (ftp_preprocess(p, ref_gray, 1, ws, L, st)) return 1;
+  if (ftp_preprocess(p, ref_gray, 1, ws, L, st, true)) return 1;
   float* Ip = (float*)(ws + L.total);
   float2* F = (float2*)(ws + L.total + align256((size_t)N * N * 4));
-  vistaf_stage_mark("F.reference_dense_fft", st);
+  vistaf_stage_mark("R.dense_fft_carrier", st);
   VL(), k_ftp_pad<<<dim3(cdiv(N, 256), N), 256, 0, st>>>((float*)(ws + L.Iw), (FtpScal*)(ws + L.scal), Ip, p->h, p->w, N, p->P.fft_pad);
   CKL();
   if (fft2d_dense(Ip, F, p->fN, p->fN, N, N, 1, -1, true, st)) return 1;
@@ -1313,7 +1339,7 @@ template <bool ORDER2>
 static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, SelectState* sel, float* zc, unsigned int* pc,
                     float* rc, int nb, int mode, cudaStream_t st) {
   const int npix = p->h * p->w;
-  const FitGeom g{p->w, (float)((p->w - 1) / 2.0), (float)((p->h - 1) / 2.0), (unsigned int)(((1ull << 40) + p->w - 1) / p->w)};
+  const FitGeom g = make_fitgeom(p);
   unsigned int* lists = sel_lists(sel, nb);
   VL(), k_irls_begin<<<nb, 1, 0, st>>>(sc, mode);
   for (int g0 = 0; g0 < nb; g0 += IRLS_GROUP) {
@@ -1329,7 +1355,7 @@ static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, S
     fmg.rel += (size_t)g0 * fm.plane; fmg.contact_d += (size_t)g0 * fm.plane; fmg.sc = scg;
     int gx = (148 * 4 + ng - 1) / ng;
     if (gx > 128) gx = 128;
-    VL(), k_irls_compact<<<dim3(gx, ng), 256, 0, st>>>(zg, fmg, scg, zcg, pcg, npix);
+    VL(), k_irls_compact<<<dim3(gx, ng), 256, 0, st>>>(zg, fmg, scg, g, zcg, pcg, npix);
     for (int it = 0; it < 6; it++) {
       VL(), k_irls_accum<ORDER2><<<dim3(gx, ng), 256, 0, st>>>(zcg, pcg, rcg, scg, g, npix, it);
       if (it == 5) break;
@@ -1345,7 +1371,7 @@ static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, S
 }
 
 static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const VistafFtpOutputs& O, size_t f0, char* ws,
-                     const FtpWs& L, cudaStream_t st) {
+                     const FtpWs& L, cudaStream_t st, bool preprocessed = false) {
   const VistafFtpParams& P = p->P;
   const int h = p->h, w = p->w, npix = h * w;
   const long long plane = npix;
@@ -1366,11 +1392,11 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   FtpScal* sc = (FtpScal*)(ws + L.scal);
   SelectState* sel = (SelectState*)(ws + L.sel);
   float* out = O.height_mm + f0 * (size_t)npix;
-  const FitGeom g{w, (float)((w - 1) / 2.0), (float)((h - 1) / 2.0), (unsigned int)(((1ull << 40) + w - 1) / w)};
+  const FitGeom g = make_fitgeom(p);
   const dim3 gpix(cdiv(npix, 256), nb);
 
   // ---- A: demodulation
-  if (ftp_preprocess(p, gray, nb, ws, L, st)) return 1;
+  if (!preprocessed && ftp_preprocess(p, gray, nb, ws, L, st)) return 1;
   if (ftp_patch_field(p, nb, ws, L, false, st)) return 1;
   vistaf_stage_mark("F.quality_reliable_mask", st);
   // ---- B: reliable mask
@@ -1482,6 +1508,29 @@ extern "C" int vistaf_ftp_batch(VistafFtpPlan* p, const uint8_t* def_gray, int b
     if (ftp_chunk(p, def_gray, nb, *out, (size_t)f0, (char*)workspace, L, (cudaStream_t)stream)) return 1;
   }
   return 0;
+}
+
+// Split form of vistaf_ftp_batch for ONE chunk: _begin runs the part of the chain that does not need the reference
+// frame (bad pixels, Telea fill, illumination normalisation, apodisation, median), so a caller can issue it before /
+// beside vistaf_ftp_set_reference; _finish runs the rest on the same workspace.
+extern "C" int vistaf_ftp_batch_begin(VistafFtpPlan* p, const uint8_t* def_gray, int batch, void* workspace, size_t ws_bytes,
+                                      void* stream) {
+  if (!p || !def_gray || !workspace || batch < 1)
+    return vistaf_set_err("vistaf_ftp_batch_begin: bad argument", cudaErrorInvalidValue, __FILE__, __LINE__);
+  FtpWs L;
+  ftp_layout(p, batch, L);
+  if (L.total > ws_bytes) return vistaf_set_err("vistaf_ftp_batch_begin: workspace too small for the batch in one chunk", cudaErrorInvalidValue, __FILE__, __LINE__);
+  return ftp_preprocess(p, def_gray, batch, (char*)workspace, L, (cudaStream_t)stream);
+}
+extern "C" int vistaf_ftp_batch_finish(VistafFtpPlan* p, const uint8_t* def_gray, int batch, const VistafFtpOutputs* out,
+                                       void* workspace, size_t ws_bytes, void* stream) {
+  if (!p || !def_gray || !out || !out->height_mm || !out->records || !workspace || batch < 1)
+    return vistaf_set_err("vistaf_ftp_batch_finish: bad argument", cudaErrorInvalidValue, __FILE__, __LINE__);
+  if (!p->have_ref) return vistaf_set_err("vistaf_ftp_batch_finish: call vistaf_ftp_set_reference first", cudaErrorInvalidValue, __FILE__, __LINE__);
+  FtpWs L;
+  ftp_layout(p, batch, L);
+  if (L.total > ws_bytes) return vistaf_set_err("vistaf_ftp_batch_finish: workspace too small for the batch in one chunk", cudaErrorInvalidValue, __FILE__, __LINE__);
+  return ftp_chunk(p, def_gray, batch, *out, 0, (char*)workspace, L, (cudaStream_t)stream, true);
 }
 
 // force_sensor.depth_map_to_volume_cm3 on device maps: out3[b] = (volume_cm3, area_mm2, max_depth_mm)

@@ -42,12 +42,20 @@ static inline MorphSE se_rect(int kx, int ky) {
 #define MORPH_TW 32
 #define MORPH_TH 128
 template <bool DILATE, class Load, class Post>
-__global__ void __launch_bounds__(128) k_morph(Load ld, Post post, uint8_t* __restrict__ dst, int h, int w, MorphSE se) {
+__global__ void __launch_bounds__(128) k_morph(Load ld, Post post, uint8_t* __restrict__ dst, int h, int w, MorphSE se,
+                                               int4 win) {   // win = (x0, x1, y0, y1): the input is known to be 0 outside it
   __shared__ unsigned long long Wd[MORPH_TH + MORPH_MAXROWS - 1];
   __shared__ unsigned int Rw[MORPH_TH];
   const int ry = se.rows / 2, nrow = MORPH_TH + se.rows - 1;
   const int b = blockIdx.z, x0 = blockIdx.x * MORPH_TW, y0 = blockIdx.y * MORPH_TH;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (x0 - 16 >= win.y || x0 + MORPH_TW + 16 <= win.x || y0 - ry >= win.w || y0 + MORPH_TH + ry <= win.z) {
+    for (int ty = wid; ty < MORPH_TH; ty += 4) {     // all-zero neighbourhood: dilation and erosion both give 0
+      const int y = y0 + ty, x = x0 + lane;
+      if (y < h && x < w) dst[(size_t)b * h * w + (size_t)y * w + x] = (uint8_t)post(b, y, x, 0);
+    }
+    return;
+  }
   for (int ty = wid; ty < nrow; ty += 4) {
     const int y = y0 - ry + ty;
     const bool yin = y >= 0 && y < h;
@@ -87,12 +95,14 @@ __global__ void __launch_bounds__(128) k_morph(Load ld, Post post, uint8_t* __re
 }
 
 template <bool DILATE, class Load, class Post>
-static int morph(Load ld, Post post, uint8_t* dst, int h, int w, int batch, const MorphSE& se, cudaStream_t st) {
+static int morph(Load ld, Post post, uint8_t* dst, int h, int w, int batch, const MorphSE& se, cudaStream_t st,
+                 const int4* window = nullptr) {
   for (int i = 0; i < se.rows; i++)
     if (se.half[i] > 16) return vistaf_set_err("morph: structuring element wider than 33", cudaErrorInvalidValue, __FILE__, __LINE__);
   if (se.rows > MORPH_MAXROWS) return vistaf_set_err("morph: structuring element taller than 33", cudaErrorInvalidValue, __FILE__, __LINE__);
   dim3 grid(cdiv(w, MORPH_TW), cdiv(h, MORPH_TH), batch);
-  VL(), k_morph<DILATE, Load, Post><<<grid, 128, 0, st>>>(ld, post, dst, h, w, se);
+  const int4 win = window ? *window : make_int4(0, w, 0, h);
+  VL(), k_morph<DILATE, Load, Post><<<grid, 128, 0, st>>>(ld, post, dst, h, w, se, win);
   CKL();
   return 0;
 }

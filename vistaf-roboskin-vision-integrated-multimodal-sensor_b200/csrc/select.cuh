@@ -287,9 +287,14 @@ __global__ void __launch_bounds__(1024) k_sel_p2(Val val, Out out, SelectState* 
       if ((key >> 10) == p22) atomicAdd(&h3[key & 1023u], 1u);
     }
   } else {
-    for (long long i = threadIdx.x; i < n; i += 1024) {
-      float v;
-      if (val(b, i, v)) { const unsigned int key = f2key(v); if ((key >> 10) == p22) atomicAdd(&h3[key & 1023u], 1u); }
+    for (long long i0 = threadIdx.x; i0 < n; i0 += 4096) {          // four element fetches in flight per thread
+      float v[4];
+      bool ok[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) { const long long i = i0 + j * 1024; ok[j] = i < n && val(b, i, v[j]); }
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (ok[j]) { const unsigned int key = f2key(v[j]); if ((key >> 10) == p22) atomicAdd(&h3[key & 1023u], 1u); }
     }
   }
   __syncthreads();

@@ -564,6 +564,7 @@ struct FeatArgs {
   TempScal* sc; const DevModel* models; const int* gam; const int* cbr;
   float* fused; uint8_t *o_sat, *o_light, *o_support, *o_colorok, *o_source;
   int h, w;
+  int bx0, bx1, by0, by1;        // ROI bounding box: tiles outside it only write the NaN / zero background
   float color_lo, color_hi, ok_lo, ok_hi, blend_lo, blend_hi, final_lo, final_hi, chroma_min;
 };
 
@@ -575,6 +576,19 @@ __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
   const size_t plane = (size_t)h * w;
   const uint8_t* img = a.frames + (size_t)b * plane * 3;
   const int tid = threadIdx.y * FT_W + threadIdx.x;
+  if (x0 >= a.bx1 || x0 + FT_W <= a.bx0 || y0 >= a.by1 || y0 + FT_H <= a.by0) {
+    const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
+    if (x < w && y < h) {
+      const size_t bi = (size_t)b * plane + (size_t)y * w + x;
+      a.fused[bi] = __int_as_float(0x7fc00000);
+      if (a.o_sat) a.o_sat[bi] = 0;
+      if (a.o_light) a.o_light[bi] = 0;
+      if (a.o_support) a.o_support[bi] = 0;
+      if (a.o_colorok) a.o_colorok[bi] = 0;
+      if (a.o_source) a.o_source[bi] = 0;
+    }
+    return;
+  }
   // 5x5 Gaussian on uint8 uses BORDER_REFLECT_101 (cv2.GaussianBlur default)
   for (int e = tid; e < (FT_H + 4) * (FT_W + 4); e += FT_W * FT_H) {
     int ty = e / (FT_W + 4), tx = e - ty * (FT_W + 4);
@@ -709,11 +723,11 @@ struct FinalStore {
     }
   }
 };
-struct FinalVal {              // value stream for the median: final map over the ROI
-  const float* fin; const uint8_t* roi; long long plane;
+struct FinalVal {              // value stream for the median: final map over the ROI (rows of its bounding box only)
+  const float* fin; const uint8_t* roi; long long plane; long long off;     // off = first bounding-box row * width
   __device__ bool operator()(int b, long long i, float& v) const {
-    if (!roi[i]) return false;
-    v = fin[(long long)b * plane + i];
+    if (!roi[off + i]) return false;
+    v = fin[(long long)b * plane + off + i];
     return v == v;
   }
 };
@@ -945,10 +959,12 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   DarkLoad dl{maskA, p->roi, sat, sc, plane, W, p->y0, p->y1};
   MorphSE se_c = se_rect(P.close_kx | 1, P.close_ky | 1), se_o = se_rect(P.open_kx | 1, P.open_ky | 1);
   uint8_t* dark = O.dark ? O.dark + f0 * (size_t)npix : maskA;      // final dark mask destination
-  if (morph<true>(dl, PostId(), m1, H, W, nb, se_c, st)) return 1;
-  if (morph<false>(MaskLoad{m1, plane, W}, PostId(), m2, H, W, nb, se_c, st)) return 1;
-  if (morph<false>(MaskLoad{m2, plane, W}, PostId(), m1, H, W, nb, se_o, st)) return 1;
-  if (morph<true>(MaskLoad{m1, plane, W}, PostRoiEff{p->roi, sat, sc, plane, W}, dark, H, W, nb, se_o, st)) return 1;
+  // every plane of this chain is 0 outside the ROI bounding box grown by the structuring elements (<= 15 + 3 rows)
+  const int4 mwin = make_int4(p->x0 - 24, p->x1 + 24, p->y0 - 24, p->y1 + 24);
+  if (morph<true>(dl, PostId(), m1, H, W, nb, se_c, st, &mwin)) return 1;
+  if (morph<false>(MaskLoad{m1, plane, W}, PostId(), m2, H, W, nb, se_c, st, &mwin)) return 1;
+  if (morph<false>(MaskLoad{m2, plane, W}, PostId(), m1, H, W, nb, se_o, st, &mwin)) return 1;
+  if (morph<true>(MaskLoad{m1, plane, W}, PostRoiEff{p->roi, sat, sc, plane, W}, dark, H, W, nb, se_o, st, &mwin)) return 1;
   vistaf_stage_mark("T.features_models_fuse", st);
   // features, models, fusion
   FeatArgs fa;
@@ -961,6 +977,7 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   fa.o_colorok = O.color_ok ? O.color_ok + f0 * (size_t)npix : nullptr;
   fa.o_source = O.source ? O.source + f0 * (size_t)npix : nullptr;
   fa.h = H; fa.w = W;
+  fa.bx0 = p->x0; fa.bx1 = p->x1; fa.by0 = p->y0; fa.by1 = p->y1;
   fa.color_lo = P.color_t_min - 5.0f; fa.color_hi = P.color_t_max + 5.0f;
   fa.ok_lo = P.color_t_min - P.guard_band; fa.ok_hi = P.color_t_max + P.guard_band;
   fa.blend_lo = P.color_t_max - P.switch_margin; fa.blend_hi = P.color_t_max + P.switch_margin;
@@ -972,11 +989,13 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   float* fin = O.final_map + f0 * (size_t)npix;
   FusedLoad fl{fa.fused, plane, W};
   FinalStore fs{p->roi, fin, sc, plane, W, P.final_t_min, P.final_t_max, 0.0, 0.0, 3.0e38f, 0.f, 0u};
-  if (gauss_blur(fl, fs, tmp, H, W, nb, p->g_across, p->g_along, st)) return 1;
+  const BlurWindow fwin{p->x0, p->x1, p->y0, p->y1};      // the final map is NaN outside the ROI whatever the blur gives
+  if (gauss_blur(fl, fs, tmp, H, W, nb, p->g_across, p->g_along, st, &fwin)) return 1;
   vistaf_stage_mark("T.stats_median", st);
-  FinalVal fv{fin, p->roi, plane};
+  FinalVal fv{fin, p->roi, plane, (long long)p->y0 * W};
+  const long long nsel = (long long)(p->y1 - p->y0) * W;
   if (sel_reset(sel, nb, st)) return 1;
-  if (select_quantile(fv, sel, (long long)npix, nb, -1.0f, true, st)) return 1;
+  if (select_quantile(fv, sel, nsel, nb, -1.0f, true, st)) return 1;
   VL(), k_temp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, sel, O.records + f0, nb, W / 2, H / 2);
   CKL();
   vistaf_stage_mark("", st);

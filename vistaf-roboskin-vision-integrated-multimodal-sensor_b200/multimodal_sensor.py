@@ -304,10 +304,15 @@ class MultimodalPlan:
         tstream.wait_stream(main)
         with t.cuda.stream(tstream):
             res = {"temp": self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None)}    # async
+        # the front of the FTP chain (bad pixels, Telea fill, normalisation) does not read the reference frame: it is
+        # issued first, so the reference's own serial chain (one frame, one host read of the carrier) runs beside it
+        gray = self.ftp.crop_gray(frames_dev)
+        self.ftp.begin(gray)
         with t.cuda.stream(self._side):
             self.set_reference(ref_frame_dev)     # host returns when the side stream has the carrier
         main.wait_stream(self._side)
-        gray = self.ftp.crop_gray(frames_dev)
+        for s in self.ftp.lane_streams:
+            s.wait_stream(self._side)
         res["ftp"] = self.ftp.run(gray, masks=masks, out=cache["ftp"] if cache else None)
         main.wait_stream(tstream)
         return self._finish(res, B, cache, key, reuse_outputs)

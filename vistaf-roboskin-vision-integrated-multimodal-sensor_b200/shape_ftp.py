@@ -182,6 +182,10 @@ class FtpPlan:
         self.lane_ws = [self.torch.empty(self.ws_bytes, dtype=self.torch.uint8, device="cuda") for _ in range(self.lanes)]
         self.lane_streams = [self.torch.cuda.Stream() for _ in range(self.lanes)] if self.lanes > 1 else []
         self.ws = self.lane_ws[0]
+        # the reference frame is demodulated in its own one-frame workspace, so it can run beside a batch's begin()
+        self.ref_ws_bytes = int(N.lib().vistaf_ftp_workspace_bytes(self.handle, 1))
+        self.ref_ws = self.torch.empty(self.ref_ws_bytes, dtype=self.torch.uint8, device="cuda")
+        self._begun = None
         self.active_lanes = self.lanes        # set to 1 to serialise a batch on the current stream (stage timing)
         self.ref_info = None
 
@@ -209,7 +213,7 @@ class FtpPlan:
         """ref_gray_dev: uint8 CUDA [h,w] crop of the reference frame."""
         assert tuple(ref_gray_dev.shape) == (self.h, self.w) and ref_gray_dev.is_contiguous()
         info = N.FtpReferenceInfo()
-        N.check(N.lib().vistaf_ftp_set_reference(self.handle, ref_gray_dev.data_ptr(), self.ws.data_ptr(), self.ws_bytes,
+        N.check(N.lib().vistaf_ftp_set_reference(self.handle, ref_gray_dev.data_ptr(), self.ref_ws.data_ptr(), self.ref_ws_bytes,
                                                  C.byref(info), self._stream()), "ftp_set_reference")
         self.ref_info = info
         return info
@@ -227,13 +231,40 @@ class FtpPlan:
         N.check(N.lib().vistaf_ftp_workspace_plane(self.handle, chunk or self.lane_frames, name.encode(), C.byref(off), C.byref(nb)))
         return self.ws[off.value:off.value + nb.value]
 
+    def _slices(self, B):
+        L = min(self.lanes, max(1, int(self.active_lanes)))
+        if L == 1 or B < 2 * L:
+            return [(0, B)]
+        per = -(-B // L)
+        return [(k * per, min(B, (k + 1) * per)) for k in range(L) if k * per < B]
+
+    def begin(self, def_gray_dev) -> bool:
+        """Issue the reference-independent front of the chain (bad pixels, Telea fill, normalisation) for a batch, one
+        slice per lane; may be called BEFORE set_reference.  Returns False (nothing issued) when a slice does not fit
+        its lane workspace in one chunk; run() then does the whole chain."""
+        t = self.torch
+        B = int(def_gray_dev.shape[0])
+        sl = self._slices(B)
+        if any(hi - lo > self.lane_frames for lo, hi in sl):
+            return False
+        cur = t.cuda.current_stream()
+        for k, (lo, hi) in enumerate(sl):
+            s = self.lane_streams[k] if len(sl) > 1 else cur
+            if s is not cur:
+                s.wait_stream(cur)
+            N.check(N.lib().vistaf_ftp_batch_begin(self.handle, def_gray_dev[lo:].data_ptr(), hi - lo, self.lane_ws[k].data_ptr(),
+                                                   self.ws_bytes, C.c_void_p(s.cuda_stream)), "ftp_batch_begin")
+        self._begun = (def_gray_dev.data_ptr(), B, sl)
+        return True
+
     def run(self, def_gray_dev, masks: bool = True, out: Optional[dict] = None) -> dict:
-        """def_gray_dev: uint8 CUDA [B,h,w] (aligned crops).  Returns dict of CUDA tensors."""
+        """def_gray_dev: uint8 CUDA [B,h,w] (aligned crops).  Returns dict of CUDA tensors.  After begin() on the same
+        tensor only the reference-dependent rest of the chain is issued."""
         t = self.torch
         if self.ref_info is None:
             raise RuntimeError("FtpPlan.run: call set_reference first")
         assert def_gray_dev.is_cuda and def_gray_dev.dtype == t.uint8 and def_gray_dev.is_contiguous()
-        B = def_gray_dev.shape[0]
+        B = int(def_gray_dev.shape[0])
         assert tuple(def_gray_dev.shape[1:]) == (self.h, self.w)
         if out is None:
             out = {"height_mm": t.empty((B, self.h, self.w), dtype=t.float32, device="cuda"),
@@ -241,27 +272,28 @@ class FtpPlan:
             if masks:
                 for k in MASK_NAMES:
                     out[k] = t.empty((B, self.h, self.w), dtype=t.uint8, device="cuda")
+        begun = self._begun is not None and self._begun[:2] == (def_gray_dev.data_ptr(), B)
+        sl = self._begun[2] if begun else self._slices(B)
+        self._begun = None
+
         def call(lo, hi, ws, stream):
             O = N.FtpOutputs()
             O.height_mm, O.records = out["height_mm"][lo:].data_ptr(), out["records"][lo:].data_ptr()
             for k in MASK_NAMES:
                 setattr(O, k, out[k][lo:].data_ptr() if k in out else None)
-            N.check(N.lib().vistaf_ftp_batch(self.handle, def_gray_dev[lo:].data_ptr(), hi - lo, C.byref(O), ws.data_ptr(),
-                                             self.ws_bytes, C.c_void_p(stream.cuda_stream)), "ftp_batch")
+            fn = N.lib().vistaf_ftp_batch_finish if begun else N.lib().vistaf_ftp_batch
+            N.check(fn(self.handle, def_gray_dev[lo:].data_ptr(), hi - lo, C.byref(O), ws.data_ptr(),
+                       self.ws_bytes, C.c_void_p(stream.cuda_stream)), "ftp_batch")
 
         cur = t.cuda.current_stream()
-        L = min(self.lanes, max(1, int(self.active_lanes)))
-        if L == 1 or B < 2 * L:
-            call(0, B, self.ws, cur)
+        if len(sl) == 1:
+            call(0, B, self.lane_ws[0], cur)
             return out
-        per = -(-B // L)
         used = []
-        for k in range(L):
-            lo, hi = k * per, min(B, (k + 1) * per)
-            if lo >= hi:
-                break
+        for k, (lo, hi) in enumerate(sl):
             s = self.lane_streams[k]
-            s.wait_stream(cur)
+            if not begun:
+                s.wait_stream(cur)             # (a begun slice is already ordered after the inputs on its lane stream)
             call(lo, hi, self.lane_ws[k], s)
             used.append(s)
         for s in used:
