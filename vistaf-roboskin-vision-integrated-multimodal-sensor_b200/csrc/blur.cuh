@@ -34,21 +34,36 @@ static inline GaussKernel make_gauss(double sigma, int ksize_override = 0) {
   return g;
 }
 
-// Optional active window [x0,x1) x [y0,y1): outputs outside it are not computed -- the column pass hands the Store a
-// 0 there (for Stores whose result does not depend on the value outside the window, e.g. NaN outside a ROI) and the
-// row pass skips rows / segments no active column block reads.
-struct BlurWindow { int x0, x1, y0, y1; };
+// Optional active window.  The column pass computes outputs only in blocks that overlap [x0,x1) x [y0,y1); elsewhere
+// it hands the Store the per-frame constant *fill (0 when fill is null).  The row pass computes only rows [ry0,ry1)
+// (and row segments near the window); the column pass reads every other row as the per-frame constant *rowfill.
+// Two uses: (a) a Store that ignores the value outside a ROI (fill = rowfill = null, [ry0,ry1) = the rows the active
+// column blocks read); (b) an input that is a per-frame constant c outside a bounding box: rows outside the box blur
+// to rowfill = R(c) and pixels farther than the kernel radius from it to fill = C(R(c)), both computed once per
+// frame with the same fmaf sequence as the kernels below (gauss_constant), so the result is bit-identical.
+struct BlurWindow {
+  int x0, x1, y0, y1;
+  int ry0, ry1;
+  const float* fill; const float* rowfill; size_t stride;   // per-frame values: *(float*)((char*)fill + b * stride)
+};
+__device__ __forceinline__ float blur_frame_const(const float* p, size_t stride, int b) {
+  return p ? *(const float*)((const char*)p + (size_t)b * stride) : 0.f;
+}
+// blur of a constant row / column: the kernels' accumulation order (taps 0..kpad-1, zero-padded)
+__device__ __forceinline__ float gauss_constant(const float* w, int kpad, float c) {
+  float acc = 0.f;
+  for (int k = 0; k < kpad; k++) acc = fmaf(w[k], c, acc);
+  return acc;
+}
 
 // Row pass.  grid = (ceil(w/1280), h, batch), block = 160.  Load: float operator()(int b,int y,int x).
 template <class Load>
 __global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* __restrict__ tmp, int h, int w,
-                                                                 long long plane, GaussKernel g, BlurWindow win, int rady) {   // rady: column radius + column block height
+                                                                 long long plane, GaussKernel g, BlurWindow win) {
   __shared__ float s[8 * BLUR_ROW_PITCH];
   __shared__ float wk[BLUR_MAXK];
   const int b = blockIdx.z, y = blockIdx.y, x0 = blockIdx.x * BLUR_ROW_SEG;
-  // rows the active column blocks read: the window widened by the column radius and one block height (blocks are
-  // aligned to their own grid); border reflection maps into that same range
-  if (y < win.y0 - rady || y >= win.y1 + rady || x0 >= win.x1 + 32 || x0 + BLUR_ROW_SEG <= win.x0 - 32) return;
+  if (y < win.ry0 || y >= win.ry1 || x0 >= win.x1 + 32 || x0 + BLUR_ROW_SEG <= win.x0 - 32) return;
   const int rad = g.ksize >> 1;
   const int need = BLUR_ROW_SEG + g.kpad + 8;
   for (int e = threadIdx.x; e < need; e += BLUR_ROW_THREADS) {
@@ -98,7 +113,9 @@ __global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int 
     if (x < w) {
       const int r0o = threadIdx.y * 8;
 #pragma unroll
-      for (int j = 0; j < 8; j++) { const int y = y0 + r0o + j; if (y < h) sto(b, y, x, 0.f); }
+      const float fv = blur_frame_const(win.fill, win.stride, b);
+#pragma unroll
+      for (int j = 0; j < 8; j++) { const int y = y0 + r0o + j; if (y < h) sto(b, y, x, fv); }
     }
     sto.finish(b);
     return;
@@ -106,10 +123,14 @@ __global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int 
   const int rad = g.ksize >> 1;
   const int need = TY + g.kpad + 8;
   const float* src = tmp + (long long)b * plane;
+  const float rowfill = blur_frame_const(win.rowfill, win.stride, b);
   for (int e = threadIdx.y; e < need; e += blockDim.y) {
     int y = y0 - rad + e;
     float v = 0.f;
-    if (e < TY + g.ksize - 1 && x < w && y < h + rad) v = src[(long long)reflect101(y, h) * w + x];
+    if (e < TY + g.ksize - 1 && x < w && y < h + rad) {
+      const int yr = reflect101(y, h);
+      v = (yr >= win.ry0 && yr < win.ry1) ? src[(long long)yr * w + x] : rowfill;
+    }
     sc[e * 32 + threadIdx.x] = v;
   }
   const int tid = threadIdx.y * 32 + threadIdx.x;
@@ -147,11 +168,15 @@ template <class Load, class Store>
 static int gauss_blur(Load ld, Store st, float* tmp, int h, int w, int batch, const GaussKernel& gx,
                       const GaussKernel& gy, cudaStream_t stream, const BlurWindow* window = nullptr) {
   const long long plane = (long long)h * w;
-  const BlurWindow win = window ? *window : BlurWindow{0, w, 0, h};
-  dim3 g1(cdiv(w, BLUR_ROW_SEG), h, batch);
-  VL(), k_blur_rows<Load><<<g1, BLUR_ROW_THREADS, 0, stream>>>(ld, tmp, h, w, plane, gx, win, (gy.ksize >> 1) + 8 * (gy.ksize > 100 ? 32 : 16));
-  CKL();
   const int tyt = gy.ksize > 100 ? 32 : 16;
+  BlurWindow win = window ? *window : BlurWindow{0, w, 0, h, 0, h, nullptr, nullptr, 0};
+  if (window && !window->rowfill) {           // rows the active column blocks (aligned to their own grid) read
+    win.ry0 = win.y0 - (gy.ksize >> 1) - 8 * tyt;
+    win.ry1 = win.y1 + (gy.ksize >> 1) + 8 * tyt;
+  }
+  dim3 g1(cdiv(w, BLUR_ROW_SEG), h, batch);
+  VL(), k_blur_rows<Load><<<g1, BLUR_ROW_THREADS, 0, stream>>>(ld, tmp, h, w, plane, gx, win);
+  CKL();
   dim3 blk(32, tyt), g2(cdiv(w, 32), cdiv(h, 8 * tyt), batch);
   size_t sm = sizeof(float) * 32 * (size_t)(8 * tyt + gy.kpad + 8);
   static bool attr_done = false;   // per template instantiation

@@ -1334,7 +1334,12 @@ extern "C" int vistaf_ftp_set_reference(VistafFtpPlan* p, const uint8_t* ref_gra
 // The fit runs over groups of IRLS_GROUP frames: one group's samples and masks (7 MB per frame) stay resident in the
 // 126 MB L2 across the ~30 sweeps of the six iterations, so only the first sweep of a group reads HBM.  Per
 // iteration: accumulate (+ solve in the last block), median of the residuals, median of |r - med| (3 launches each).
-#define IRLS_GROUP 8
+#define IRLS_GROUP_DEFAULT 64
+static int irls_group() {
+  static int g = 0;
+  if (!g) { const char* e = getenv("VISTAF_IRLS_GROUP"); g = e ? atoi(e) : IRLS_GROUP_DEFAULT; if (g < 1) g = 1; }
+  return g;
+}
 template <bool ORDER2>
 static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, SelectState* sel, float* zc, unsigned int* pc,
                     float* rc, int nb, int mode, cudaStream_t st) {
@@ -1342,8 +1347,9 @@ static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, S
   const FitGeom g = make_fitgeom(p);
   unsigned int* lists = sel_lists(sel, nb);
   VL(), k_irls_begin<<<nb, 1, 0, st>>>(sc, mode);
-  for (int g0 = 0; g0 < nb; g0 += IRLS_GROUP) {
-    const int ng = nb - g0 < IRLS_GROUP ? nb - g0 : IRLS_GROUP;
+  const int G = irls_group();
+  for (int g0 = 0; g0 < nb; g0 += G) {
+    const int ng = nb - g0 < G ? nb - g0 : G;
     const float* zg = z + (size_t)g0 * npix;
     float* zcg = zc + (size_t)g0 * npix;
     unsigned int* pcg = pc + (size_t)g0 * npix;

@@ -36,7 +36,7 @@ struct SelectState {           // one per frame, device memory
   unsigned int pad_[3];
 };
 
-static inline size_t sel_ws_bytes(int chunk) { return (size_t)chunk * (sizeof(SelectState) + (size_t)SEL_CAP * 4); }
+static inline size_t sel_ws_bytes(int chunk, unsigned int cap = SEL_CAP) { return (size_t)chunk * (sizeof(SelectState) + (size_t)cap * 4); }
 __host__ __device__ inline unsigned int* sel_lists(SelectState* st, int batch) { return (unsigned int*)(st + batch); }
 
 // NumPy >= 2 evaluates the virtual index of a float32 sample in float32:
@@ -143,7 +143,7 @@ __device__ __forceinline__ unsigned int sel_next_bin(const unsigned int* hist, u
 // ---- S1: level-1 histogram (top 11 key bits) + rank location by the last block of each frame.
 template <class Val>
 __global__ void __launch_bounds__(256) k_sel_s1(Val val, SelectState* st, long long n, float q0, const float* qv,
-                                                size_t qstride) {
+                                                size_t qstride, unsigned int cap) {
   __shared__ unsigned int h[SEL_BINS];
   __shared__ unsigned int sh[34];
   __shared__ unsigned int s_last;
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(256) k_sel_s1(Val val, SelectState* st, long l
   if (threadIdx.x == 0) {
     const unsigned int inbin = h[b1];
     s.count = count; s.k = k; s.b1 = b1; s.below = below; s.inbin = inbin; s.nlist = 0; s.ticket = 0;
-    s.mode = inbin <= (unsigned int)SEL_CAP ? 1u : 2u;
+    s.mode = inbin <= cap ? 1u : 2u;
     s.need_next = (k + 1 < count && k + 1 - below >= inbin) ? 1u : 0u;
     s.min_next = 0xffffffffu;
   }
@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(256) k_sel_s1(Val val, SelectState* st, long l
 
 // ---- S2: keys of bin b1 -> level-2 histogram (bits [20:10]) and, in gather mode, the per-frame list.
 template <class Val>
-__global__ void __launch_bounds__(256) k_sel_s2(Val val, SelectState* st, unsigned int* lists, long long n) {
+__global__ void __launch_bounds__(256) k_sel_s2(Val val, SelectState* st, unsigned int* lists, long long n, unsigned int cap) {
   __shared__ unsigned int h[SEL_BINS];
   const int b = blockIdx.y, lane = threadIdx.x & 31;
   SelectState& s = st[b];
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(256) k_sel_s2(Val val, SelectState* st, unsign
   if (mode == 0) return;
   const unsigned int b1 = s.b1;
   const bool need_next = s.need_next != 0, gather = mode == 1;
-  unsigned int* list = lists + (size_t)b * SEL_CAP;
+  unsigned int* list = lists + (size_t)b * cap;
   for (int i = threadIdx.x; i < SEL_BINS; i += 256) h[i] = 0;
   __syncthreads();
   unsigned int mn = 0xffffffffu;
@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(256) k_sel_s2(Val val, SelectState* st, unsign
       base = __shfl_sync(0xffffffffu, base, 0);
       if (take) {
         const unsigned int at = base + (unsigned int)__popc(bits & ((1u << lane) - 1u));
-        if (at < (unsigned int)SEL_CAP) list[at] = key;
+        if (at < cap) list[at] = key;
       }
     }
   }
@@ -259,7 +259,7 @@ struct SelNoOut { __device__ void operator()(int, float, unsigned int) const {} 
 // unsigned int count), called by thread 0.
 template <class Val, class Out>
 __global__ void __launch_bounds__(1024) k_sel_p2(Val val, Out out, SelectState* st, unsigned int* lists, long long n, float q0,
-                                                 const float* qv, size_t qstride) {
+                                                 const float* qv, size_t qstride, unsigned int cap) {
   __shared__ unsigned int h3[1024];
   __shared__ unsigned int sh[34];
   __shared__ unsigned int s_min;
@@ -272,8 +272,8 @@ __global__ void __launch_bounds__(1024) k_sel_p2(Val val, Out out, SelectState* 
     return;                                             // S1 left hist / nlist / ticket clean
   }
   n = sel_limit(val, b, n, 0);
-  const unsigned int* list = lists + (size_t)b * SEL_CAP;
-  const unsigned int nl = min(s.nlist, (unsigned int)SEL_CAP);
+  const unsigned int* list = lists + (size_t)b * cap;
+  const unsigned int nl = min(s.nlist, cap);
   const unsigned int count = s.count, k = s.k, b1 = s.b1, inbin = s.inbin;
   const unsigned int r0 = k - s.below;                  // rank inside bin b1
   unsigned int sb, below2;
@@ -343,16 +343,17 @@ __global__ void __launch_bounds__(1024) k_sel_p2(Val val, Out out, SelectState* 
 // stream (a first-sweep functor may materialise the values it computes for the second to re-read).
 template <class Val1, class Val2, class Out>
 static int select_quantile_out2(Val1 val1, Val2 val2, Out out, SelectState* st, unsigned int* lists, long long n, int batch,
-                                float q, cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0) {
+                                float q, cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0,
+                                unsigned int cap = SEL_CAP) {
   int gx = (148 * 6 + batch - 1) / batch;
   const int gmax = (int)((n + 1023) / 1024);
   if (gx > gmax) gx = gmax;
   if (gx > 592) gx = 592;
   if (gx < 1) gx = 1;
   dim3 grid(gx, batch);
-  VL(), k_sel_s1<Val1><<<grid, 256, 0, stream>>>(val1, st, n, q, qv, qstride);
-  VL(), k_sel_s2<Val2><<<grid, 256, 0, stream>>>(val2, st, lists, n);
-  VL(), k_sel_p2<Val2, Out><<<batch, 1024, 0, stream>>>(val2, out, st, lists, n, q, qv, qstride);
+  VL(), k_sel_s1<Val1><<<grid, 256, 0, stream>>>(val1, st, n, q, qv, qstride, cap);
+  VL(), k_sel_s2<Val2><<<grid, 256, 0, stream>>>(val2, st, lists, n, cap);
+  VL(), k_sel_p2<Val2, Out><<<batch, 1024, 0, stream>>>(val2, out, st, lists, n, q, qv, qstride, cap);
   CKL();
   return 0;
 }
@@ -364,7 +365,7 @@ static int select_quantile_out(Val val, Out out, SelectState* st, unsigned int* 
 // call-site compatible form: the key lists live right behind the `batch` states (sel_ws_bytes)
 template <class Val>
 static int select_quantile(Val val, SelectState* st, long long n, int batch, float q, bool need_count,
-                           cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0) {
+                           cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0, unsigned int cap = SEL_CAP) {
   (void)need_count;
-  return select_quantile_out(val, SelNoOut(), st, sel_lists(st, batch), n, batch, q, stream, qv, qstride);
+  return select_quantile_out2(val, val, SelNoOut(), st, sel_lists(st, batch), n, batch, q, stream, qv, qstride, cap);
 }

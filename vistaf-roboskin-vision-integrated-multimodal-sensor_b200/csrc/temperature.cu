@@ -11,8 +11,11 @@
 #include <new>
 
 #define TOPK 16
-#define COLS_PER_BLOCK 4
+#define COLS_PER_BLOCK 2      // 2 columns x 2 buffers x 2161 float2 = 69 KB: three blocks per SM overlap each other's barriers
+#define COLS_THREADS 256
 #define MAXBAND 45            // 2*22+1
+#define TEMP_SEL_CAP (1u << 20) // key-list capacity per frame for the median of the final map: temperatures of a frame
+                                // crowd into one or two top-11-bit float bins (values in [20, 75])
 
 struct Cand { float mag; int ky, kx; int pad; };
 
@@ -35,6 +38,8 @@ struct TempScal {             // per-frame scalars living in the workspace
   double t_sum, t_sumsq;
   float t_min, t_max;
   unsigned int t_count, pad;
+  float blur_rc, blur_cc;       // sigma-20 blur of the constant background: row pass R(median), column pass C(R(median))
+  float pad2[2];
 };
 
 struct VistafTempPlan {
@@ -183,6 +188,13 @@ struct IllumStore {
     if (threadIdx.x == 0 && threadIdx.y == 0 && v[0] != 0.0) atomicAdd(&sc[b].norm_sum, v[0]);
   }
 };
+
+// blur of the median-filled background far from the ROI: the exact value both passes of gauss_blur produce there
+__global__ void k_temp_blur_consts(TempScal* sc, GaussKernel g) {
+  TempScal& s = sc[blockIdx.x];
+  s.blur_rc = gauss_constant(g.w, g.kpad, s.median);
+  s.blur_cc = gauss_constant(g.w, g.kpad, s.blur_rc);
+}
 
 __global__ void k_temp_mu(TempScal* sc) {
   TempScal& s = sc[blockIdx.x];
@@ -785,7 +797,7 @@ static void temp_layout(const VistafTempPlan* p, int chunk, TempWs& L) {
   L.m2 = take(c * npix);
   L.cand = take(c * (size_t)p->nblk_cols * TOPK * sizeof(Cand));
   L.scal = take(c * sizeof(TempScal));
-  L.sel = take(sel_ws_bytes((int)c));
+  L.sel = take(sel_ws_bytes((int)c, TEMP_SEL_CAP));
   L.total = o;
 }
 
@@ -934,13 +946,19 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   // illumination normalisation
   IllumLoad il{gray8, p->roi, sc, plane, W};
   IllumStore is{gray8, p->roi, sat, sc, norm, plane, W, 0.0};
-  if (gauss_blur(il, is, tmp, H, W, nb, p->g_illum, p->g_illum, st)) return 1;
+  // outside the ROI the image is the per-frame median: only the ROI bounding box grown by the kernel radius is blurred,
+  // everything else takes the constants R(median) / C(R(median)) (bit-identical to blurring the whole frame)
+  VL(), k_temp_blur_consts<<<nb, 1, 0, st>>>(sc, p->g_illum);
+  const int irad = p->g_illum.ksize >> 1;
+  const BlurWindow iwin{p->x0 - irad, p->x1 + irad, p->y0 - irad, p->y1 + irad, p->y0, p->y1, &sc[0].blur_cc, &sc[0].blur_rc,
+                        sizeof(TempScal)};
+  if (gauss_blur(il, is, tmp, H, W, nb, p->g_illum, p->g_illum, st, &iwin)) return 1;
   VL(), k_temp_mu<<<nb, 1, 0, st>>>(sc);
   vistaf_stage_mark("T.fft_rows", st);
   // forward FFT + carrier peak
   VL(), k_temp_fft_rows<<<dim3(cdiv(H, 2), nb), 256, (size_t)W * 16, st>>>(norm, A, sc, p->fw, H, Wh);
   vistaf_stage_mark("T.fft_cols_peaks", st);
-  VL(), k_temp_fft_cols_peaks<<<dim3(p->nblk_cols, nb), 512, (size_t)COLS_PER_BLOCK * (H + 1) * 16, st>>>(A, cand, p->fh, W, Wh,
+  VL(), k_temp_fft_cols_peaks<<<dim3(p->nblk_cols, nb), COLS_THREADS, (size_t)COLS_PER_BLOCK * (H + 1) * 16, st>>>(A, cand, p->fh, W, Wh,
                                                                                                   P.dc_exclusion);
   const int ncand = p->nblk_cols * TOPK;
   VL(), k_temp_peak_select<<<nb, 256, (size_t)2 * ncand * 4, st>>>(cand, sc, ncand, H, W, P.dc_exclusion, P.peak_max_dy_frac);
@@ -989,13 +1007,13 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   float* fin = O.final_map + f0 * (size_t)npix;
   FusedLoad fl{fa.fused, plane, W};
   FinalStore fs{p->roi, fin, sc, plane, W, P.final_t_min, P.final_t_max, 0.0, 0.0, 3.0e38f, 0.f, 0u};
-  const BlurWindow fwin{p->x0, p->x1, p->y0, p->y1};      // the final map is NaN outside the ROI whatever the blur gives
+  const BlurWindow fwin{p->x0, p->x1, p->y0, p->y1, 0, 0, nullptr, nullptr, 0};      // the final map is NaN outside the ROI whatever the blur gives
   if (gauss_blur(fl, fs, tmp, H, W, nb, p->g_across, p->g_along, st, &fwin)) return 1;
   vistaf_stage_mark("T.stats_median", st);
   FinalVal fv{fin, p->roi, plane, (long long)p->y0 * W};
   const long long nsel = (long long)(p->y1 - p->y0) * W;
   if (sel_reset(sel, nb, st)) return 1;
-  if (select_quantile(fv, sel, nsel, nb, -1.0f, true, st)) return 1;
+  if (select_quantile(fv, sel, nsel, nb, -1.0f, true, st, nullptr, 0, TEMP_SEL_CAP)) return 1;
   VL(), k_temp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, sel, O.records + f0, nb, W / 2, H / 2);
   CKL();
   vistaf_stage_mark("", st);
