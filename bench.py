@@ -231,10 +231,27 @@ def main():
 
     dev2, ref2 = torch.empty_like(dev), torch.empty_like(ref_dev)
 
+    copy_stream = torch.cuda.Stream()
+    n_slices = max(1, a.lanes_ftp, a.lanes_temp)
+
     def step_e2e():
-        ref2.copy_(ref_pinned, non_blocking=True)
-        dev2.copy_(pinned, non_blocking=True)
-        return plan.step(ref2, dev2, masks=False)["records"].cpu()
+        """Host -> device staging of the reference and of the frames in slices on a copy stream (events mark each slice
+        ready, so a lane starts as soon as its frames have landed), the step through the public API, records to host."""
+        main = torch.cuda.current_stream()
+        copy_stream.wait_stream(main)             # the previous step has finished reading dev2 / ref2
+        ready = []
+        with torch.cuda.stream(copy_stream):
+            ref2.copy_(ref_pinned, non_blocking=True)
+            ev_ref = torch.cuda.Event()
+            ev_ref.record(copy_stream)
+            per = -(-F // n_slices)
+            for lo in range(0, F, per):
+                hi = min(F, lo + per)
+                dev2[lo:hi].copy_(pinned[lo:hi], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+                ready.append((lo, hi, ev))
+        return plan.step(ref2, dev2, masks=False, ready=ready, ref_ready=ev_ref)["records"].cpu()
 
     def barrier():
         if world > 1:

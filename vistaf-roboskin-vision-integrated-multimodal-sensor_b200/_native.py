@@ -226,3 +226,12 @@ def require_cuda():
     if not torch.cuda.is_available():
         raise RuntimeError("VISTAF B200 path needs a CUDA device; there is no CPU fallback")
     return torch
+
+
+def wait_ready(stream, ready, lo, hi):
+    """`ready`: optional list of (lo, hi, torch.cuda.Event) -- frames [lo, hi) of the batch are valid once the event has
+    completed (sliced host->device staging).  Makes `stream` wait for every slice overlapping frames [lo, hi)."""
+    if ready:
+        for a, b, ev in ready:
+            if a < hi and b > lo:
+                stream.wait_event(ev)

@@ -286,14 +286,23 @@ class MultimodalPlan:
         self._tstream = self.torch.cuda.Stream() if mode == "multimodal" else None
         self.concurrent = True                # False: temperature half, then FTP half, on the current stream (stage timing)
 
-    def step(self, ref_frame_dev, frames_dev, masks: bool = False, reuse_outputs: bool = True) -> dict:
+    def step(self, ref_frame_dev, frames_dev, masks: bool = False, reuse_outputs: bool = True, ready=None, ref_ready=None) -> dict:
         """One batch against a (new) reference frame.  The reference-frame half (demodulation of one frame: a short,
         latency-bound chain of kernels plus one small device->host read of the carrier peak) runs on a side stream
         while the temperature half of the batch runs on the current stream; the FTP batch follows both."""
         t = self.torch
         if self._side is None:
-            self.set_reference(ref_frame_dev)
-            return self.run(frames_dev, masks, reuse_outputs)
+            if ref_ready is not None:
+                t.cuda.current_stream().wait_event(ref_ready)
+            if self.ftp is not None:
+                gray = self.ftp.begin(frames_dev=frames_dev, ready=ready)
+                self.set_reference(ref_frame_dev)
+                B = int(frames_dev.shape[0])
+                key = (B, bool(masks))
+                cache = self._out.get(key) if reuse_outputs else None
+                res = {"ftp": self.ftp.run(gray, masks=masks, out=cache["ftp"] if cache else None)}
+                return self._finish(res, B, cache, key, reuse_outputs)
+            return self.run(frames_dev, masks, reuse_outputs, ready=ready)
         main = t.cuda.current_stream()
         B = int(frames_dev.shape[0])
         key = (B, bool(masks))
@@ -303,12 +312,13 @@ class MultimodalPlan:
         tstream = self._tstream if self.concurrent else main
         tstream.wait_stream(main)
         with t.cuda.stream(tstream):
-            res = {"temp": self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None)}    # async
+            res = {"temp": self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None, ready=ready)}    # async
         # the front of the FTP chain (bad pixels, Telea fill, normalisation) does not read the reference frame: it is
         # issued first, so the reference's own serial chain (one frame, one host read of the carrier) runs beside it
-        gray = self.ftp.crop_gray(frames_dev)
-        self.ftp.begin(gray)
+        gray = self.ftp.begin(frames_dev=frames_dev, ready=ready)
         with t.cuda.stream(self._side):
+            if ref_ready is not None:
+                self._side.wait_event(ref_ready)
             self.set_reference(ref_frame_dev)     # host returns when the side stream has the carrier
         main.wait_stream(self._side)
         for s in self.ftp.lane_streams:
@@ -322,7 +332,7 @@ class MultimodalPlan:
         if self.ftp is not None:
             return self.ftp.set_reference(self.ftp.crop_gray(ref_frame_dev[None])[0].contiguous())
 
-    def run(self, frames_dev, masks: bool = False, reuse_outputs: bool = True) -> dict:
+    def run(self, frames_dev, masks: bool = False, reuse_outputs: bool = True, ready=None) -> dict:
         """frames_dev: uint8 CUDA [B,H,W,3].  Returns {"ftp": {...}, "temp": {...}, "records": uint8 [B,184]}."""
         t = self.torch
         B = int(frames_dev.shape[0])
@@ -335,10 +345,11 @@ class MultimodalPlan:
             if forked:                            # temperature half beside the FTP half
                 self._tstream.wait_stream(cur)
                 with t.cuda.stream(self._tstream):
-                    res["temp"] = self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None)
+                    res["temp"] = self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None, ready=ready)
             else:
-                res["temp"] = self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None)
+                res["temp"] = self.temp.run(frames_dev, masks=masks, out=cache["temp"] if cache else None, ready=ready)
         if self.ftp is not None:
+            N.wait_ready(cur, ready, 0, B)
             gray = self.ftp.crop_gray(frames_dev)
             res["ftp"] = self.ftp.run(gray, masks=masks, out=cache["ftp"] if cache else None)
         if forked:

@@ -238,24 +238,42 @@ class FtpPlan:
         per = -(-B // L)
         return [(k * per, min(B, (k + 1) * per)) for k in range(L) if k * per < B]
 
-    def begin(self, def_gray_dev) -> bool:
+    def begin(self, def_gray_dev=None, frames_dev=None, ready=None):
         """Issue the reference-independent front of the chain (bad pixels, Telea fill, normalisation) for a batch, one
-        slice per lane; may be called BEFORE set_reference.  Returns False (nothing issued) when a slice does not fit
-        its lane workspace in one chunk; run() then does the whole chain."""
+        slice per lane; may be called BEFORE set_reference.  Input: cropped gray frames, or full BGR frames (cropped here,
+        slice by slice on the lane streams; `ready` = [(lo, hi, event)] marks when slices of frames_dev become valid).
+        Returns the gray tensor to hand to run().  When a slice does not fit its lane workspace in one chunk nothing is
+        issued ahead and run() does the whole chain."""
         t = self.torch
-        B = int(def_gray_dev.shape[0])
-        sl = self._slices(B)
-        if any(hi - lo > self.lane_frames for lo, hi in sl):
-            return False
         cur = t.cuda.current_stream()
+        B = int((def_gray_dev if def_gray_dev is not None else frames_dev).shape[0])
+        sl = self._slices(B)
+        fits = all(hi - lo <= self.lane_frames for lo, hi in sl)
+        if def_gray_dev is None:
+            if getattr(self, "_gray", None) is None or self._gray.shape[0] != B:
+                self._gray = t.empty((B, self.h, self.w), dtype=t.uint8, device="cuda")
+            gray = self._gray
+            if not fits or len(sl) == 1:
+                N.wait_ready(cur, ready, 0, B)
+                gray = self.crop_gray(frames_dev)
+        else:
+            gray = def_gray_dev
+        if not fits:
+            return gray
         for k, (lo, hi) in enumerate(sl):
             s = self.lane_streams[k] if len(sl) > 1 else cur
             if s is not cur:
                 s.wait_stream(cur)
-            N.check(N.lib().vistaf_ftp_batch_begin(self.handle, def_gray_dev[lo:].data_ptr(), hi - lo, self.lane_ws[k].data_ptr(),
+                if def_gray_dev is None:
+                    N.wait_ready(s, ready, lo, hi)
+                    with t.cuda.stream(s):
+                        g = self.geom
+                        N.check(N.lib().vistaf_crop_gray(frames_dev[lo:].data_ptr(), hi - lo, self.H, self.W, g["x1"], g["y1"], self.h,
+                                                         self.w, gray[lo:].data_ptr(), C.c_void_p(s.cuda_stream)), "crop_gray")
+            N.check(N.lib().vistaf_ftp_batch_begin(self.handle, gray[lo:].data_ptr(), hi - lo, self.lane_ws[k].data_ptr(),
                                                    self.ws_bytes, C.c_void_p(s.cuda_stream)), "ftp_batch_begin")
-        self._begun = (def_gray_dev.data_ptr(), B, sl)
-        return True
+        self._begun = (gray.data_ptr(), B, sl)
+        return gray
 
     def run(self, def_gray_dev, masks: bool = True, out: Optional[dict] = None) -> dict:
         """def_gray_dev: uint8 CUDA [B,h,w] (aligned crops).  Returns dict of CUDA tensors.  After begin() on the same

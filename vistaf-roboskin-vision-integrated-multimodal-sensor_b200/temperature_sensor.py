@@ -161,7 +161,7 @@ class TempPlan:
         N.check(N.lib().vistaf_temp_workspace_plane(self.handle, self.lane_frames, name.encode(), C.byref(off), C.byref(nb)))
         return self.ws[off.value:off.value + nb.value]
 
-    def run(self, frames_dev, masks: bool = True, out: Optional[dict] = None) -> dict:
+    def run(self, frames_dev, masks: bool = True, out: Optional[dict] = None, ready=None) -> dict:
         """frames_dev: torch uint8 CUDA tensor [B,H,W,3] (BGR).  Returns dict of CUDA tensors."""
         t = self.torch
         assert frames_dev.is_cuda and frames_dev.dtype == t.uint8 and frames_dev.is_contiguous()
@@ -185,6 +185,7 @@ class TempPlan:
         cur = t.cuda.current_stream()
         L = min(self.lanes, max(1, int(self.active_lanes)))
         if L == 1 or B < 2 * L:
+            N.wait_ready(cur, ready, 0, B)
             call(0, B, self.ws, cur)
             return out
         per = -(-B // L)
@@ -195,6 +196,7 @@ class TempPlan:
                 break
             s = self.lane_streams[k]
             s.wait_stream(cur)
+            N.wait_ready(s, ready, lo, hi)
             call(lo, hi, self.lane_ws[k], s)
             used.append(s)
         for s in used:
