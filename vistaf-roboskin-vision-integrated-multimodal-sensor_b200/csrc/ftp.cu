@@ -1472,8 +1472,8 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   CKL();
   vistaf_stage_mark("F.chamfer_frontier_assemble", st);
   // ---- F: frontier taper, assembly, sigma-9 fill of the unreliable part, phase -> mm
-  if (chamfer_dt(NotMaskZero{rel, plane, w}, dist_in, dtmp, h, w, nb, st)) return 1;
-  if (chamfer_dt(MaskZero{rel, plane, w}, dist_out, dtmp, h, w, nb, st)) return 1;
+  if (chamfer_dt2(NotMaskZero{rel, plane, w}, dist_in, dtmp, MaskZero{rel, plane, w}, dist_out, (unsigned int*)sm, h, w, nb, st))
+    return 1;                                     // sm (written by the sigma-9 blur below) doubles as the second scratch plane
   if (gauss_blur(AsmLoad{hm, dist_in, rel, p->roi, sc, plane, w, P.frontier_band}, Den9Store{p->den9, sm, plane, w}, tmp, h, w,
                  nb, p->g_unrel, p->g_unrel, st))
     return 1;

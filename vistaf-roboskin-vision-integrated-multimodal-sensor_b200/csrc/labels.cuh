@@ -201,8 +201,25 @@ __device__ __forceinline__ int block_prefix_min(int v, int* sh) {   // inclusive
 
 // out: float distances [batch][h][w]
 template <class Zero>
+__device__ __forceinline__ void chamfer_body(Zero zero, float* __restrict__ out, unsigned int* __restrict__ tmp, int h, int w);
+
+template <class Zero>
 __global__ void __launch_bounds__(CH_THREADS) k_chamfer(Zero zero, float* __restrict__ out, unsigned int* __restrict__ tmp,
                                                          int h, int w) {
+  chamfer_body(zero, out, tmp, h, w);
+}
+// two independent transforms in one launch (grid.y selects): the row walk is a serial chain, so running both side by
+// side halves the latency of the pair
+template <class ZeroA, class ZeroB>
+__global__ void __launch_bounds__(CH_THREADS) k_chamfer2(ZeroA za, float* __restrict__ outa, unsigned int* __restrict__ tmpa,
+                                                          ZeroB zb, float* __restrict__ outb, unsigned int* __restrict__ tmpb,
+                                                          int h, int w) {
+  if (blockIdx.y == 0) chamfer_body(za, outa, tmpa, h, w);
+  else chamfer_body(zb, outb, tmpb, h, w);
+}
+
+template <class Zero>
+__device__ __forceinline__ void chamfer_body(Zero zero, float* __restrict__ out, unsigned int* __restrict__ tmp, int h, int w) {
   extern __shared__ unsigned int rows[];          // prev[w + 2], cur[w + 2]
   __shared__ int sh[32];
   const int b = blockIdx.x, W2 = w + 2;
@@ -287,6 +304,15 @@ __global__ void __launch_bounds__(CH_THREADS) k_chamfer(Zero zero, float* __rest
   }
 }
 
+template <class ZeroA, class ZeroB>
+static int chamfer_dt2(ZeroA za, float* outa, unsigned int* tmpa, ZeroB zb, float* outb, unsigned int* tmpb, int h, int w,
+                       int batch, cudaStream_t st) {
+  if (w > CH_THREADS * CH_MAXPT) return vistaf_set_err("chamfer_dt: row too long", cudaErrorInvalidValue, __FILE__, __LINE__);
+  VL(), k_chamfer2<ZeroA, ZeroB><<<dim3(batch, 2), CH_THREADS, sizeof(unsigned int) * 2 * (size_t)(w + 2), st>>>(
+      za, outa, tmpa, zb, outb, tmpb, h, w);
+  CKL();
+  return 0;
+}
 template <class Zero>
 static int chamfer_dt(Zero zero, float* out, unsigned int* tmp, int h, int w, int batch, cudaStream_t st) {
   if (w > CH_THREADS * CH_MAXPT) return vistaf_set_err("chamfer_dt: row too long", cudaErrorInvalidValue, __FILE__, __LINE__);

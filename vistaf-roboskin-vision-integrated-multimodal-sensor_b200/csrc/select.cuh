@@ -282,9 +282,13 @@ __global__ void __launch_bounds__(1024) k_sel_p2(Val val, Out out, SelectState* 
   h3[threadIdx.x] = 0;
   __syncthreads();
   if (mode == 1) {
-    for (unsigned int i = threadIdx.x; i < nl; i += 1024) {
-      const unsigned int key = list[i];
-      if ((key >> 10) == p22) atomicAdd(&h3[key & 1023u], 1u);
+    for (unsigned int i0 = threadIdx.x; i0 < nl; i0 += 8192) {      // eight key loads in flight per thread
+      unsigned int key[8];
+#pragma unroll
+      for (int j = 0; j < 8; j++) { const unsigned int i = i0 + j * 1024; key[j] = i < nl ? list[i] : 0u; }
+#pragma unroll
+      for (int j = 0; j < 8; j++)
+        if (i0 + j * 1024 < nl && (key[j] >> 10) == p22) atomicAdd(&h3[key[j] & 1023u], 1u);
     }
   } else {
     for (long long i0 = threadIdx.x; i0 < n; i0 += 4096) {          // four element fetches in flight per thread

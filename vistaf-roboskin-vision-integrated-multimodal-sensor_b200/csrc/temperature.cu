@@ -9,6 +9,7 @@
 #include "morph.cuh"
 #include <string.h>
 #include <new>
+#include <vector>
 
 #define TOPK 16
 #define COLS_PER_BLOCK 2      // 2 columns x 2 buffers x 2161 float2 = 69 KB: three blocks per SM overlap each other's barriers
@@ -534,7 +535,7 @@ struct PostRoiEff {
 
 // ------------------------------------------------------------------ T7-T11: features, models, fusion
 struct DevModel {
-  int nfeat, nterms, niso, pad;
+  int nfeat, nterms, niso, canon;       // canon = degree (2 / 3) when the terms are in canonical sklearn order, else 0
   float mean[4], scale[4];
   int prev[VISTAF_MAX_TERMS], feat[VISTAF_MAX_TERMS];   // XP[t] = XP[prev[t]] * z[feat[t]]  (sklearn build order)
   double coef[VISTAF_MAX_TERMS];
@@ -544,16 +545,53 @@ struct DevModel {
 
 // StandardScaler (float32) -> PolynomialFeatures (float32 products) -> dot (float64) -> float32
 // [-> isotonic clip + linear interpolation in float64 -> float32]   (temperature_sensor.py:236-240)
-__device__ float model_predict(const DevModel* __restrict__ M, const float* x) {
-  float z[4], XP[VISTAF_MAX_TERMS];
-  const int nf = M->nfeat, nt = M->nterms;
-  for (int i = 0; i < nf; i++) z[i] = __fdiv_rn(__fsub_rn(x[i], M->mean[i]), M->scale[i]);
-  XP[0] = 1.0f;
+// Canonical PolynomialFeatures(degree DEG, include_bias) order over NF features, fully unrolled: every coefficient
+// index is a compile-time constant and the term products stay in registers.  Same products and the same
+// accumulation order as the table-driven loop below (term (i<=j<=k) = (z_j * z_k) * z_i).
+template <int NF, int DEG>
+__device__ __forceinline__ double poly_dot(const DevModel* __restrict__ M, const float* z) {
   double acc = M->intercept + M->coef[0];
-  for (int t = 1; t < nt; t++) {
-    float v = M->prev[t] == 0 ? z[M->feat[t]] : __fmul_rn(XP[M->prev[t]], z[M->feat[t]]);
-    XP[t] = v;
-    acc = fma(M->coef[t], (double)v, acc);
+  int t = 1;
+#pragma unroll
+  for (int i = 0; i < NF; i++) acc = fma(M->coef[t++], (double)z[i], acc);
+  float p2[NF][NF];
+#pragma unroll
+  for (int i = 0; i < NF; i++)
+#pragma unroll
+    for (int j = i; j < NF; j++) {
+      p2[i][j] = __fmul_rn(z[j], z[i]);
+      acc = fma(M->coef[t++], (double)p2[i][j], acc);
+    }
+  if (DEG >= 3) {
+#pragma unroll
+    for (int i = 0; i < NF; i++)
+#pragma unroll
+      for (int j = i; j < NF; j++)
+#pragma unroll
+        for (int k = j; k < NF; k++) acc = fma(M->coef[t++], (double)__fmul_rn(p2[j][k], z[i]), acc);
+  }
+  return acc;
+}
+
+__device__ float model_predict(const DevModel* __restrict__ M, const float* x) {
+  float z[4];
+  const int nf = M->nfeat, nt = M->nterms;
+  for (int i = 0; i < 4; i++) z[i] = i < nf ? __fdiv_rn(__fsub_rn(x[i], M->mean[i]), M->scale[i]) : 0.f;
+  double acc;
+  const int canon = M->canon;
+  if (canon == 3 && nf == 4) acc = poly_dot<4, 3>(M, z);
+  else if (canon == 2 && nf == 3) acc = poly_dot<3, 2>(M, z);
+  else if (canon == 2 && nf == 4) acc = poly_dot<4, 2>(M, z);
+  else if (canon == 3 && nf == 3) acc = poly_dot<3, 3>(M, z);
+  else {
+    float XP[VISTAF_MAX_TERMS];
+    XP[0] = 1.0f;
+    acc = M->intercept + M->coef[0];
+    for (int t = 1; t < nt; t++) {
+      float v = M->prev[t] == 0 ? z[M->feat[t]] : __fmul_rn(XP[M->prev[t]], z[M->feat[t]]);
+      XP[t] = v;
+      acc = fma(M->coef[t], (double)v, acc);
+    }
   }
   float pred = (float)acc;
   if (M->niso > 0) {
@@ -822,6 +860,23 @@ static int build_dev_model(const VistafPolyModel& m, DevModel& d) {
     }
     if (prev < 0) return vistaf_set_err("polynomial terms not in PolynomialFeatures order", cudaErrorInvalidValue, __FILE__, __LINE__);
     d.prev[t] = prev; d.feat[t] = low;
+  }
+  // canonical order check (enables the unrolled evaluation): bias, degree 1, degree 2 (i <= j), degree 3 (i <= j <= k)
+  for (int deg = 2; deg <= 3 && !d.canon; deg++) {
+    const int nf = d.nfeat;
+    std::vector<int> cp(1, 0), cf(1, 0);
+    std::vector<int> idx2(16, -1);
+    for (int i = 0; i < nf; i++) { cp.push_back(0); cf.push_back(i); }
+    for (int i = 0; i < nf; i++)
+      for (int j = i; j < nf; j++) { idx2[i * 4 + j] = (int)cp.size(); cp.push_back(1 + j); cf.push_back(i); }
+    if (deg == 3)
+      for (int i = 0; i < nf; i++)
+        for (int j = i; j < nf; j++)
+          for (int k = j; k < nf; k++) { cp.push_back(idx2[j * 4 + k]); cf.push_back(i); }
+    if ((int)cp.size() != d.nterms) continue;
+    bool same = true;
+    for (int t = 1; t < d.nterms; t++) same = same && cp[t] == d.prev[t] && cf[t] == d.feat[t];
+    if (same) d.canon = deg;
   }
   d.intercept = m.intercept;
   for (int i = 0; i < d.niso; i++) { d.iso_x[i] = m.iso_x[i]; d.iso_y[i] = m.iso_y[i]; }
