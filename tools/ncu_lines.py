@@ -1,7 +1,7 @@
 """Stall samples / executed instructions per CUDA source line of one kernel: joins the SASS rows of
 `ncu -i REP --page source --csv` with the line table of `nvdisasm -g -c` on the cubin extracted from the
 library that produced the report (cuobjdump -xelf all lib/libvistaf.so).
-  python tools/ncu_lines.py REP.ncu-rep CUBIN MANGLED_KERNEL_SUBSTRING [top]"""
+  [NCU_FILTER='--kernel-name-base demangled -k regex:IllumStore'] python tools/ncu_lines.py REP.ncu-rep CUBIN MANGLED_KERNEL_SUBSTRING [top]"""
 import collections, csv, io, re, subprocess, sys
 rep, cubin, kern = sys.argv[1:4]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
@@ -21,7 +21,9 @@ for l in sass.split("\n"):
         continue
     if re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+.*?;", l):
         seq.append(cur)
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+import os
+extra = os.environ.get("NCU_FILTER", "").split()
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + extra, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hdr, data = rows[1], rows[2:]
 si, ie = hdr.index("# Samples"), hdr.index("Instructions Executed")

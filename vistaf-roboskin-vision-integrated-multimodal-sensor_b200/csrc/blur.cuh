@@ -56,6 +56,15 @@ __device__ __forceinline__ float gauss_constant(const float* w, int kpad, float 
   return acc;
 }
 
+// Stores may provide `void outside(int b, int y, int x, float v)` for pixels of blocks outside the window (a cheaper
+// path that need not look at per-pixel masks); otherwise the normal operator() is used there too.
+template <class S>
+__device__ __forceinline__ auto blur_outside(S& s, int b, int y, int x, float v, int) -> decltype(s.outside(b, y, x, v), void()) {
+  s.outside(b, y, x, v);
+}
+template <class S>
+__device__ __forceinline__ void blur_outside(S& s, int b, int y, int x, float v, long) { s(b, y, x, v); }
+
 // Row pass.  grid = (ceil(w/1280), h, batch), block = 160.  Load: float operator()(int b,int y,int x).
 template <class Load>
 __global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* __restrict__ tmp, int h, int w,
@@ -115,7 +124,7 @@ __global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int 
 #pragma unroll
       const float fv = blur_frame_const(win.fill, win.stride, b);
 #pragma unroll
-      for (int j = 0; j < 8; j++) { const int y = y0 + r0o + j; if (y < h) sto(b, y, x, fv); }
+      for (int j = 0; j < 8; j++) { const int y = y0 + r0o + j; if (y < h) blur_outside(sto, b, y, x, fv, 0); }
     }
     sto.finish(b);
     return;

@@ -185,8 +185,9 @@ struct GrabOut {                 // output functor of select_quantile_out: runs 
 // select + grab in one call (lists behind the `batch` states of `sel`)
 template <class Val>
 static int select_grab(Val val, FtpScal* sc, int which, SelectState* sel, long long n, int batch, float q, cudaStream_t st,
-                       const float* qv = nullptr, size_t qstride = 0) {
-  return select_quantile_out(val, GrabOut{sc, which}, sel, sel_lists(sel, batch), n, batch, q, st, qv, qstride);
+                       const float* qv = nullptr, size_t qstride = 0, bool heavy = false) {
+  return select_quantile_out2(val, val, GrabOut{sc, which}, sel, sel_lists(sel, batch), n, batch, q, st, qv, qstride, SEL_CAP,
+                              heavy);
 }
 
 // ------------------------------------------------------------------ F2: bad pixels (shape_ftp.py:625-649)
@@ -1219,8 +1220,8 @@ static int ftp_preprocess(VistafFtpPlan* p, const uint8_t* gray, int nb, char* w
   VL(), k_ftp_init<<<cdiv(nb, 128), 128, 0, st>>>(sc, nb);
   VL(), k_ftp_sobel<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(gray, img, grad, h, w);
   CKL();
-  if (select_grab(MaskedVal{img, p->valid, plane}, sc, G_HI, sel, npix, nb, P.bad_int_pct, st)) return 1;
-  if (select_grab(MaskedVal{grad, p->valid, plane}, sc, G_GRAD, sel, npix, nb, P.bad_grad_pct, st)) return 1;
+  if (select_grab(MaskedVal{img, p->valid, plane}, sc, G_HI, sel, npix, nb, P.bad_int_pct, st, nullptr, 0, true)) return 1;   // 8-bit levels
+  if (select_grab(MaskedVal{grad, p->valid, plane}, sc, G_GRAD, sel, npix, nb, P.bad_grad_pct, st, nullptr, 0, true)) return 1;
   BadLoad bl{img, grad, p->valid, sc, plane, w};
   if (P.bad_dilate > 1) {
     if (morph<true>(bl, PostId(), bad, h, w, nb, p->se_bad, st)) return 1;

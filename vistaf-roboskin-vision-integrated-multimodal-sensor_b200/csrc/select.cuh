@@ -259,7 +259,7 @@ struct SelNoOut { __device__ void operator()(int, float, unsigned int) const {} 
 // unsigned int count), called by thread 0.
 template <class Val, class Out>
 __global__ void __launch_bounds__(1024) k_sel_p2(Val val, Out out, SelectState* st, unsigned int* lists, long long n, float q0,
-                                                 const float* qv, size_t qstride, unsigned int cap) {
+                                                 const float* qv, size_t qstride, unsigned int cap, int defer) {
   __shared__ unsigned int h3[1024];
   __shared__ unsigned int sh[34];
   __shared__ unsigned int s_min;
@@ -279,6 +279,20 @@ __global__ void __launch_bounds__(1024) k_sel_p2(Val val, Out out, SelectState* 
   unsigned int sb, below2;
   sel_find_bin<1024, SEL_BINS>(s.hist, r0, sh, sb, below2);
   const unsigned int p22 = (b1 << 11) | sb;
+  if (mode == 2 && defer) {
+    // radix mode with a grid sweep to follow (S3 / P3): leave the 22-bit prefix, the rank inside the sub-bin and where
+    // rank k+1 comes from (0 same sub-bin, 2 first key of the next sub-bin of b1, 3 first key above bin b1)
+    const unsigned int insub = s.hist[sb], r = r0 - below2;
+    unsigned int src = 0, p2 = 0;
+    if (k + 1 < count && r + 1 >= insub) {
+      if (r0 + 1 < inbin) { src = 2; p2 = (b1 << 11) | sel_next_bin<1024, SEL_BINS>(s.hist, sb, sh); }
+      else src = 3;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < SEL_BINS; i += 1024) s.hist[i] = 0;
+    if (threadIdx.x == 0) { s.b1 = p22; s.below = r; s.inbin = insub; s.need_next = src; s.nlist = p2; s.mode = 4; }
+    return;
+  }
   h3[threadIdx.x] = 0;
   __syncthreads();
   if (mode == 1) {
@@ -341,6 +355,69 @@ __global__ void __launch_bounds__(1024) k_sel_p2(Val val, Out out, SelectState* 
   }
 }
 
+// ---- S3 (deferred radix mode only): grid sweep for the last 10 key bits under the 22-bit prefix (+ first key of the
+// next sub-bin when rank k+1 lives there).  Frames in any other mode cost one early exit per block.
+template <class Val>
+__global__ void __launch_bounds__(256) k_sel_s3(Val val, SelectState* st, long long n) {
+  __shared__ unsigned int h[1024];
+  const int b = blockIdx.y;
+  SelectState& s = st[b];
+  if (s.mode != 4) return;
+  const unsigned int p22 = s.b1, p2 = s.nlist;
+  const bool want2 = s.need_next == 2;
+  for (int i = threadIdx.x; i < 1024; i += 256) h[i] = 0;
+  __syncthreads();
+  n = sel_limit(val, b, n, 0);
+  unsigned int mn = 0xffffffffu;
+  for (long long i0 = (long long)blockIdx.x * 1024 + threadIdx.x; i0 < n; i0 += (long long)gridDim.x * 1024) {
+    float v[4];
+    bool ok[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) { const long long i = i0 + (long long)j * 256; ok[j] = i < n && val(b, i, v[j]); }
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+      if (ok[j]) {
+        const unsigned int key = f2key(v[j]);
+        if ((key >> 10) == p22) atomicAdd(&h[key & 1023u], 1u);
+        else if (want2 && (key >> 10) == p2) mn = min(mn, key);
+      }
+  }
+  if (want2) {
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    if ((threadIdx.x & 31) == 0 && mn != 0xffffffffu) atomicMin(&s.min_next, mn);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 1024; i += 256)
+    if (h[i]) atomicAdd(&s.hist[i], h[i]);
+}
+// ---- P3 (deferred radix mode only): finish from the 1024-bin histogram.
+template <class Out>
+__global__ void __launch_bounds__(1024) k_sel_p3(Out out, SelectState* st, float q0, const float* qv, size_t qstride) {
+  __shared__ unsigned int sh[34];
+  const int b = blockIdx.x;
+  SelectState& s = st[b];
+  if (s.mode != 4) return;
+  const float q = sel_q(q0, qv, qstride, b);
+  const unsigned int p22 = s.b1, r = s.below, insub = s.inbin, count = s.count, k = s.k;
+  unsigned int lo, below3;
+  sel_find_bin<1024, 1024>(s.hist, r, sh, lo, below3);
+  const unsigned int key0 = (p22 << 10) | lo;
+  unsigned int key1 = key0;
+  if (k + 1 < count) {
+    if (r + 1 - below3 < s.hist[lo]) key1 = key0;
+    else if (r + 1 < insub) key1 = (p22 << 10) | sel_next_bin<1024, 1024>(s.hist, lo, sh);
+    else key1 = s.min_next;
+  }
+  __syncthreads();
+  s.hist[threadIdx.x] = 0;
+  if (threadIdx.x == 0) {
+    s.vk = key2f(key0); s.vk1 = key2f(key1);
+    sel_interpolate(s, q);
+    out(b, s.result, count);
+    s.mode = 0; s.nlist = 0; s.min_next = 0xffffffffu; s.need_next = 0;
+  }
+}
+
 // Host: selection of quantile q (percent; q < 0 = median) for `batch` frames over n candidates each.
 // `lists`: batch * SEL_CAP keys.  The result lands in st[b].result / st[b].count and in `out`.
 // val1 feeds the first sweep, val2 the second sweep and the finishing block: they must describe the same value
@@ -348,7 +425,7 @@ __global__ void __launch_bounds__(1024) k_sel_p2(Val val, Out out, SelectState* 
 template <class Val1, class Val2, class Out>
 static int select_quantile_out2(Val1 val1, Val2 val2, Out out, SelectState* st, unsigned int* lists, long long n, int batch,
                                 float q, cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0,
-                                unsigned int cap = SEL_CAP) {
+                                unsigned int cap = SEL_CAP, bool heavy = false) {   // heavy: duplicated data expected
   int gx = (148 * 6 + batch - 1) / batch;
   const int gmax = (int)((n + 1023) / 1024);
   if (gx > gmax) gx = gmax;
@@ -357,7 +434,11 @@ static int select_quantile_out2(Val1 val1, Val2 val2, Out out, SelectState* st, 
   dim3 grid(gx, batch);
   VL(), k_sel_s1<Val1><<<grid, 256, 0, stream>>>(val1, st, n, q, qv, qstride, cap);
   VL(), k_sel_s2<Val2><<<grid, 256, 0, stream>>>(val2, st, lists, n, cap);
-  VL(), k_sel_p2<Val2, Out><<<batch, 1024, 0, stream>>>(val2, out, st, lists, n, q, qv, qstride, cap);
+  VL(), k_sel_p2<Val2, Out><<<batch, 1024, 0, stream>>>(val2, out, st, lists, n, q, qv, qstride, cap, heavy ? 1 : 0);
+  if (heavy) {      // frames whose bin overflowed the list finish with a grid sweep instead of a one-block sweep
+    VL(), k_sel_s3<Val2><<<grid, 256, 0, stream>>>(val2, st, n);
+    VL(), k_sel_p3<Out><<<batch, 1024, 0, stream>>>(out, st, q, qv, qstride);
+  }
   CKL();
   return 0;
 }
@@ -369,7 +450,8 @@ static int select_quantile_out(Val val, Out out, SelectState* st, unsigned int* 
 // call-site compatible form: the key lists live right behind the `batch` states (sel_ws_bytes)
 template <class Val>
 static int select_quantile(Val val, SelectState* st, long long n, int batch, float q, bool need_count,
-                           cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0, unsigned int cap = SEL_CAP) {
+                           cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0, unsigned int cap = SEL_CAP,
+                           bool heavy = false) {
   (void)need_count;
-  return select_quantile_out2(val, val, SelNoOut(), st, sel_lists(st, batch), n, batch, q, stream, qv, qstride, cap);
+  return select_quantile_out2(val, val, SelNoOut(), st, sel_lists(st, batch), n, batch, q, stream, qv, qstride, cap, heavy);
 }

@@ -182,6 +182,10 @@ struct IllumStore {
     norm[(long long)b * plane + i] = n;
     if (in && !sat_at(sc[b], sat + (long long)b * plane, i)) acc += (double)n;
   }
+  __device__ void outside(int b, int y, int x, float blur) {     // window blocks lie outside the ROI: g = median
+    if (blur < 1e-6f) blur = 1.0f;
+    norm[(long long)b * plane + (long long)y * w + x] = __fdiv_rn(sc[b].median, blur);
+  }
   __device__ void finish(int b) {
     __shared__ double sh[32];
     double v[1] = {acc};
@@ -752,6 +756,7 @@ struct FinalStore {
     }
     out[(long long)b * plane + i] = r;
   }
+  __device__ void outside(int b, int y, int x, float) { out[(long long)b * plane + (long long)y * w + x] = __int_as_float(0x7fc00000); }
   __device__ void finish(int b) {
     __shared__ double sh[3 * 32];
     __shared__ float shm[2 * 32];
@@ -1068,7 +1073,7 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   FinalVal fv{fin, p->roi, plane, (long long)p->y0 * W};
   const long long nsel = (long long)(p->y1 - p->y0) * W;
   if (sel_reset(sel, nb, st)) return 1;
-  if (select_quantile(fv, sel, nsel, nb, -1.0f, true, st, nullptr, 0, TEMP_SEL_CAP)) return 1;
+  if (select_quantile(fv, sel, nsel, nb, -1.0f, true, st, nullptr, 0, TEMP_SEL_CAP, true)) return 1;
   VL(), k_temp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, sel, O.records + f0, nb, W / 2, H / 2);
   CKL();
   vistaf_stage_mark("", st);
