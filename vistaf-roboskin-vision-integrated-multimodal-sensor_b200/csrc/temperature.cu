@@ -463,7 +463,7 @@ __global__ void __launch_bounds__(256) k_temp_ifft_rows(const float2* __restrict
                                                          const uint8_t* __restrict__ gray8,
                                                          const uint8_t* __restrict__ roi, const uint8_t* __restrict__ sat,
                                                          uint8_t* __restrict__ maskA, TempScal* sc, Fft1D p, int h,
-                                                         int ybeg, int R) {
+                                                         int ybeg, int R, float2* __restrict__ Z, int zx0, int zw, int zrows) {
   extern __shared__ float2 sm[];
   __shared__ double red[4 * 32];
   const int n = p.n, b = blockIdx.y, y = ybeg + blockIdx.x, nb = 2 * R + 1;
@@ -491,6 +491,12 @@ __global__ void __launch_bounds__(256) k_temp_ifft_rows(const float2* __restrict
     }
     block_sum<2>(v, red);
     if (threadIdx.x == 0) { atomicAdd(&S.csum[0], v[0]); atomicAdd(&S.csum[1], v[1]); }
+    // keep the analytic signal over the ROI bounding box: the sign split (k_temp_split) re-reads it instead of
+    // transforming every row a second time
+    if (Z) {
+      float2* zr = Z + ((size_t)b * zrows + blockIdx.x) * zw;
+      for (int x = threadIdx.x; x < zw; x += blockDim.x) zr[x] = z[zx0 + x];
+    }
   } else {
     const double phi0 = atan2(S.csum[1], S.csum[0]);
     const double cs = cos(phi0), sn = sin(phi0);
@@ -509,6 +515,39 @@ __global__ void __launch_bounds__(256) k_temp_ifft_rows(const float2* __restrict
       atomicAdd(&S.sumA, v[0]); atomicAdd(&S.cntA, (unsigned)v[1]);
       atomicAdd(&S.sumB, v[2]); atomicAdd(&S.cntB, (unsigned)v[3]);
     }
+  }
+}
+
+// A / B split by the sign of s = Re(z e^{-i phi0}) over roi_eff, and the mean gray of both classes
+// (temperature_sensor.py:475-489), from the analytic signal stored by k_temp_ifft_rows<1>.  maskA is written over
+// the ROI bounding box only (its readers test the ROI first).
+__global__ void __launch_bounds__(256) k_temp_split(const float2* __restrict__ Z, const uint8_t* __restrict__ gray8,
+                                                     const uint8_t* __restrict__ roi, const uint8_t* __restrict__ sat,
+                                                     uint8_t* __restrict__ maskA, TempScal* sc, int h, int w, int ybeg, int zx0,
+                                                     int zw, int zrows) {
+  __shared__ double red[4 * 32];
+  const int b = blockIdx.z, ry = blockIdx.y, y = ybeg + ry, xx = blockIdx.x * 256 + threadIdx.x;
+  TempScal& S = sc[b];
+  const bool has_sat = S.sat_raw_count != 0;
+  const double phi0 = atan2(S.csum[1], S.csum[0]);
+  const double cs = cos(phi0), sn = sin(phi0);
+  double v[4] = {0.0, 0.0, 0.0, 0.0};
+  if (xx < zw) {
+    const int x = zx0 + xx;
+    const size_t row = (size_t)y * w, fr = (size_t)b * h * w;
+    int mA = 0;
+    if (roi[row + x] && !(has_sat && sat[fr + row + x])) {
+      const float2 z = Z[((size_t)b * zrows + ry) * zw + xx];
+      const float s = (float)((double)z.x * cs + (double)z.y * sn);
+      const float g = (float)gray8[fr + row + x];
+      if (s >= 0.f) { mA = 1; v[0] += g; v[1] += 1.0; } else { v[2] += g; v[3] += 1.0; }
+    }
+    maskA[fr + row + x] = (uint8_t)mA;
+  }
+  block_sum<4>(v, red);
+  if (threadIdx.x == 0 && (v[1] != 0.0 || v[3] != 0.0)) {
+    atomicAdd(&S.sumA, v[0]); atomicAdd(&S.cntA, (unsigned)v[1]);
+    atomicAdd(&S.sumB, v[2]); atomicAdd(&S.cntB, (unsigned)v[3]);
   }
 }
 
@@ -1028,8 +1067,13 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   const int R = P.band_radius, nbnd = 2 * R + 1;
   VL(), k_temp_band<<<dim3(nbnd, nb), 256, (size_t)H * 8, st>>>(A, G, sc, p->fh, W, Wh, R);
   const int nrows = p->y1 - p->y0;
-  VL(), k_temp_ifft_rows<1><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R);
-  VL(), k_temp_ifft_rows<2><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R);
+  // the half spectrum A has been consumed by k_temp_band: its plane now holds the analytic signal over the ROI box
+  float2* Z = A;
+  const int zw = p->x1 - p->x0;
+  if ((size_t)zw * nrows > (size_t)H * Wh) return vistaf_set_err("temperature: ROI box larger than the spectrum plane", cudaErrorInvalidValue, __FILE__, __LINE__);
+  VL(), k_temp_ifft_rows<1><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R,
+                                                                      Z, p->x0, zw, nrows);
+  VL(), k_temp_split<<<dim3(cdiv(zw, 256), nrows, nb), 256, 0, st>>>(Z, gray8, p->roi, sat, maskA, sc, H, W, p->y0, p->x0, zw, nrows);
   VL(), k_temp_choose_dark<<<nb, 1, 0, st>>>(sc);
   CKL();
   vistaf_stage_mark("T.morph_close_open", st);
