@@ -22,6 +22,7 @@
 #include "morph.cuh"
 #include "labels.cuh"
 #include "telea.cuh"
+#include <cuda_pipeline.h>
 #include <string.h>
 #include <new>
 #include <vector>
@@ -655,11 +656,19 @@ __device__ void irls_solve_dev(FtpScal& s, int iter) {
   for (int i = 0; i < 6; i++) s.coef[i] = i < NC ? (float)x[i] : 0.f;
 }
 
+// Each block streams a contiguous range of the frame's compacted samples (value, packed pixel, previous residual)
+// through a three-stage ring of 1024-sample tiles in shared memory filled by 16-byte asynchronous copies
+// (cp.async), so ~36 KB per block are in flight whatever the register budget of the 28 float64 accumulators.
+#define ACC_TILE 1024
+#define ACC_STAGES 3
 template <bool ORDER2>
 __global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ zc, const unsigned int* __restrict__ pc,
                                                      const float* __restrict__ rc, FtpScal* sc, FitGeom g, int npix, int iter) {
   constexpr int NC = ORDER2 ? 6 : 3, NV = NC * (NC + 1) / 2 + NC + 1;
   __shared__ double sh[NV * 32];
+  __shared__ __align__(16) float s_z[ACC_STAGES][ACC_TILE];
+  __shared__ __align__(16) unsigned int s_p[ACC_STAGES][ACC_TILE];
+  __shared__ __align__(16) float s_r[ACC_STAGES][ACC_TILE];
   const int b = blockIdx.y;
   if (sc[b].irls_skip) return;
   const float cs = __fmul_rn(IRLS_C, sc[b].sigma);
@@ -668,44 +677,69 @@ __global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ zc
   double acc[NV];
 #pragma unroll
   for (int i = 0; i < NV; i++) acc[i] = 0.0;
-  // four samples per thread and trip, all eight loads issued before any is used
-  for (int j0 = blockIdx.x * 1024 + threadIdx.x; j0 < n; j0 += gridDim.x * 1024) {
-    float z4[4], r4[4];
-    unsigned int p4[4];
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      const int jj = j0 + j * 256;
-      z4[j] = jj < n ? zc[o + jj] : 0.f;
-      p4[j] = jj < n ? pc[o + jj] : 0u;
-      r4[j] = (jj < n && iter > 0) ? rc[o + jj] : 0.f;       // residuals of the previous solve (RFirst)
+  const int ntiles = (n + ACC_TILE - 1) / ACC_TILE;
+  const int per = (ntiles + gridDim.x - 1) / gridDim.x;
+  const int t0 = blockIdx.x * per, t1 = min(ntiles, t0 + per);
+  const bool use_r = iter > 0;
+  // tile t of the frame -> ring slot; every thread copies 4 consecutive samples of each array (the arrays are
+  // 16-byte aligned per frame and padded to the plane size, so a tile may over-read past n inside the plane)
+  auto issue = [&](int t) {
+    if (t < t1 && (size_t)t * ACC_TILE + threadIdx.x * 4 + 4 <= (size_t)npix) {
+      const int slot = (t - t0) % ACC_STAGES;
+      const size_t e = o + (size_t)t * ACC_TILE + threadIdx.x * 4;
+      __pipeline_memcpy_async(&s_z[slot][threadIdx.x * 4], zc + e, 16);
+      __pipeline_memcpy_async(&s_p[slot][threadIdx.x * 4], pc + e, 16);
+      if (use_r) __pipeline_memcpy_async(&s_r[slot][threadIdx.x * 4], rc + e, 16);
     }
+    __pipeline_commit();
+  };
+  issue(t0);
+  issue(t0 + 1);
+  for (int t = t0; t < t1; t++) {
+    issue(t + 2);
+    __pipeline_wait_prior(2);
+    __syncthreads();
+    const int slot = (t - t0) % ACC_STAGES;
+    const int jbase = t * ACC_TILE;
+    float part[NV];
+#pragma unroll
+    for (int i = 0; i < NV; i++) part[i] = 0.f;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
-      if (j0 + j * 256 >= n) continue;
-      const float zz = z4[j];
+      const int e = threadIdx.x + j * 256;
+      if (jbase + e >= n) continue;
+      const float zz = s_z[slot][e];
       float xn, yn;
-      g.norm_packed(p4[j], xn, yn);
+      g.norm_packed(s_p[slot][e], xn, yn);
       float wt = 1.0f;
-      if (iter > 0) {
-        const float u = __fdiv_rn(r4[j], cs);
+      if (use_r) {
+        const float u = __fdiv_rn(s_r[slot][e], cs);
         wt = __fdiv_rn(1.0f, __fadd_rn(1.0f, __fmul_rn(u, u)));
       }
-      const double w2 = (double)wt * (double)wt;
-      double a[NC];
-      a[0] = xn; a[1] = yn; a[2] = 1.0;
-      if (ORDER2) { a[3] = (double)__fmul_rn(xn, xn); a[4] = (double)__fmul_rn(xn, yn); a[5] = (double)__fmul_rn(yn, yn); }
+      // the four samples' products are summed in float32 (each rounded once more than in float64, unbiased, ~6e-8
+      // relative: averaged over 10^5..10^6 samples that is orders below the float32 design matrix's own rounding) and
+      // flushed into the float64 accumulators once per tile
+      const float w2 = wt * wt;
+      float a[NC];
+      a[0] = xn; a[1] = yn; a[2] = 1.0f;
+      if (ORDER2) { a[3] = __fmul_rn(xn, xn); a[4] = __fmul_rn(xn, yn); a[5] = __fmul_rn(yn, yn); }
       int k = 0;
 #pragma unroll
       for (int p = 0; p < NC; p++) {
-        const double wa = w2 * a[p];
+        const float wa = w2 * a[p];
 #pragma unroll
-        for (int q = p; q < NC; q++) acc[k++] += wa * a[q];
+        for (int q = p; q < NC; q++) part[k] = fmaf(wa, a[q], part[k]), k++;
       }
+      const float wz = w2 * zz;
 #pragma unroll
-      for (int p = 0; p < NC; p++) acc[k++] += w2 * a[p] * (double)zz;
-      acc[k] += 1.0;
+      for (int p = 0; p < NC; p++) part[k] = fmaf(wz, a[p], part[k]), k++;
+      part[k] += 1.0f;
     }
+#pragma unroll
+    for (int i = 0; i < NV; i++) acc[i] += (double)part[i];
+    __syncthreads();                                   // slot is refilled by the next issue()
   }
+  __pipeline_wait_prior(0);
   block_sum<NV>(acc, sh);
   if (threadIdx.x == 0) {
     for (int i = 0; i < NV; i++)
