@@ -1394,7 +1394,7 @@ static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, S
     unsigned int* listg = lists + (size_t)g0 * SEL_CAP;
     FitMask fmg = fm;
     fmg.rel += (size_t)g0 * fm.plane; fmg.contact_d += (size_t)g0 * fm.plane; fmg.sc = scg;
-    int gx = (148 * 4 + ng - 1) / ng;
+    int gx = (148 * 16 + ng - 1) / ng;           // ~8 waves of blocks: the last partial wave costs little
     if (gx > 128) gx = 128;
     VL(), k_irls_compact<<<dim3(gx, ng), 256, 0, st>>>(zg, fmg, scg, g, zcg, pcg, npix);
     for (int it = 0; it < 6; it++) {

@@ -426,7 +426,7 @@ template <class Val1, class Val2, class Out>
 static int select_quantile_out2(Val1 val1, Val2 val2, Out out, SelectState* st, unsigned int* lists, long long n, int batch,
                                 float q, cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0,
                                 unsigned int cap = SEL_CAP, bool heavy = false) {   // heavy: duplicated data expected
-  int gx = (148 * 6 + batch - 1) / batch;
+  int gx = (148 * 12 + batch - 1) / batch;      // several waves of blocks per sweep: a short last wave
   const int gmax = (int)((n + 1023) / 1024);
   if (gx > gmax) gx = gmax;
   if (gx > 592) gx = 592;
