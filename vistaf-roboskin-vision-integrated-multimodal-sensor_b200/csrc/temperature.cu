@@ -14,6 +14,7 @@
 #define TOPK 16
 #define COLS_PER_BLOCK 2      // 2 columns x 2 buffers x 2161 float2 = 69 KB: three blocks per SM overlap each other's barriers
 #define COLS_THREADS 256
+#define COLS_PT 18             // bins per thread held in registers for the top-16 search: COLS_PER_BLOCK * H <= 18 * 256
 #define MAXBAND 45            // 2*22+1
 #define TEMP_SEL_CAP (1u << 20) // key-list capacity per frame for the median of the final map: temperatures of a frame
                                 // crowd into one or two top-11-bit float bins (values in [20, 75])
@@ -293,34 +294,66 @@ __global__ void __launch_bounds__(512) k_temp_fft_cols_peaks(const float2* __res
     mag[t] = (ex1 && ex2) ? -1.f : m;
   }
   __syncthreads();
-  __shared__ float smax[16];
-  __shared__ int sidx[16];
+  // Top-16 of the block's bins without block-wide rounds: every lane keeps its bins in registers, each warp extracts
+  // its own 16 largest with shuffles only (ties -> smaller index, as a full-block argmax would), and warp 0 merges
+  // the 8 x 16 survivors.
+  __shared__ float wm[COLS_THREADS / 32][TOPK];
+  __shared__ int wi[COLS_THREADS / 32][TOPK];
   Cand* out = cand + ((size_t)b * gridDim.x + blockIdx.x) * TOPK;
+  const int tot = nc * n, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float mv[COLS_PT];
+#pragma unroll
+  for (int j = 0; j < COLS_PT; j++) { const int t = threadIdx.x + j * COLS_THREADS; mv[j] = t < tot ? mag[t] : -3.f; }
   for (int round = 0; round < TOPK; round++) {
-    float best = -2.f;
-    int bi = -1;
-    for (int t = threadIdx.x; t < nc * n; t += blockDim.x) {
-      float m = mag[t];
-      if (m > best) { best = m; bi = t; }
-    }
+    float best = -4.f;
+    int bt = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < COLS_PT; j++)
+      if (mv[j] > best) { best = mv[j]; bt = threadIdx.x + j * COLS_THREADS; }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-      float ob = __shfl_xor_sync(0xffffffffu, best, o);
-      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (ob > best || (ob == best && oi >= 0 && (bi < 0 || oi < bi))) { best = ob; bi = oi; }
+      const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int ot = __shfl_xor_sync(0xffffffffu, bt, o);
+      if (ob > best || (ob == best && ot < bt)) { best = ob; bt = ot; }
     }
-    if ((threadIdx.x & 31) == 0) { smax[threadIdx.x >> 5] = best; sidx[threadIdx.x >> 5] = bi; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      for (int i = 1; i < (int)(blockDim.x >> 5); i++)
-        if (smax[i] > best || (smax[i] == best && sidx[i] >= 0 && (bi < 0 || sidx[i] < bi))) { best = smax[i]; bi = sidx[i]; }
-      Cand cd;
-      cd.mag = best; cd.pad = 0;
-      if (bi >= 0 && best >= 0.f) { int c = bi / n; cd.kx = c0 + c; cd.ky = bi - c * n; mag[bi] = -1.f; }
-      else { cd.kx = -1; cd.ky = -1; cd.mag = -1.f; }
-      out[round] = cd;
+#pragma unroll
+    for (int j = 0; j < COLS_PT; j++)
+      if (threadIdx.x + j * COLS_THREADS == bt) mv[j] = -4.f;       // the winner leaves its lane's set
+    if (lane == 0) { wm[wid][round] = best; wi[wid][round] = bt; }
+  }
+  __syncthreads();
+  if (wid == 0) {
+    constexpr int NE = (COLS_THREADS / 32) * TOPK / 32;             // survivors per lane
+    float em[NE];
+    int ei[NE];
+#pragma unroll
+    for (int q = 0; q < NE; q++) {
+      const int e = lane + 32 * q;
+      em[q] = wm[e / TOPK][e % TOPK]; ei[q] = wi[e / TOPK][e % TOPK];
     }
-    __syncthreads();
+    for (int round = 0; round < TOPK; round++) {
+      float best = -4.f;
+      int bt = 0x7fffffff;
+#pragma unroll
+      for (int q = 0; q < NE; q++)
+        if (em[q] > best || (em[q] == best && ei[q] < bt)) { best = em[q]; bt = ei[q]; }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int ot = __shfl_xor_sync(0xffffffffu, bt, o);
+        if (ob > best || (ob == best && ot < bt)) { best = ob; bt = ot; }
+      }
+#pragma unroll
+      for (int q = 0; q < NE; q++)
+        if (ei[q] == bt && em[q] == best) em[q] = -4.f;
+      if (lane == 0) {
+        Cand cd;
+        cd.mag = best; cd.pad = 0;
+        if (best >= 0.f) { const int c = bt / n; cd.kx = c0 + c; cd.ky = bt - c * n; }
+        else { cd.kx = -1; cd.ky = -1; cd.mag = -1.f; }
+        out[round] = cd;
+      }
+    }
   }
 }
 
@@ -529,8 +562,13 @@ __global__ void __launch_bounds__(256) k_temp_split(const float2* __restrict__ Z
   const int b = blockIdx.z, ry = blockIdx.y, y = ybeg + ry, xx = blockIdx.x * 256 + threadIdx.x;
   TempScal& S = sc[b];
   const bool has_sat = S.sat_raw_count != 0;
-  const double phi0 = atan2(S.csum[1], S.csum[0]);
-  const double cs = cos(phi0), sn = sin(phi0);
+  __shared__ double s_cs[2];
+  if (threadIdx.x == 0) {                     // one float64 atan2 / sincos per block, not per pixel
+    const double phi0 = atan2(S.csum[1], S.csum[0]);
+    s_cs[0] = cos(phi0); s_cs[1] = sin(phi0);
+  }
+  __syncthreads();
+  const double cs = s_cs[0], sn = s_cs[1];
   double v[4] = {0.0, 0.0, 0.0, 0.0};
   if (xx < zw) {
     const int x = zx0 + xx;
@@ -938,7 +976,8 @@ extern "C" int vistaf_temp_plan_create(const VistafTempParams* P, VistafTempPlan
   p->H = P->height; p->W = P->width; p->Wh = P->width / 2 + 1;
   p->nblk_cols = cdiv(p->Wh, COLS_PER_BLOCK);
   if (fft1d_create(&p->fw, p->W) || fft1d_create(&p->fh, p->H)) return 1;
-  if ((size_t)p->W * 16 > 200 * 1024 || (size_t)COLS_PER_BLOCK * (p->H + 1) * 16 > 220 * 1024)
+  if ((size_t)p->W * 16 > 200 * 1024 || (size_t)COLS_PER_BLOCK * (p->H + 1) * 16 > 220 * 1024 ||
+      COLS_PER_BLOCK * p->H > COLS_PT * COLS_THREADS)
     return vistaf_set_err("frame too large for the shared-memory FFT", cudaErrorInvalidValue, __FILE__, __LINE__);
   p->g_illum = make_gauss(P->illum_sigma);
   p->g_across = make_gauss(P->sigma_across);
