@@ -701,9 +701,6 @@ __global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ zc
     __syncthreads();
     const int slot = (t - t0) % ACC_STAGES;
     const int jbase = t * ACC_TILE;
-    float part[NV];
-#pragma unroll
-    for (int i = 0; i < NV; i++) part[i] = 0.f;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       const int e = threadIdx.x + j * 256;
@@ -716,27 +713,23 @@ __global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ zc
         const float u = __fdiv_rn(s_r[slot][e], cs);
         wt = __fdiv_rn(1.0f, __fadd_rn(1.0f, __fmul_rn(u, u)));
       }
-      // the four samples' products are summed in float32 (each rounded once more than in float64, unbiased, ~6e-8
-      // relative: averaged over 10^5..10^6 samples that is orders below the float32 design matrix's own rounding) and
-      // flushed into the float64 accumulators once per tile
-      const float w2 = wt * wt;
-      float a[NC];
-      a[0] = xn; a[1] = yn; a[2] = 1.0f;
-      if (ORDER2) { a[3] = __fmul_rn(xn, xn); a[4] = __fmul_rn(xn, yn); a[5] = __fmul_rn(yn, yn); }
+      // products and sums in float64: the sums then agree to ~1e-16 whatever the grid / batch layout, so the float32
+      // coefficients (and every mask derived from them) do not depend on how a batch is chunked
+      const double w2 = (double)wt * (double)wt;
+      double a[NC];
+      a[0] = xn; a[1] = yn; a[2] = 1.0;
+      if (ORDER2) { a[3] = (double)__fmul_rn(xn, xn); a[4] = (double)__fmul_rn(xn, yn); a[5] = (double)__fmul_rn(yn, yn); }
       int k = 0;
 #pragma unroll
       for (int p = 0; p < NC; p++) {
-        const float wa = w2 * a[p];
+        const double wa = w2 * a[p];
 #pragma unroll
-        for (int q = p; q < NC; q++) part[k] = fmaf(wa, a[q], part[k]), k++;
+        for (int q = p; q < NC; q++) acc[k++] += wa * a[q];
       }
-      const float wz = w2 * zz;
 #pragma unroll
-      for (int p = 0; p < NC; p++) part[k] = fmaf(wz, a[p], part[k]), k++;
-      part[k] += 1.0f;
+      for (int p = 0; p < NC; p++) acc[k++] += w2 * a[p] * (double)zz;
+      acc[k] += 1.0;
     }
-#pragma unroll
-    for (int i = 0; i < NV; i++) acc[i] += (double)part[i];
     __syncthreads();                                   // slot is refilled by the next issue()
   }
   __pipeline_wait_prior(0);
