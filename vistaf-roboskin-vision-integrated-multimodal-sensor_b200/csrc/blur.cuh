@@ -84,6 +84,8 @@ __global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* 
   for (int e = threadIdx.x; e < g.kpad; e += BLUR_ROW_THREADS) wk[e] = g.w[e];
   __syncthreads();
   const int t = threadIdx.x;
+  // outputs no active column block reads (column blocks are 32 wide, aligned to their own grid) are not computed
+  if (x0 + t * 8 + 8 <= win.x0 - 32 || x0 + t * 8 >= win.x1 + 32) return;
   float acc[8], wreg[16];
 #pragma unroll
   for (int j = 0; j < 8; j++) { acc[j] = 0.f; wreg[j] = s[j * BLUR_ROW_PITCH + t]; }

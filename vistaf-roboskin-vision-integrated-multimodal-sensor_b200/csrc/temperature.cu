@@ -40,6 +40,7 @@ struct TempScal {             // per-frame scalars living in the workspace
   double t_sum, t_sumsq;
   float t_min, t_max;
   unsigned int t_count, pad;
+  double rot_c, rot_s;          // cos / sin of phi0 (temperature_sensor.py:470-474), set by k_temp_phi0
   float blur_rc, blur_cc;       // sigma-20 blur of the constant background: row pass R(median), column pass C(R(median))
   float pad2[2];
 };
@@ -279,19 +280,27 @@ __global__ void __launch_bounds__(512) k_temp_fft_cols_peaks(const float2* __res
   float2* F = fft_smem<-1>(a, bb, p, nc, lds);
   float* mag = (float*)(F == a ? bb : a);          // scratch buffer is free now
   __syncthreads();
+  // the DC exclusion box only reaches columns |kx| <= dc: every other block skips the (modulo-heavy) box test
+  const bool near_dc = c0 <= dc + 1 || c0 + COLS_PER_BLOCK >= w / 2;
   for (int t = threadIdx.x; t < nc * n; t += blockDim.x) {
-    int c = t / n, ky = t - c * n, kx = c0 + c;
+    int c = 0, ky = t;
+#pragma unroll
+    for (int q = 1; q < COLS_PER_BLOCK; q++) if (ky >= n) { ky -= n; c++; }
+    const int kx = c0 + c;
     float2 v = F[c * lds + ky];
     float m = sqrtf(v.x * v.x + v.y * v.y);
-    // entry 1: (kx, ky); entry 2 (twin, same magnitude): (-kx, -ky).  Drop the bin if both are excluded.
-    int x1 = (kx + w / 2) % w, y1 = (ky + n / 2) % n;
-    bool ex1 = dc_excluded(x1, y1, n, w, dc);
-    bool ex2 = true;
-    if (kx != 0 && kx != w / 2) {
-      int x2 = (w - kx + w / 2) % w, y2 = ((n - ky) % n + n / 2) % n;
-      ex2 = dc_excluded(x2, y2, n, w, dc);
+    if (near_dc) {
+      // entry 1: (kx, ky); entry 2 (twin, same magnitude): (-kx, -ky).  Drop the bin if both are excluded.
+      int x1 = (kx + w / 2) % w, y1 = (ky + n / 2) % n;
+      bool ex1 = dc_excluded(x1, y1, n, w, dc);
+      bool ex2 = true;
+      if (kx != 0 && kx != w / 2) {
+        int x2 = (w - kx + w / 2) % w, y2 = ((n - ky) % n + n / 2) % n;
+        ex2 = dc_excluded(x2, y2, n, w, dc);
+      }
+      if (ex1 && ex2) m = -1.f;
     }
-    mag[t] = (ex1 && ex2) ? -1.f : m;
+    mag[t] = m;
   }
   __syncthreads();
   // Top-16 of the block's bins without block-wide rounds: every lane keeps its bins in registers, each warp extracts
@@ -562,13 +571,7 @@ __global__ void __launch_bounds__(256) k_temp_split(const float2* __restrict__ Z
   const int b = blockIdx.z, ry = blockIdx.y, y = ybeg + ry, xx = blockIdx.x * 256 + threadIdx.x;
   TempScal& S = sc[b];
   const bool has_sat = S.sat_raw_count != 0;
-  __shared__ double s_cs[2];
-  if (threadIdx.x == 0) {                     // one float64 atan2 / sincos per block, not per pixel
-    const double phi0 = atan2(S.csum[1], S.csum[0]);
-    s_cs[0] = cos(phi0); s_cs[1] = sin(phi0);
-  }
-  __syncthreads();
-  const double cs = s_cs[0], sn = s_cs[1];
+  const double cs = S.rot_c, sn = S.rot_s;
   double v[4] = {0.0, 0.0, 0.0, 0.0};
   if (xx < zw) {
     const int x = zx0 + xx;
@@ -589,6 +592,11 @@ __global__ void __launch_bounds__(256) k_temp_split(const float2* __restrict__ Z
   }
 }
 
+__global__ void k_temp_phi0(TempScal* sc) {       // one float64 atan2 / sincos per frame
+  TempScal& s = sc[blockIdx.x];
+  const double phi0 = atan2(s.csum[1], s.csum[0]);
+  s.rot_c = cos(phi0); s.rot_s = sin(phi0);
+}
 __global__ void k_temp_choose_dark(TempScal* sc) {
   TempScal& s = sc[blockIdx.x];
   double ma = s.cntA ? s.sumA / s.cntA : 1e9, mb = s.cntB ? s.sumB / s.cntB : 1e9;
@@ -1112,6 +1120,7 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   if ((size_t)zw * nrows > (size_t)H * Wh) return vistaf_set_err("temperature: ROI box larger than the spectrum plane", cudaErrorInvalidValue, __FILE__, __LINE__);
   VL(), k_temp_ifft_rows<1><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R,
                                                                       Z, p->x0, zw, nrows);
+  VL(), k_temp_phi0<<<nb, 1, 0, st>>>(sc);
   VL(), k_temp_split<<<dim3(cdiv(zw, 256), nrows, nb), 256, 0, st>>>(Z, gray8, p->roi, sat, maskA, sc, H, W, p->y0, p->x0, zw, nrows);
   VL(), k_temp_choose_dark<<<nb, 1, 0, st>>>(sc);
   CKL();
