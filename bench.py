@@ -235,7 +235,7 @@ def main():
     dev2, ref2 = torch.empty_like(dev), torch.empty_like(ref_dev)
 
     copy_stream = torch.cuda.Stream()
-    n_slices = max(1, a.lanes_ftp, a.lanes_temp)
+    n_slices = 2 * max(1, a.lanes_ftp, a.lanes_temp)
 
     def step_e2e():
         """Host -> device staging of the reference and of the frames in slices on a copy stream (events mark each slice
@@ -248,7 +248,12 @@ def main():
             ev_ref = torch.cuda.Event()
             ev_ref.record(copy_stream)
             per = -(-F // n_slices)
-            for lo in range(0, F, per):
+            per = -(-per // N_DISTINCT) * N_DISTINCT
+            starts = list(range(0, F, per))
+            # staging order: the first slices of every lane first (the temperature lanes start at frame 0 and F/2)
+            half = len(starts) // 2
+            order = starts[:2] + starts[half:half + 1] + starts[2:half] + starts[half + 1:] if len(starts) >= 4 else starts
+            for lo in order:
                 hi = min(F, lo + per)
                 for c in range(lo, hi, N_DISTINCT):              # F x 24.9 MB cross PCIe every step
                     n = min(N_DISTINCT, hi - c)

@@ -196,8 +196,11 @@ class TempPlan:
                 break
             s = self.lane_streams[k]
             s.wait_stream(cur)
-            N.wait_ready(s, ready, lo, hi)
-            call(lo, hi, self.lane_ws[k], s)
+            # one library call per workspace-sized piece, each waiting only for the staged slices it covers
+            for a in range(lo, hi, self.lane_frames):
+                b = min(hi, a + self.lane_frames)
+                N.wait_ready(s, ready, a, b)
+                call(a, b, self.lane_ws[k], s)
             used.append(s)
         for s in used:
             cur.wait_stream(s)
