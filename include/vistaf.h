@@ -28,13 +28,14 @@ extern "C" {
 /* per-frame status bits */
 #define VISTAF_ST_EMPTY_ROI        0x001  /* temperature_sensor.py:443  / shape_ftp.py:1677 */
 #define VISTAF_ST_NO_PEAK          0x002  /* temperature_sensor.py:457 */
-#define VISTAF_ST_SATURATED        0x004  /* saturated pixels present: Telea fill of the maps not applied (T10) */
+#define VISTAF_ST_SATURATED        0x004  /* saturated pixels present: wide map quantised + Telea-filled (T10, temperature_sensor.py:546) */
 #define VISTAF_ST_ROTATED_CARRIER  0x008  /* carrier angle != 0: oriented blur ran axis-aligned (T12) */
 #define VISTAF_ST_RESIDUES         0x010  /* phase residues inside the reliable mask: unwrap is path dependent (F10) */
 #define VISTAF_ST_FEW_RELIABLE     0x020  /* < 200 reliable pixels: polynomial detrend skipped (shape_ftp.py:1103) */
 #define VISTAF_ST_SIGN_FLIPPED     0x040  /* auto sign flip taken (shape_ftp.py:1759) */
 #define VISTAF_ST_CONTACT_P95      0x080  /* contact threshold fell back to p95 / p98 (shape_ftp.py:1733-1738) */
 #define VISTAF_ST_BG_FALLBACK      0x100  /* background < 15 % of reliable: detrend on reliable (shape_ftp.py:1744) */
+#define VISTAF_ST_SAT_UNFILLED     0x200  /* more than an eighth of one chunk's frames saturated: T10 skipped for this frame; re-run it in a smaller batch */
 
 /* StandardScaler -> PolynomialFeatures -> linear model [-> isotonic], temperature_sensor.py:236 */
 typedef struct {

@@ -20,7 +20,7 @@ def env():
     import synthetic as S
     import multimodal_sensor as MS
     ref = S.make_frame(0, reference=True)
-    frames = np.stack([S.make_frame(s) for s in (3, 16, 5, 7, 11, 2)])      # seed 16: saturated blobs
+    frames = np.stack([S.make_frame(s) for s in (3, 15, 5, 7, 11, 2)])      # seed 15: saturated blobs (T10)
     return torch, S, MS, ref, frames
 
 

@@ -95,9 +95,41 @@ def test_saturated_frame_masks(mods):
     assert int(o["sat"].sum()) > 0
     assert int(rec["status"]) & N.ST_SATURATED
     assert int(rec["sat_pixels"]) == int(o["sat"].sum())
-    for k in ("sat", "dark", "light", "color_support"):
+    for k in ("sat", "dark", "light", "color_support", "color_ok"):
         g = out[k][0].cpu().numpy().astype(bool)
         assert int((g != o[k]).sum()) == 0, k
+    # T10 (temperature_sensor.py:546-577): the wide map of a saturated frame is quantised to 8 bits, its holes are filled
+    # by Telea (r = 7, 8-bit stores) and every inside value is replaced by the de-quantised byte, then fused.
+    assert int((out["source"][0].cpu().numpy() != o["source"]).sum()) == 0
+    for k in ("fused", "final"):
+        g = out[k][0].cpu().numpy()
+        assert np.array_equal(np.isnan(g), np.isnan(o[k])), k
+        assert np.isfinite(g[o["sat"]]).all(), k                      # the glare blobs carry filled temperatures
+        assert float(np.nanmax(np.abs(g - o[k]))) <= 1e-2, k          # degC
+    for k in ("mean_C", "median_C", "std_C", "min_C", "max_C"):
+        assert abs(float(rec[k]) - o["stats"][k]) <= 1e-2, k
+
+
+def test_saturated_frames_beyond_the_slots(mods):
+    """T10 runs on (chunk + 7) // 8 compacted frames per chunk: a chunk where more frames are saturated flags the rest
+    with ST_SAT_UNFILLED at the C ABI; the synchronous wrapper redoes those frames alone and clears the flag."""
+    import torch
+    S, TS, TO = mods
+    import _native as N
+    fr = np.stack([S.make_frame(15), S.make_frame(31), S.make_frame(3)])
+    dev = torch.from_numpy(fr).cuda()
+    raw = TS.get_plan(2160, 3840, 3).run(dev, masks=False)
+    st = [int(r["status"]) for r in TS.records_to_numpy(raw["records"])]
+    assert st[0] & N.ST_SATURATED and not st[0] & N.ST_SAT_UNFILLED
+    assert st[1] & N.ST_SATURATED and st[1] & N.ST_SAT_UNFILLED
+    assert not st[2] & (N.ST_SATURATED | N.ST_SAT_UNFILLED)
+    out = TS.run_batch(fr, chunk=3)
+    alone = TS.run_batch(fr[1:2], chunk=1)
+    assert not int(out["records_np"][1]["status"]) & N.ST_SAT_UNFILLED
+    for k in ("fused", "final"):
+        a, b = out[k][1], alone[k][0]
+        assert bool(((a == b) | (a.isnan() & b.isnan())).all()), k
+    assert out["records_np"][1].tobytes() == alone["records_np"][0].tobytes()
 
 
 def test_repeatable_and_batch_independent(mods):

@@ -61,9 +61,9 @@ struct EdgeZero { __device__ int operator()(int, int, int) const { return 0; } }
 
 // One warp per row: run-wise initialisation.  grid = (ceil(h/4), batch), block = 128.
 template <class Fg, class Edge>
-__global__ void k_uf_init_rows(Fg fg, Edge edge, ull* __restrict__ uf, int h, int w) {
+__global__ void k_uf_init_rows(Fg fg, Edge edge, ull* __restrict__ uf, int h, int w, const int* __restrict__ active) {
   const int b = blockIdx.y, y = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (y >= h) return;
+  if (y >= h || (active && active[b] < 0)) return;
   ull* u = uf + (size_t)b * h * w;
   bool carry_run = false;
   int carry_start = 0, carry_delta = 0;
@@ -102,8 +102,9 @@ __global__ void k_uf_init_rows(Fg fg, Edge edge, ull* __restrict__ uf, int h, in
 // inconsistent loops (phase residues).  grid = (ceil(w/256), h, batch).
 template <class Fg, class Edge>
 __global__ void k_uf_merge(Fg fg, Edge edge, ull* __restrict__ uf, unsigned int* __restrict__ bad, size_t bad_stride,
-                           int h, int w) {
+                           int h, int w, const int* __restrict__ active) {
   const int b = blockIdx.z, y = blockIdx.y, x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (active && active[b] < 0) return;
   if (y == 0 || x >= w || !fg(b, y, x)) return;
   ull* u = uf + (size_t)b * h * w;
   const int p = y * w + x;
@@ -122,8 +123,10 @@ __global__ void k_uf_merge(Fg fg, Edge edge, ull* __restrict__ uf, unsigned int*
 
 // Flatten: every foreground word becomes (root, k - k[root]); optionally accumulates component areas
 // (area[b][root], pre-zeroed).  grid = (ceil(npix/256), batch).
-static __global__ void k_uf_flatten(ull* __restrict__ uf, unsigned int* __restrict__ area, int npix) {
+static __global__ void k_uf_flatten(ull* __restrict__ uf, unsigned int* __restrict__ area, int npix,
+                                    const int* __restrict__ active) {
   const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (active && active[b] < 0) return;
   ull* u = uf + (size_t)b * npix;
   unsigned int root = UF_BG;
   if (i < npix) {
@@ -154,12 +157,13 @@ static __global__ void k_uf_largest(const ull* __restrict__ uf, const unsigned i
 
 template <class Fg, class Edge>
 static int uf_label(Fg fg, Edge edge, ull* uf, unsigned int* area, unsigned int* bad, size_t bad_stride, int h, int w,
-                    int batch, cudaStream_t st) {
+                    int batch, cudaStream_t st, const int* active = nullptr) {
+  // active (optional, device): frames b with active[b] < 0 are skipped by every kernel (their planes stay undefined)
   const int npix = h * w;
-  VL(), k_uf_init_rows<Fg, Edge><<<dim3(cdiv(h, 4), batch), 128, 0, st>>>(fg, edge, uf, h, w);
-  VL(), k_uf_merge<Fg, Edge><<<dim3(cdiv(w, 256), h, batch), 256, 0, st>>>(fg, edge, uf, bad, bad_stride, h, w);
+  VL(), k_uf_init_rows<Fg, Edge><<<dim3(cdiv(h, 4), batch), 128, 0, st>>>(fg, edge, uf, h, w, active);
+  VL(), k_uf_merge<Fg, Edge><<<dim3(cdiv(w, 256), h, batch), 256, 0, st>>>(fg, edge, uf, bad, bad_stride, h, w, active);
   if (area) CK(cudaMemsetAsync(area, 0, sizeof(unsigned int) * (size_t)npix * batch, st));
-  VL(), k_uf_flatten<<<dim3(cdiv(npix, 256), batch), 256, 0, st>>>(uf, area, npix);
+  VL(), k_uf_flatten<<<dim3(cdiv(npix, 256), batch), 256, 0, st>>>(uf, area, npix, active);
   CKL();
   return 0;
 }

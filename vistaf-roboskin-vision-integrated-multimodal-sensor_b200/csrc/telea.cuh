@@ -76,11 +76,13 @@ static inline void telea_ws_carve(char* base, int h, int w, int batch, TeleaWs& 
 // ------------------------------------------------------------------ 1. flags on the padded frame
 // Mask: bool operator()(int b, int y, int x) on image coordinates.  block (32, 8), tile 32 x 32.
 template <class Mask>
-__global__ void k_telea_prep(Mask mask, uint8_t* __restrict__ flag, float* __restrict__ T, int h, int w, int range) {
-  extern __shared__ uint8_t sm[];                 // m[(32+2R)^2], rowhit[(32+2R) x 32]
+__global__ void k_telea_prep(Mask mask, uint8_t* __restrict__ flag, float* __restrict__ T, int h, int w, int range,
+                             const int* __restrict__ active) {
+  if (active && active[blockIdx.z] < 0) return;
+  extern __shared__ uint8_t tl_prep_sm[];         // m[(32+2R)^2], rowhit[(32+2R) x 32]
   const int R = range, TW = 32 + 2 * R;
-  uint8_t* m = sm;
-  uint8_t* rh = sm + TW * TW;
+  uint8_t* m = tl_prep_sm;
+  uint8_t* rh = tl_prep_sm + TW * TW;
   const int Hp = h + 2, Wp = w + 2, b = blockIdx.z;
   const int X0 = blockIdx.x * 32, Y0 = blockIdx.y * 32;      // padded coordinates of the tile
   const int tid = threadIdx.y * 32 + threadIdx.x;
@@ -125,8 +127,9 @@ struct TeleaFg {          // cluster foreground on the padded frame
 // ------------------------------------------------------------------ 3. cluster table
 // slots: one slot per union-find root.
 static __global__ void k_telea_slots(const ull* __restrict__ uf, unsigned int* __restrict__ slot, TeleaFrame* fr,
-                              TeleaCluster* cl, int Hp, int Wp) {
+                              TeleaCluster* cl, int Hp, int Wp, const int* __restrict__ active) {
   const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (active && active[b] < 0) return;
   const size_t sp = (size_t)Hp * Wp;
   if (i >= Hp * Wp) return;
   if (uf_parent(uf[(size_t)b * sp + i]) != (unsigned int)i) return;
@@ -140,8 +143,10 @@ static __global__ void k_telea_slots(const ull* __restrict__ uf, unsigned int* _
 }
 // counts: cells and band cells per cluster (warp-aggregated by root).
 static __global__ void k_telea_count(const ull* __restrict__ uf, const unsigned int* __restrict__ slot,
-                              const uint8_t* __restrict__ flag, TeleaCluster* cl, int Hp, int Wp) {
+                              const uint8_t* __restrict__ flag, TeleaCluster* cl, int Hp, int Wp,
+                              const int* __restrict__ active) {
   const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (active && active[b] < 0) return;
   const size_t sp = (size_t)Hp * Wp;
   unsigned int root = UF_BG;
   bool band = false;
@@ -218,8 +223,9 @@ static __global__ void __launch_bounds__(256) k_telea_schedule(TeleaFrame* fr, T
 // band lists (unordered within a cluster; the heap keys carry the raster order).
 static __global__ void k_telea_bandlist(const ull* __restrict__ uf, const unsigned int* __restrict__ slot,
                                  const uint8_t* __restrict__ flag, TeleaCluster* cl, int* __restrict__ band, size_t cap,
-                                 int Hp, int Wp) {
+                                 int Hp, int Wp, const int* __restrict__ active) {
   const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (active && active[b] < 0) return;
   const size_t sp = (size_t)Hp * Wp;
   if (i >= Hp * Wp) return;
   if (!(flag[(size_t)b * sp + i] & TL_BAND)) return;
@@ -361,7 +367,8 @@ __device__ __forceinline__ void tl_gather(const uint8_t* f, const float* T, int 
 }
 
 static __global__ void __launch_bounds__(32 * TL_WARPS) k_telea_march(TeleaWs Wsp, float* __restrict__ img,
-                                                                size_t img_stride, int h, int w, int range, int batch) {
+                                                                size_t img_stride, int h, int w, int range, int batch,
+                                                                int quant) {
   extern __shared__ unsigned char tl_smem[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   ull* sk = (ull*)tl_smem + (size_t)wid * TL_HCAP;
@@ -533,7 +540,10 @@ static __global__ void __launch_bounds__(32 * TL_WARPS) k_telea_march(TeleaWs Ws
         Ia = __shfl_sync(0xffffffffu, Ia, 0); Jx = __shfl_sync(0xffffffffu, Jx, 1);
         Jy = __shfl_sync(0xffffffffu, Jy, 2); sw = __shfl_sync(0xffffffffu, sw, 3);
         const float nrm = __fadd_rn(__fsqrt_rn(__fadd_rn(__fmul_rn(Jx, Jx), __fmul_rn(Jy, Jy))), 1.0e-20f);
-        const float val = __fadd_rn(__fdiv_rn(Ia, sw), __fdiv_rn(__fadd_rn(Jx, Jy), nrm));
+        float val = __fadd_rn(__fdiv_rn(Ia, sw), __fdiv_rn(__fadd_rn(Jx, Jy), nrm));
+        // 8-bit images (cv2.inpaint on CV_8UC1): OpenCV stores saturate_cast<uchar>(value + 0.5f), i.e. round-half-even of
+        // the biased value clamped to [0, 255]; later taps read the stored byte.
+        if (quant) val = fminf(fmaxf(rintf(__fadd_rn(val, 0.5f)), 0.f), 255.f);
         if (lane == 0) {
           im[(size_t)(i - 1) * w + (j - 1)] = val;
           T[p] = dist;
@@ -549,23 +559,24 @@ static __global__ void __launch_bounds__(32 * TL_WARPS) k_telea_march(TeleaWs Ws
 // Host driver.  mask functor on image coordinates; img is modified in place on the hole pixels.
 template <class Mask>
 static int telea_inpaint(Mask mask, float* img, size_t img_stride, unsigned int* status, size_t status_stride,
-                         char* ws, int h, int w, int batch, int range, cudaStream_t st) {
+                         char* ws, int h, int w, int batch, int range, cudaStream_t st, int quant = 0,
+                         const int* active = nullptr) {
   if (range < 1 || range > 8) return vistaf_set_err("telea: radius out of range", cudaErrorInvalidValue, __FILE__, __LINE__);
   TeleaWs W;
   telea_ws_carve(ws, h, w, batch, W);
   const int Hp = h + 2, Wp = w + 2, sp = Hp * Wp;
   const int TW = 32 + 2 * range;
   VL(), k_telea_prep<Mask><<<dim3(cdiv(Wp, 32), cdiv(Hp, 32), batch), dim3(32, 8), (size_t)TW * TW + (size_t)TW * 32, st>>>(
-      mask, W.flag, W.T, h, w, range);
+      mask, W.flag, W.T, h, w, range, active);
   CKL();
   TeleaFg fg{W.flag, (size_t)sp, Wp};
-  if (uf_label(fg, EdgeZero(), W.uf, (unsigned int*)nullptr, (unsigned int*)nullptr, 0, Hp, Wp, batch, st)) return 1;
+  if (uf_label(fg, EdgeZero(), W.uf, (unsigned int*)nullptr, (unsigned int*)nullptr, 0, Hp, Wp, batch, st, active)) return 1;
   CK(cudaMemsetAsync(W.fr, 0, sizeof(TeleaFrame) * (size_t)batch, st));
   const dim3 gcell(cdiv(sp, 256), batch);
-  VL(), k_telea_slots<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.fr, W.cl, Hp, Wp);
-  VL(), k_telea_count<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.flag, W.cl, Hp, Wp);
+  VL(), k_telea_slots<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.fr, W.cl, Hp, Wp, active);
+  VL(), k_telea_count<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.flag, W.cl, Hp, Wp, active);
   VL(), k_telea_schedule<<<batch, 256, 0, st>>>(W.fr, W.cl, W.order, (unsigned int)W.cap, status, status_stride);
-  VL(), k_telea_bandlist<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.flag, W.cl, W.band, W.cap, Hp, Wp);
+  VL(), k_telea_bandlist<<<gcell, 256, 0, st>>>(W.uf, W.slot, W.flag, W.cl, W.band, W.cap, Hp, Wp, active);
   const size_t march_smem = (size_t)TL_WARPS * (TL_HCAP * 12 + 32 * 16) + (size_t)TL_MAXTAPS * 8;
   static int n_sm = 0;
   if (!n_sm) {
@@ -574,7 +585,7 @@ static int telea_inpaint(Mask mask, float* img, size_t img_stride, unsigned int*
     CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
     CK(cudaFuncSetAttribute((const void*)k_telea_march, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)march_smem));
   }
-  VL(), k_telea_march<<<n_sm * TL_BLOCKS_PER_SM, 32 * TL_WARPS, march_smem, st>>>(W, img, img_stride, h, w, range, batch);
+  VL(), k_telea_march<<<n_sm * TL_BLOCKS_PER_SM, 32 * TL_WARPS, march_smem, st>>>(W, img, img_stride, h, w, range, batch, quant);
   CKL();
   return 0;
 }

@@ -7,9 +7,12 @@
 #include "blur.cuh"
 #include "select.cuh"
 #include "morph.cuh"
+#include "labels.cuh"
+#include "telea.cuh"
 #include <string.h>
 #include <new>
 #include <vector>
+#include <algorithm>
 
 #define TOPK 16
 #define COLS_PER_BLOCK 2      // 2 columns x 2 buffers x 2161 float2 = 69 KB: three blocks per SM overlap each other's barriers
@@ -23,6 +26,8 @@ struct Cand { float mag; int ky, kx; int pad; };
 
 struct TempWs {               // per-chunk workspace layout (byte offsets), planes are [chunk][...]
   size_t gray8, satraw, sat, norm, tmp, A, G, maskA, m1, m2, cand, scal, sel, total;
+  size_t t10_frame, t10_stat, t10_wide, t10_color, t10_telea;      // T10 slots (saturated frames only)
+  int t10_slots;
 };
 
 struct TempScal {             // per-frame scalars living in the workspace
@@ -42,7 +47,8 @@ struct TempScal {             // per-frame scalars living in the workspace
   unsigned int t_count, pad;
   double rot_c, rot_s;          // cos / sin of phi0 (temperature_sensor.py:470-474), set by k_temp_phi0
   float blur_rc, blur_cc;       // sigma-20 blur of the constant background: row pass R(median), column pass C(R(median))
-  float pad2[2];
+  int t10_slot;                 // T10 slot of a saturated frame (-1: none free, the fill is skipped and flagged)
+  unsigned int wmin_key, wmax_key, pad2;      // ordered keys of min / max of the raw wide-model map over roi_eff
 };
 
 struct VistafTempPlan {
@@ -705,7 +711,33 @@ struct FeatArgs {
   int h, w;
   int bx0, bx1, by0, by1;        // ROI bounding box: tiles outside it only write the NaN / zero background
   float color_lo, color_hi, ok_lo, ok_hi, blend_lo, blend_hi, final_lo, final_hi, chroma_min;
+  // T10 (saturated frames that own a slot): raw wide-model map and clamped colour map on the ROI window
+  float *t10_wide, *t10_color; const int* t10_frame; unsigned int* t10_stat;
+  int wx0, wy0, ww, wh;
 };
+
+// fusion of the wide and colour maps at one pixel (temperature_sensor.py:594-641); wide / colour are clamped already
+__device__ __forceinline__ float fuse_px(const FeatArgs& a, float wide, float color, bool support, int& cok, int& source) {
+  cok = support && color >= a.ok_lo && color <= a.ok_hi;
+  source = 0;
+  float fused = wide;
+  if (cok) { fused = color; source = 255; }
+  if (wide == wide && cok && wide > a.blend_lo && wide < a.blend_hi) {
+    float wg = __fdiv_rn(__fsub_rn(a.blend_hi, wide), __fsub_rn(a.blend_hi, a.blend_lo));
+    wg = fminf(fmaxf(wg, 0.f), 1.f);
+    fused = __fadd_rn(__fmul_rn(wg, color), __fmul_rn(__fsub_rn(1.0f, wg), wide));
+    source = 128;
+  }
+  if (fused == fused) fused = fminf(fmaxf(fused, a.final_lo), a.final_hi);
+  return fused;
+}
+__device__ __forceinline__ unsigned int f32_key(float f) {       // order-preserving uint key of a float
+  const unsigned int u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key_f32(unsigned int k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
 
 #define FT_W 32
 #define FT_H 16
@@ -737,12 +769,14 @@ __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
   }
   __syncthreads();
   const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
-  int n_ok = 0, n_dark = 0;
+  int n_ok = 0, n_dark = 0, slot = -1;
+  float wlo = 3.0e38f, whi = -3.0e38f;
   if (x < w && y < h) {
     const size_t i = (size_t)y * w + x, bi = (size_t)b * plane + i;
     const TempScal& S = a.sc[b];
     const bool in_roi = a.roi[i] != 0;
     const bool is_sat = in_roi && sat_at(S, a.sat + (size_t)b * plane, i);
+    slot = S.sat_count ? S.t10_slot : -1;
     float fused = __int_as_float(0x7fc00000);
     int light = 0, support = 0, cok = 0, source = 0;
     if (in_roi) {
@@ -785,21 +819,17 @@ __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
       }
       const int ca = A - 128, cb = Bb - 128;
       support = light_d && roi_eff && (sqrtf((float)(ca * ca + cb * cb)) >= a.chroma_min);
-      float wide = __int_as_float(0x7fc00000), color = wide;
-      if (roi_eff) wide = fminf(fmaxf(model_predict(a.models + 1, feat), a.final_lo), a.final_hi);
+      float wide = __int_as_float(0x7fc00000), color = wide, wraw = wide;
+      if (roi_eff) { wraw = model_predict(a.models + 1, feat); wide = fminf(fmaxf(wraw, a.final_lo), a.final_hi); }
       if (support) color = fminf(fmaxf(model_predict(a.models + 0, feat), a.color_lo), a.color_hi);
-      // fusion (temperature_sensor.py:594-641)
-      const bool wide_ok = roi_eff;                 // finite
-      cok = support && color >= a.ok_lo && color <= a.ok_hi;
-      fused = wide;
-      if (cok) { fused = color; source = 255; }
-      if (wide_ok && cok && wide > a.blend_lo && wide < a.blend_hi) {
-        float wg = __fdiv_rn(__fsub_rn(a.blend_hi, wide), __fsub_rn(a.blend_hi, a.blend_lo));
-        wg = fminf(fmaxf(wg, 0.f), 1.f);
-        fused = __fadd_rn(__fmul_rn(wg, color), __fmul_rn(__fsub_rn(1.0f, wg), wide));
-        source = 128;
+      fused = fuse_px(a, wide, color, support, cok, source);
+      if (slot >= 0) {          // saturated frame: k_t10_refuse redoes the fusion from the Telea-filled wide map
+        const size_t wi = ((size_t)slot * a.wh + (y - a.wy0)) * a.ww + (x - a.wx0);
+        a.t10_wide[wi] = wraw;
+        a.t10_color[wi] = color;
+        if (roi_eff) { wlo = wraw; whi = wraw; }
+        cok = 0;
       }
-      if (fused == fused) fused = fminf(fmaxf(fused, a.final_lo), a.final_hi);
       n_ok += cok;
     }
     a.fused[bi] = fused;
@@ -815,6 +845,95 @@ __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
     if (n_ok) atomicAdd(&a.sc[b].color_ok_count, (unsigned)n_ok);
     if (n_dark) atomicAdd(&a.sc[b].dark_count, (unsigned)n_dark);
   }
+  if (__any_sync(0xffffffffu, slot >= 0)) {       // min / max of the raw wide map over roi_eff (temperature_sensor.py:557)
+    wlo = warp_min(wlo); whi = warp_max(whi);
+    if ((tid & 31) == 0 && wlo <= whi) {
+      atomicMin(&a.sc[b].wmin_key, f32_key(wlo));
+      atomicMax(&a.sc[b].wmax_key, f32_key(whi));
+    }
+  }
+}
+
+// ------------------------------------------------------------------ T10: Telea fill of the wide map on saturated frames
+// temperature_sensor.py:546-577: when a masked-in pixel is non-finite (= saturated pixels exist) the known values are
+// quantised to 8 bits over [vmin, vmax], the holes are filled by cv2.inpaint(TELEA, r = 7) and EVERY inside value is
+// replaced by the de-quantised byte.  Saturated frames are rare, so the step runs on `slots` compacted frames per chunk.
+__global__ void k_t10_slots(TempScal* sc, int nb, int* slot_frame, unsigned int* slot_stat, int slots) {
+  if (threadIdx.x) return;
+  int n = 0;
+  for (int b = 0; b < nb; b++) {
+    if (!sc[b].sat_count) continue;
+    if (n < slots) { slot_frame[n] = b; sc[b].t10_slot = n++; }
+    else sc[b].status |= VISTAF_ST_SAT_UNFILLED;
+  }
+  for (int s = 0; s < slots; s++) { slot_stat[s] = 0; if (s >= n) slot_frame[s] = -1; }
+}
+// mode 0: quantise + Telea; 1: flat map (hole pixels take vmin, :562-565); 2: no known pixel (pass-through)
+__device__ __forceinline__ int t10_mode(const TempScal& S, float& vmin, float& rng) {
+  if (S.wmin_key > S.wmax_key) { vmin = 0.f; rng = 0.f; return 2; }
+  vmin = key_f32(S.wmin_key);
+  const double d = (double)key_f32(S.wmax_key) - (double)vmin;
+  rng = (float)d;
+  return d < 1e-6 ? 1 : 0;
+}
+__global__ void k_t10_quant(FeatArgs a) {
+  const int s = blockIdx.z, b = a.t10_frame[s];
+  if (b < 0) return;
+  const int wx = blockIdx.x * blockDim.x + threadIdx.x, wy = blockIdx.y;
+  if (wx >= a.ww) return;
+  const TempScal& S = a.sc[b];
+  float vmin, rng;
+  const int mode = t10_mode(S, vmin, rng);
+  const size_t i = (size_t)(wy + a.wy0) * a.w + wx + a.wx0, wi = ((size_t)s * a.wh + wy) * a.ww + wx;
+  const bool in_roi = a.roi[i] != 0;
+  const bool known = in_roi && !sat_at(S, a.sat + (size_t)b * a.h * a.w, i);
+  float v = known ? a.t10_wide[wi] : 0.f;
+  if (mode == 0) {
+    if (known) v = truncf(fminf(fmaxf(__fmul_rn(__fdiv_rn(__fsub_rn(v, vmin), rng), 255.0f), 0.f), 255.f));
+  } else if (mode == 1 && in_roi && !known) v = vmin;
+  a.t10_wide[wi] = v;
+}
+struct T10Mask {                 // holes of a slot's window: roi & saturated
+  const int* slot_frame; const uint8_t* roi; const uint8_t* sat; const TempScal* sc; size_t plane; int W, wx0, wy0;
+  __device__ bool operator()(int s, int y, int x) const {
+    const int b = slot_frame[s];
+    if (b < 0) return false;
+    const TempScal& S = sc[b];
+    float vmin, rng;
+    if (t10_mode(S, vmin, rng) != 0) return false;
+    const size_t i = (size_t)(y + wy0) * W + x + wx0;
+    return roi[i] && sat_at(S, sat + (size_t)b * plane, i);
+  }
+};
+__global__ void k_t10_refuse(FeatArgs a) {
+  const int s = blockIdx.z, b = a.t10_frame[s];
+  if (b < 0) return;
+  const int wx = blockIdx.x * blockDim.x + threadIdx.x, wy = blockIdx.y;
+  TempScal& S = a.sc[b];
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && a.t10_stat[s]) atomicOr(&S.status, a.t10_stat[s]);
+  int cok = 0;
+  if (wx < a.ww) {
+    float vmin, rng;
+    const int mode = t10_mode(S, vmin, rng);
+    const size_t plane = (size_t)a.h * a.w;
+    const size_t i = (size_t)(wy + a.wy0) * a.w + wx + a.wx0, wi = ((size_t)s * a.wh + wy) * a.ww + wx;
+    if (a.roi[i]) {
+      float wide = a.t10_wide[wi];
+      if (mode == 0) wide = __fadd_rn(__fmul_rn(__fdiv_rn(wide, 255.0f), rng), vmin);
+      else if (mode == 2) wide = __int_as_float(0x7fc00000);
+      else if (sat_at(S, a.sat + (size_t)b * plane, i)) wide = vmin;
+      if (wide == wide) wide = fminf(fmaxf(wide, a.final_lo), a.final_hi);
+      const float color = a.t10_color[wi];
+      int source;
+      const float fused = fuse_px(a, wide, color, color == color, cok, source);
+      const size_t bi = (size_t)b * plane + i;
+      a.fused[bi] = fused;
+      if (a.o_colorok) a.o_colorok[bi] = cok;
+      if (a.o_source) a.o_source[bi] = source;
+    }
+  }
+  cok = warp_sum(cok);
+  if ((threadIdx.x & 31) == 0 && cok) atomicAdd(&S.color_ok_count, (unsigned)cok);
 }
 
 // ------------------------------------------------------------------ T12: oriented smoothing + M1 statistics
@@ -878,6 +997,7 @@ __global__ void k_temp_init(TempScal* sc, int n) {
   TempScal z;
   memset(&z, 0, sizeof(z));
   z.t_min = 3.0e38f; z.t_max = 0.f;
+  z.t10_slot = -1; z.wmin_key = 0xffffffffu; z.wmax_key = 0u;
   sc[i] = z;
 }
 
@@ -904,11 +1024,19 @@ __global__ void k_temp_records(const TempScal* sc, const SelectState* sel, Vista
   r.median_gray = s.median;
   r.sat_pixels = (int)s.sat_count; r.roi_eff_pixels = (int)s.n_eff;
   r.dark_pixels = (int)s.dark_count; r.color_ok_pixels = (int)s.color_ok_count;
-  r.status = (int)s.status | (s.sat_count ? VISTAF_ST_SATURATED : 0);
+  r.status = (int)s.status | (s.sat_count ? VISTAF_ST_SATURATED : 0);      // SAT_UNFILLED comes from k_t10_slots
   rec[i] = r;
 }
 
 // ================================================================== host side
+struct T10Win { int x0, y0, w, h; };
+#define T10_RADIUS 7            // temperature_sensor.py:829 (wide map); the colour map never has holes inside its support
+static T10Win t10_window(const VistafTempPlan* p) {       // ROI bounding box grown past the Telea ring
+  const int m = T10_RADIUS + 5;
+  const int x0 = std::max(0, p->x0 - m), x1 = std::min(p->W, p->x1 + m);
+  const int y0 = std::max(0, p->y0 - m), y1 = std::min(p->H, p->y1 + m);
+  return T10Win{x0, y0, x1 - x0, y1 - y0};
+}
 static void temp_layout(const VistafTempPlan* p, int chunk, TempWs& L) {
   const size_t npix = (size_t)p->H * p->W, c = (size_t)chunk;
   size_t o = 0;
@@ -926,6 +1054,16 @@ static void temp_layout(const VistafTempPlan* p, int chunk, TempWs& L) {
   L.cand = take(c * (size_t)p->nblk_cols * TOPK * sizeof(Cand));
   L.scal = take(c * sizeof(TempScal));
   L.sel = take(sel_ws_bytes((int)c, TEMP_SEL_CAP));
+  // T10 works on the ROI window of at most an eighth of the chunk's frames at a time (saturated frames are rare; every
+  // slot costs a round of empty launches on frames without glare)
+  const T10Win wn = t10_window(p);
+  const size_t ts = (size_t)((chunk + 7) / 8), wpix = (size_t)wn.h * wn.w;
+  L.t10_slots = (int)ts;
+  L.t10_frame = take(ts * 4);
+  L.t10_stat = take(ts * 4);
+  L.t10_wide = take(ts * wpix * 4);
+  L.t10_color = take(ts * wpix * 4);
+  L.t10_telea = take(telea_ws_bytes(wn.h, wn.w, (int)ts));
   L.total = o;
 }
 
@@ -1152,8 +1290,25 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   fa.ok_lo = P.color_t_min - P.guard_band; fa.ok_hi = P.color_t_max + P.guard_band;
   fa.blend_lo = P.color_t_max - P.switch_margin; fa.blend_hi = P.color_t_max + P.switch_margin;
   fa.final_lo = P.final_t_min; fa.final_hi = P.final_t_max; fa.chroma_min = P.chroma_min;
+  const T10Win wn = t10_window(p);
+  const int ts = L.t10_slots;
+  fa.t10_wide = (float*)(ws + L.t10_wide); fa.t10_color = (float*)(ws + L.t10_color);
+  int* t10_frame = (int*)(ws + L.t10_frame);
+  fa.t10_frame = t10_frame; fa.t10_stat = (unsigned int*)(ws + L.t10_stat);
+  fa.wx0 = wn.x0; fa.wy0 = wn.y0; fa.ww = wn.w; fa.wh = wn.h;
+  VL(), k_t10_slots<<<1, 32, 0, st>>>(sc, nb, t10_frame, fa.t10_stat, ts);
   VL(), k_temp_features<<<dim3(cdiv(W, FT_W), cdiv(H, FT_H), nb), dim3(FT_W, FT_H), 0, st>>>(fa);
   CKL();
+  vistaf_stage_mark("T.sat_telea_fill", st);
+  {
+    const dim3 gw(cdiv(wn.w, 256), wn.h, ts);
+    VL(), k_t10_quant<<<gw, 256, 0, st>>>(fa);
+    CKL();
+    if (telea_inpaint(T10Mask{t10_frame, p->roi, sat, sc, (size_t)npix, W, wn.x0, wn.y0}, fa.t10_wide, (size_t)wn.h * wn.w,
+                      fa.t10_stat, sizeof(unsigned int), ws + L.t10_telea, wn.h, wn.w, ts, T10_RADIUS, st, 1, t10_frame)) return 1;
+    VL(), k_t10_refuse<<<gw, 256, 0, st>>>(fa);
+    CKL();
+  }
   vistaf_stage_mark("T.final_blur", st);
   // oriented smoothing (axis aligned) + statistics
   float* fin = O.final_map + f0 * (size_t)npix;

@@ -230,6 +230,16 @@ def run_batch(frames_bgr, chunk: int = 8, masks: bool = True) -> dict:
     plan = get_plan(int(frames_bgr.shape[1]), int(frames_bgr.shape[2]), chunk)
     out = plan.run(frames_bgr, masks=masks)
     out["records_np"] = records_to_numpy(out["records"])
+    # T10 runs on at most an eighth of a chunk's frames; a frame beyond that comes back with ST_SAT_UNFILLED and is redone
+    # here on its own (a one-frame chunk always has a slot), so the synchronous wrapper never returns an unfilled frame.
+    redo = [i for i, r in enumerate(out["records_np"]) if int(r["status"]) & N.ST_SAT_UNFILLED]
+    if redo:
+        one = get_plan(int(frames_bgr.shape[1]), int(frames_bgr.shape[2]), 1)
+        for i in redo:
+            o1 = one.run(frames_bgr[i:i + 1].contiguous(), masks=masks)
+            for k, v in o1.items():
+                out[k][i:i + 1].copy_(v)
+        out["records_np"] = records_to_numpy(out["records"])
     return out
 
 
