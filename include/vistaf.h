@@ -35,6 +35,8 @@ extern "C" {
 #define VISTAF_ST_SIGN_FLIPPED     0x040  /* auto sign flip taken (shape_ftp.py:1759) */
 #define VISTAF_ST_CONTACT_P95      0x080  /* contact threshold fell back to p95 / p98 (shape_ftp.py:1733-1738) */
 #define VISTAF_ST_BG_FALLBACK      0x100  /* background < 15 % of reliable: detrend on reliable (shape_ftp.py:1744) */
+#define VISTAF_ST_SPLIT_RELIABLE   0x400  /* reliable mask not connected after the erosion: unreached components stay NaN; F14 hole fill (shape_ftp.py:1776) not applied */
+#define VISTAF_ST_TELEA_OVERFLOW   0x8000 /* a Telea cluster did not fit the march workspace (hole area > half the frame): those pixels are not filled */
 #define VISTAF_ST_SAT_UNFILLED     0x200  /* more than an eighth of one chunk's frames saturated: T10 skipped for this frame; re-run it in a smaller batch */
 
 /* StandardScaler -> PolynomialFeatures -> linear model [-> isotonic], temperature_sensor.py:236 */

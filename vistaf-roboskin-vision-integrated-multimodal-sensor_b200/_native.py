@@ -17,7 +17,7 @@ MAX_TERMS, MAX_ISO = 35, 64
 
 ST_EMPTY_ROI, ST_NO_PEAK, ST_SATURATED, ST_ROTATED_CARRIER = 0x1, 0x2, 0x4, 0x8
 ST_RESIDUES, ST_FEW_RELIABLE, ST_SIGN_FLIPPED, ST_CONTACT_P95, ST_BG_FALLBACK = 0x10, 0x20, 0x40, 0x80, 0x100
-ST_SAT_UNFILLED = 0x200
+ST_SAT_UNFILLED, ST_SPLIT_RELIABLE, ST_TELEA_OVERFLOW = 0x200, 0x400, 0x8000
 
 
 class PolyModel(C.Structure):

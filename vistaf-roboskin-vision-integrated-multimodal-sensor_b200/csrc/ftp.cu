@@ -529,15 +529,21 @@ __global__ void k_ftp_seed_root(const ull* __restrict__ uf, FtpScal* sc, int npi
   s.seed_root = (int)uf_parent(v);
   s.seed_k = uf_delta(v);
 }
-__global__ void k_ftp_unwrap_apply(const ull* __restrict__ uf, const float* __restrict__ wr, const FtpScal* sc,
+__global__ void k_ftp_unwrap_apply(const ull* __restrict__ uf, const float* __restrict__ wr, FtpScal* sc,
                                    float* __restrict__ unw, int npix) {
   const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= npix) return;
   const ull v = uf[(size_t)b * npix + i];
   float u = FNAN;
-  if (uf_parent(v) != UF_BG && (int)uf_parent(v) == sc[b].seed_root) {
-    const int dk = uf_delta(v) - sc[b].seed_k;
-    u = __fadd_rn(wr[(size_t)b * npix + i], (float)(6.283185307179586 * (double)dk));
+  if (uf_parent(v) != UF_BG) {
+    if ((int)uf_parent(v) == sc[b].seed_root) {
+      const int dk = uf_delta(v) - sc[b].seed_k;
+      u = __fadd_rn(wr[(size_t)b * npix + i], (float)(6.283185307179586 * (double)dk));
+    } else if (!(*(volatile unsigned int*)&sc[b].status & VISTAF_ST_SPLIT_RELIABLE)) {
+      // the erosion (:721) split the reliable mask: the flood never reaches this component (NaN, as in the reference),
+      // but the internal-hole fill and output_reliable bookkeeping of such pixels (F14, :1776-1801) are not carried out
+      atomicOr(&sc[b].status, VISTAF_ST_SPLIT_RELIABLE);
+    }
   }
   unw[(size_t)b * npix + i] = u;
 }

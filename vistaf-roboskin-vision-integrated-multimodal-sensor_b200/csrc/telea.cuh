@@ -218,7 +218,7 @@ static __global__ void __launch_bounds__(256) k_telea_schedule(TeleaFrame* fr, T
     __syncthreads();
   }
   if (tid == 0 && (f->nclusters > TL_MAXCLUSTERS || f->overflow))
-    atomicOr((unsigned int*)((char*)status + (size_t)b * status_stride), 0x8000u);
+    atomicOr((unsigned int*)((char*)status + (size_t)b * status_stride), VISTAF_ST_TELEA_OVERFLOW);
 }
 // band lists (unordered within a cluster; the heap keys carry the raster order).
 static __global__ void k_telea_bandlist(const ull* __restrict__ uf, const unsigned int* __restrict__ slot,
