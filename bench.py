@@ -186,12 +186,15 @@ def main():
     ap.add_argument("--chunk-temp", type=int, default=64, help="temperature frames per library chunk")
     ap.add_argument("--lanes-ftp", type=int, default=4, help="concurrent slices (streams + workspaces) of the FTP batch")
     ap.add_argument("--lanes-temp", type=int, default=2, help="concurrent slices of the temperature batch")
+    ap.add_argument("--distinct", type=int, default=8,
+                    help="distinct synthetic seeds per rank (16 brings in one glare frame per 16: the T10 path)")
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--cpu-workers", type=int, default=None)
     ap.add_argument("--cpu-frames", type=int, default=None, help="frames per CPU step (default: one per worker)")
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     a = ap.parse_args()
+    globals()["N_DISTINCT"] = max(1, a.distinct)
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
     config = {"workload": f"{a.workload}: {a.frames} synthetic 2160x3840 BGR fringe+TLC frames per GPU per step "
