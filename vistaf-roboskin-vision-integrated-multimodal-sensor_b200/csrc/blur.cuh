@@ -75,10 +75,12 @@ __global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* 
   if (y < win.ry0 || y >= win.ry1 || x0 >= win.x1 + 32 || x0 + BLUR_ROW_SEG <= win.x0 - 32) return;
   const int rad = g.ksize >> 1;
   const int need = BLUR_ROW_SEG + g.kpad + 8;
+  // inputs of outputs nobody reads (farther than the kernel radius from the window grown by one column block) stay 0
+  const int xlo = win.x0 - 40 - rad, xhi = win.x1 + 40 + rad;
   for (int e = threadIdx.x; e < need; e += BLUR_ROW_THREADS) {
     int x = x0 - rad + e;
     float v = 0.f;
-    if (e < BLUR_ROW_SEG + g.ksize - 1 && x < w + rad) v = ld(b, y, reflect101(x, w));
+    if (e < BLUR_ROW_SEG + g.ksize - 1 && x < w + rad && x >= xlo && x < xhi) v = ld(b, y, reflect101(x, w));
     s[(e & 7) * BLUR_ROW_PITCH + (e >> 3)] = v;
   }
   for (int e = threadIdx.x; e < g.kpad; e += BLUR_ROW_THREADS) wk[e] = g.w[e];
