@@ -141,6 +141,8 @@ __device__ __forceinline__ unsigned int sel_next_bin(const unsigned int* hist, u
 }
 
 // ---- S1: level-1 histogram (top 11 key bits) + rank location by the last block of each frame.
+#define SEL_U 4                 // element fetches in flight per thread in the S1 / S2 sweeps
+#define SEL_TILE (256 * SEL_U)  // elements per block per sweep step
 template <class Val>
 __global__ void __launch_bounds__(256) k_sel_s1(Val val, SelectState* st, long long n, float q0, const float* qv,
                                                 size_t qstride, unsigned int cap) {
@@ -154,13 +156,13 @@ __global__ void __launch_bounds__(256) k_sel_s1(Val val, SelectState* st, long l
   n = sel_limit(val, b, n, 0);
   // four independent element fetches are in flight before the first histogram update (the value functors are
   // chains of dependent loads: mask byte, then sample)
-  for (long long i0 = (long long)blockIdx.x * 1024 + threadIdx.x; i0 < n; i0 += (long long)gridDim.x * 1024) {
-    float v[4];
-    bool ok[4];
+  for (long long i0 = (long long)blockIdx.x * SEL_TILE + threadIdx.x; i0 < n; i0 += (long long)gridDim.x * SEL_TILE) {
+    float v[SEL_U];
+    bool ok[SEL_U];
 #pragma unroll
-    for (int j = 0; j < 4; j++) { const long long i = i0 + (long long)j * 256; ok[j] = i < n && val(b, i, v[j]); }
+    for (int j = 0; j < SEL_U; j++) { const long long i = i0 + (long long)j * 256; ok[j] = i < n && val(b, i, v[j]); }
 #pragma unroll
-    for (int j = 0; j < 4; j++) if (ok[j]) atomicAdd(&h[f2key(v[j]) >> 21], 1u);
+    for (int j = 0; j < SEL_U; j++) if (ok[j]) atomicAdd(&h[f2key(v[j]) >> 21], 1u);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < SEL_BINS; i += 256)
@@ -214,15 +216,15 @@ __global__ void __launch_bounds__(256) k_sel_s2(Val val, SelectState* st, unsign
   unsigned int mn = 0xffffffffu;
   n = sel_limit(val, b, n, 0);
   // warp-uniform trip count (ballots inside): lanes of a warp walk consecutive elements
-  const long long stride = (long long)gridDim.x * 1024;
-  const long long start = (long long)blockIdx.x * 1024 + (threadIdx.x & ~31) * 4;
+  const long long stride = (long long)gridDim.x * SEL_TILE;
+  const long long start = (long long)blockIdx.x * SEL_TILE + (threadIdx.x & ~31) * SEL_U;
   for (long long i0 = start; i0 < n; i0 += stride) {
-    float v[4];
-    bool ok[4];
+    float v[SEL_U];
+    bool ok[SEL_U];
 #pragma unroll
-    for (int j = 0; j < 4; j++) { const long long i = i0 + j * 32 + lane; ok[j] = i < n && val(b, i, v[j]); }
+    for (int j = 0; j < SEL_U; j++) { const long long i = i0 + j * 32 + lane; ok[j] = i < n && val(b, i, v[j]); }
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
+    for (int j = 0; j < SEL_U; j++) {
       unsigned int key = 0;
       bool take = false;
       if (ok[j]) {
