@@ -741,13 +741,20 @@ __device__ __forceinline__ float key_f32(unsigned int k) {
 
 #define FT_W 32
 #define FT_H 16
+// T10 = false: every frame of the chunk (grid.z = frame), all outputs.  T10 = true: the saturated frames only (grid.z =
+// T10 slot): the same per-pixel features and models, but the only products are the raw wide map and the clamped colour
+// map on the slot's ROI window plus min / max of the raw wide map -- the inputs of k_t10_quant / k_t10_refuse.
+template <bool T10>
 __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
   __shared__ uint8_t tile[(FT_H + 4) * (FT_W + 4) * 3];
-  const int b = blockIdx.z, x0 = blockIdx.x * FT_W, y0 = blockIdx.y * FT_H, h = a.h, w = a.w;
+  const int b = T10 ? a.t10_frame[blockIdx.z] : (int)blockIdx.z;
+  if (T10 && b < 0) return;
+  const int x0 = blockIdx.x * FT_W, y0 = blockIdx.y * FT_H, h = a.h, w = a.w;
   const size_t plane = (size_t)h * w;
   const uint8_t* img = a.frames + (size_t)b * plane * 3;
   const int tid = threadIdx.y * FT_W + threadIdx.x;
   if (x0 >= a.bx1 || x0 + FT_W <= a.bx0 || y0 >= a.by1 || y0 + FT_H <= a.by0) {
+    if (T10) return;
     const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
     if (x < w && y < h) {
       const size_t bi = (size_t)b * plane + (size_t)y * w + x;
@@ -776,7 +783,7 @@ __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
     const TempScal& S = a.sc[b];
     const bool in_roi = a.roi[i] != 0;
     const bool is_sat = in_roi && sat_at(S, a.sat + (size_t)b * plane, i);
-    slot = S.sat_count ? S.t10_slot : -1;
+    slot = (T10 || S.sat_count) ? S.t10_slot : -1;
     float fused = __int_as_float(0x7fc00000);
     int light = 0, support = 0, cok = 0, source = 0;
     if (in_roi) {
@@ -822,35 +829,39 @@ __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
       float wide = __int_as_float(0x7fc00000), color = wide, wraw = wide;
       if (roi_eff) { wraw = model_predict(a.models + 1, feat); wide = fminf(fmaxf(wraw, a.final_lo), a.final_hi); }
       if (support) color = fminf(fmaxf(model_predict(a.models + 0, feat), a.color_lo), a.color_hi);
-      fused = fuse_px(a, wide, color, support, cok, source);
-      if (slot >= 0) {          // saturated frame: k_t10_refuse redoes the fusion from the Telea-filled wide map
+      if (T10) {
         const size_t wi = ((size_t)slot * a.wh + (y - a.wy0)) * a.ww + (x - a.wx0);
         a.t10_wide[wi] = wraw;
         a.t10_color[wi] = color;
         if (roi_eff) { wlo = wraw; whi = wraw; }
-        cok = 0;
+      } else {
+        fused = fuse_px(a, wide, color, support, cok, source);
+        if (slot >= 0) cok = 0;     // saturated frame: k_t10_refuse redoes the fusion from the Telea-filled wide map
+        n_ok += cok;
       }
-      n_ok += cok;
     }
-    a.fused[bi] = fused;
-    if (a.o_sat) a.o_sat[bi] = is_sat;
-    if (a.o_light) a.o_light[bi] = light;
-    if (a.o_support) a.o_support[bi] = support;
-    if (a.o_colorok) a.o_colorok[bi] = cok;
-    if (a.o_source) a.o_source[bi] = source;
+    if (!T10) {
+      a.fused[bi] = fused;
+      if (a.o_sat) a.o_sat[bi] = is_sat;
+      if (a.o_light) a.o_light[bi] = light;
+      if (a.o_support) a.o_support[bi] = support;
+      if (a.o_colorok) a.o_colorok[bi] = cok;
+      if (a.o_source) a.o_source[bi] = source;
+    }
+  }
+  if (T10) {                    // min / max of the raw wide map over roi_eff (temperature_sensor.py:557)
+    wlo = warp_min(wlo); whi = warp_max(whi);
+    if ((tid & 31) == 0 && wlo <= whi) {
+      atomicMin(&a.sc[b].wmin_key, f32_key(wlo));
+      atomicMax(&a.sc[b].wmax_key, f32_key(whi));
+    }
+    return;
   }
   n_ok = warp_sum(n_ok);
   n_dark = warp_sum(n_dark);
   if ((tid & 31) == 0) {
     if (n_ok) atomicAdd(&a.sc[b].color_ok_count, (unsigned)n_ok);
     if (n_dark) atomicAdd(&a.sc[b].dark_count, (unsigned)n_dark);
-  }
-  if (__any_sync(0xffffffffu, slot >= 0)) {       // min / max of the raw wide map over roi_eff (temperature_sensor.py:557)
-    wlo = warp_min(wlo); whi = warp_max(whi);
-    if ((tid & 31) == 0 && wlo <= whi) {
-      atomicMin(&a.sc[b].wmin_key, f32_key(wlo));
-      atomicMax(&a.sc[b].wmax_key, f32_key(whi));
-    }
   }
 }
 
@@ -859,14 +870,20 @@ __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
 // quantised to 8 bits over [vmin, vmax], the holes are filled by cv2.inpaint(TELEA, r = 7) and EVERY inside value is
 // replaced by the de-quantised byte.  Saturated frames are rare, so the step runs on `slots` compacted frames per chunk.
 __global__ void k_t10_slots(TempScal* sc, int nb, int* slot_frame, unsigned int* slot_stat, int slots) {
-  if (threadIdx.x) return;
+  const int lane = threadIdx.x;                  // one warp: frames in order, 32 at a time
   int n = 0;
-  for (int b = 0; b < nb; b++) {
-    if (!sc[b].sat_count) continue;
-    if (n < slots) { slot_frame[n] = b; sc[b].t10_slot = n++; }
-    else sc[b].status |= VISTAF_ST_SAT_UNFILLED;
+  for (int b0 = 0; b0 < nb; b0 += 32) {
+    const int b = b0 + lane;
+    const bool sat = b < nb && sc[b].sat_count != 0;
+    const unsigned int bits = __ballot_sync(0xffffffffu, sat);
+    if (sat) {
+      const int at = n + __popc(bits & ((1u << lane) - 1u));
+      if (at < slots) { slot_frame[at] = b; sc[b].t10_slot = at; }
+      else sc[b].status |= VISTAF_ST_SAT_UNFILLED;
+    }
+    n += __popc(bits);
   }
-  for (int s = 0; s < slots; s++) { slot_stat[s] = 0; if (s >= n) slot_frame[s] = -1; }
+  for (int s = lane; s < slots; s += 32) { slot_stat[s] = 0; if (s >= n) slot_frame[s] = -1; }
 }
 // mode 0: quantise + Telea; 1: flat map (hole pixels take vmin, :562-565); 2: no known pixel (pass-through)
 __device__ __forceinline__ int t10_mode(const TempScal& S, float& vmin, float& rng) {
@@ -1297,11 +1314,12 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   fa.t10_frame = t10_frame; fa.t10_stat = (unsigned int*)(ws + L.t10_stat);
   fa.wx0 = wn.x0; fa.wy0 = wn.y0; fa.ww = wn.w; fa.wh = wn.h;
   VL(), k_t10_slots<<<1, 32, 0, st>>>(sc, nb, t10_frame, fa.t10_stat, ts);
-  VL(), k_temp_features<<<dim3(cdiv(W, FT_W), cdiv(H, FT_H), nb), dim3(FT_W, FT_H), 0, st>>>(fa);
+  VL(), k_temp_features<false><<<dim3(cdiv(W, FT_W), cdiv(H, FT_H), nb), dim3(FT_W, FT_H), 0, st>>>(fa);
   CKL();
   vistaf_stage_mark("T.sat_telea_fill", st);
   {
     const dim3 gw(cdiv(wn.w, 256), wn.h, ts);
+    VL(), k_temp_features<true><<<dim3(cdiv(W, FT_W), cdiv(H, FT_H), ts), dim3(FT_W, FT_H), 0, st>>>(fa);
     VL(), k_t10_quant<<<gw, 256, 0, st>>>(fa);
     CKL();
     if (telea_inpaint(T10Mask{t10_frame, p->roi, sat, sc, (size_t)npix, W, wn.x0, wn.y0}, fa.t10_wide, (size_t)wn.h * wn.w,
