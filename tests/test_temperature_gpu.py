@@ -153,3 +153,25 @@ def test_errors_are_loud(mods):
     plan = TS.get_plan(2160, 3840, 1)
     with pytest.raises(AssertionError):
         plan.run(torch.zeros((1, 100, 100, 3), dtype=torch.uint8, device="cuda"))
+
+
+def test_fully_saturated_frame_is_flagged_and_isolated(mods):
+    """An all-white frame saturates the whole ROI: roi_eff is empty, which the reference refuses
+    (temperature_sensor.py:443 raises).  The batched path must flag it (ST_EMPTY_ROI | ST_SATURATED), must not hang in the
+    T10 fill (no known pixel: pass-through, :551-553), and must leave the other frame of the same chunk untouched."""
+    import torch
+    S, TS, TO = mods
+    import _native as N
+    good = S.make_frame(3)
+    white = np.full_like(good, 255)
+    out = TS.run_batch(np.stack([white, good]), chunk=2)
+    f_pair, d_pair = out["final"][1].clone(), out["dark"][1].clone()
+    r_pair = out["records_np"][1].tobytes()
+    st = int(out["records_np"][0]["status"])
+    assert st & N.ST_EMPTY_ROI and st & N.ST_SATURATED
+    assert int(out["records_np"][0]["roi_eff_pixels"]) == 0
+    alone = TS.run_batch(good[None], chunk=1)
+    a = alone["final"][0]
+    assert bool(((f_pair == a) | (f_pair.isnan() & a.isnan())).all())
+    assert torch.equal(d_pair, alone["dark"][0])
+    assert r_pair == alone["records_np"][0].tobytes()
