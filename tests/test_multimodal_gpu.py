@@ -69,6 +69,13 @@ def test_lanes_begin_finish_and_staging_match_single_stream(env):
     torch.cuda.synchronize()
     _same(got2, want)
 
+    # ragged batch: 5 frames over 3 FTP lanes / 2 temperature lanes (unequal slices, one short lane)
+    got5 = lanes.step(ref_dev, dev[:5].contiguous(), masks=True, reuse_outputs=False)
+    torch.cuda.synchronize()
+    cut = {h: {k: v[:5] for k, v in want[h].items() if hasattr(v, "shape")} for h in ("ftp", "temp")}
+    cut["records"] = want["records"][:5]
+    _same(got5, cut)
+
     # FTP-only and temperature-only plans share the same code paths
     fonly = MS.MultimodalPlan(H, W, chunk_ftp=B, chunk_temp=B, mode="ftp", lanes_ftp=2)
     g3 = fonly.step(ref_dev, dev, masks=True, reuse_outputs=False)
