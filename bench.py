@@ -44,17 +44,21 @@ STAGE_MB = {
 N_DISTINCT = 8          # distinct synthetic frames generated on the host per rank, tiled to the batch on the device
 
 
-def clocks_sampler(stop, samples):
+def clocks_sampler(stop, samples, n_gpus=1):
+    """Rank 0 samples the clocks and throttle reasons of all the job's GPUs (one nvidia-smi call for GPUs 0..n_gpus-1):
+    one poller per node instead of one per rank, so the polling itself does not perturb the other ranks' launches."""
     q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    ids = ",".join(str(i) for i in range(max(1, n_gpus)))
     while not stop.is_set():
         try:
-            o = subprocess.run(["nvidia-smi", "-i", os.environ.get("LOCAL_RANK", "0"), f"--query-gpu={q}",
+            o = subprocess.run(["nvidia-smi", "-i", ids, f"--query-gpu={q}",
                                 "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-            samples.append([x.strip() for x in o.strip().split(",")])
+            for ln in o.strip().splitlines():
+                samples.append([x.strip() for x in ln.split(",")])
         except Exception:
             pass
-        stop.wait(0.2)
+        stop.wait(0.25)
 
 
 def summarize_clocks(samples):
@@ -271,12 +275,16 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    host_ms = [0.0]
+
     def timed(fn, steps):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        t0 = time.perf_counter()
         for _ in range(steps):
             fn()
+        host_ms[0] = (time.perf_counter() - t0) * 1e3 / steps      # host time to ENQUEUE one step (no sync inside; includes launch-queue back-pressure)
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
@@ -288,11 +296,13 @@ def main():
     for _ in range(W):
         step_resident()
     stop, samples = threading.Event(), []
-    th = threading.Thread(target=clocks_sampler, args=(stop, samples), daemon=True)
-    th.start()
+    th = threading.Thread(target=clocks_sampler, args=(stop, samples, world), daemon=True) if rank == 0 else None
+    if th:
+        th.start()
     l0 = N.launch_count()
     ms = timed(step_resident, a.steps)           # the measured region: lanes concurrent, stage timers off
     launches = N.launch_count() - l0
+    host_enqueue_ms = host_ms[0]
     # stage table: the same steps once more with every slice serialised on one stream, so that the CUDA events the
     # library records at the stage boundaries (on the launch stream) bracket exactly one stage each
     def set_serial(on):
@@ -308,7 +318,8 @@ def main():
     N.profile_enable(False)
     set_serial(False)
     stop.set()
-    th.join()
+    if th:
+        th.join()
     step_e2e()
     e2e_steps = max(1, a.steps // 2)
     ms_e2e = timed(step_e2e, e2e_steps)
@@ -335,7 +346,8 @@ def main():
                 "dtype": "f32", "data": "synthetic", "config": config, "clocks": summarize_clocks(samples),
                 "e2e": {"value": fps_e2e, "unit": "frames/s",
                         "h2d_bytes_per_step": int(dev.numel() + ref_dev.numel()), "d2h_bytes_per_step": int(rec.numel())},
-                "gpu_launches": int(launches), "ms_per_step_serialised": ms_serial / a.steps}
+                "gpu_launches": int(launches), "ms_per_step_serialised": ms_serial / a.steps,
+                "host_enqueue_ms_per_step": host_enqueue_ms}
         table_f = [r for r in table if r["GBps"]]
         top = max(table_f, key=lambda r: r["share"]) if table_f else None
         tr_path = os.path.join(REPO, "profiles", "ncu_stage_traffic.json")
