@@ -7,10 +7,14 @@
  * points below through ctypes (INTEGRATION.md shows the stub).  Conventions:
  *   - plain pointers and sizes only; the caller owns every input / output / workspace buffer,
  *     the library owns only the opaque plan handles;
- *   - `*_batch` calls take DEVICE pointers and a cudaStream_t (as void*), are asynchronous;
- *   - `*_host` calls take HOST pointers, stage through the caller-provided device workspace and
- *     synchronise before returning (used by the drop-in single-pair Python API and the e2e bench);
- *   - return 0 on success; vistaf_last_error() describes the last failure of the calling process;
+ *   - every call takes DEVICE pointers and a cudaStream_t (as void*) and is asynchronous; host staging is the
+ *     caller's (PyTorch pinned buffers in the Python modules, multimodal_sensor.MultimodalPlan);
+ *   - a plan is read-only during `*_batch` calls, so several threads / streams may run batches on one plan with
+ *     their own workspaces; vistaf_ftp_set_reference writes the plan and must not overlap `*_finish` / `_batch`
+ *     calls that are still being ENQUEUED (stream order takes care of the device side);
+ *   - return 0 on success; vistaf_last_error() describes the last failure of the calling THREAD;
+ *   - repeated batch calls with identical arguments are replayed from a CUDA graph recorded on the second call
+ *     (vistaf_set_graphs(0) or VISTAF_GRAPHS=0 turns that off);
  *   - per-frame soft failures (empty ROI, no carrier peak, phase residues ...) are reported in the
  *     `status` word of the per-frame record, never through the return code.
  */
@@ -29,15 +33,19 @@ extern "C" {
 #define VISTAF_ST_EMPTY_ROI        0x001  /* temperature_sensor.py:443  / shape_ftp.py:1677 */
 #define VISTAF_ST_NO_PEAK          0x002  /* temperature_sensor.py:457 */
 #define VISTAF_ST_SATURATED        0x004  /* saturated pixels present: wide map quantised + Telea-filled (T10, temperature_sensor.py:546) */
-#define VISTAF_ST_ROTATED_CARRIER  0x008  /* carrier angle != 0: oriented blur ran axis-aligned (T12) */
-#define VISTAF_ST_RESIDUES         0x010  /* phase residues inside the reliable mask: unwrap is path dependent (F10) */
+#define VISTAF_ST_ROTATED_CARRIER  0x008  /* informational: carrier angle != 0, the oriented blur took the warpAffine path (T12, temperature_sensor.py:705) */
+#define VISTAF_ST_RESIDUES         0x010  /* informational: phase residues inside the reliable mask, the unwrap ran as the reference's sequential quality-guided flood (F10) */
 #define VISTAF_ST_FEW_RELIABLE     0x020  /* < 200 reliable pixels: polynomial detrend skipped (shape_ftp.py:1103) */
 #define VISTAF_ST_SIGN_FLIPPED     0x040  /* auto sign flip taken (shape_ftp.py:1759) */
 #define VISTAF_ST_CONTACT_P95      0x080  /* contact threshold fell back to p95 / p98 (shape_ftp.py:1733-1738) */
 #define VISTAF_ST_BG_FALLBACK      0x100  /* background < 15 % of reliable: detrend on reliable (shape_ftp.py:1744) */
-#define VISTAF_ST_SPLIT_RELIABLE   0x400  /* reliable mask not connected after the erosion: unreached components stay NaN; F14 hole fill (shape_ftp.py:1776) not applied */
+#define VISTAF_ST_SPLIT_RELIABLE   0x400  /* informational: reliable mask not connected after the erosion, the flood does not reach every component (as in the reference) */
+#define VISTAF_ST_HOLES_FILLED     0x800  /* internal holes of the reliable mask were Telea-filled (F14, shape_ftp.py:1776-1801) */
 #define VISTAF_ST_TELEA_OVERFLOW   0x8000 /* a Telea cluster did not fit the march workspace (hole area > half the frame): those pixels are not filled */
-#define VISTAF_ST_SAT_UNFILLED     0x200  /* more than an eighth of one chunk's frames saturated: T10 skipped for this frame; re-run it in a smaller batch */
+#define VISTAF_ST_RERUN_ALONE      0x200  /* more than an eighth of one chunk's frames are saturated (T10) or have a tilted carrier (T12): this frame
+                                             found no slot and skipped that step -- run it again in a batch of its own (the Python
+                                             modules do: TempPlan.redo_flagged, MultimodalPlan.records_host) */
+#define VISTAF_ST_SAT_UNFILLED     VISTAF_ST_RERUN_ALONE
 
 /* StandardScaler -> PolynomialFeatures -> linear model [-> isotonic], temperature_sensor.py:236 */
 typedef struct {
@@ -106,6 +114,9 @@ typedef struct {
   int32_t calls, launches;
 } VistafStageTime;
 int vistaf_profile_enable(int on);
+/* CUDA-graph replay of repeated batch calls (default on; off while the stage timers run) and how many calls were replays */
+int vistaf_set_graphs(int on);
+long long vistaf_graph_replays(void);
 int vistaf_profile_read(VistafStageTime* out, int max_stages, int* n_out);
 long long vistaf_launch_count(void);
 
@@ -158,6 +169,11 @@ typedef struct {
   VistafCurveModel height_model;     /* phase -> mm   (shape_ftp.py:672-705) */
   VistafCurveModel force_model;      /* cm^3 -> N     (force_sensor.py:149-167) */
   double grating_pitch_mm, depth_eps_mm;   /* force_sensor.py:32-33 */
+  /* F14, shape_ftp.py:139-145: FILL_INTERNAL_HOLES_IN_RELIABLE, HOLE_NEIGHBORHOOD_PX, HOLE_KNOWN_FRACTION,
+   * HOLE_MIN_DIST_FROM_RELIABLE_EDGE_PX, INPAINT_RADIUS */
+  int32_t fill_internal_holes, hole_neighborhood;
+  float hole_known_frac, hole_min_dist;
+  int32_t hole_inpaint_radius, pad2_;
 } VistafFtpParams;
 
 typedef struct {
@@ -177,6 +193,7 @@ typedef struct {
   uint8_t* contact_dilated;
   uint8_t* contact_kept;
   VistafFtpRecord* records;  /* [B] */
+  uint8_t* hole_candidates;  /* [B][h][w] 0/1, may be NULL (shape_ftp.py:1776-1784) */
 } VistafFtpOutputs;
 
 typedef struct {
@@ -207,6 +224,17 @@ int vistaf_ftp_batch_begin(VistafFtpPlan* plan, const uint8_t* def_gray, int bat
                            void* cuda_stream);
 int vistaf_ftp_batch_finish(VistafFtpPlan* plan, const uint8_t* def_gray, int batch, const VistafFtpOutputs* out,
                             void* workspace, size_t workspace_bytes, void* cuda_stream);
+/* F14 on its own (shape_ftp.py:1153-1203, 1776-1801): height [B][h][w] in/out with NaN where no height is known,
+ * reliable in; output_reliable and hole_candidates out (DEVICE uint8 [B][h][w]).  workspace as for `batch` frames. */
+int vistaf_ftp_fill_holes(VistafFtpPlan* plan, float* height, const uint8_t* reliable, int batch, uint8_t* output_reliable,
+                          uint8_t* hole_candidates, void* workspace, size_t workspace_bytes, void* cuda_stream);
+/* F10 on its own (shape_ftp.py:1043-1080): wrapped / quality float [B][h][w], reliable uint8 -> unwrapped float (NaN where
+ * the flood does not reach); residues[b] = residue count.  mode 0: as the chain does (parallel wrap-count field, the
+ * sequential flood only for frames with residues), 1: sequential flood on every frame. */
+int vistaf_ftp_unwrap(VistafFtpPlan* plan, const float* wrapped, const float* quality, const uint8_t* reliable, int batch,
+                      float* unwrapped, int32_t* residues, int mode, void* workspace, size_t workspace_bytes, void* cuda_stream);
+/* bit 0: run the sequential flood unwrap on every frame of later batches (parity tests) */
+int vistaf_ftp_set_debug(VistafFtpPlan* plan, int flags);
 int vistaf_ftp_masks(const VistafFtpPlan* plan, uint8_t* roi_dev, uint8_t* circ_dev, float* apo_dev, void* cuda_stream);
 int vistaf_ftp_workspace_plane(const VistafFtpPlan* plan, int chunk, const char* name, size_t* offset, size_t* bytes);
 /* force_sensor.depth_map_to_volume_cm3 (:93-123) on DEVICE maps: out3 = DEVICE float64 [B][3] (volume_cm3, area_mm2, max_depth_mm) */

@@ -324,7 +324,9 @@ def robust_polyfit(z, mask, order, iters=6, c=4.685):
 
 
 def masked_smooth(z, mask, sigma):
-    """shape_ftp.py:1139-1147 — normalised convolution."""
+    """shape_ftp.py:1139-1147 — normalised convolution (sigma <= 0: the input, :1140)."""
+    if sigma <= 0:
+        return z
     z0 = z.copy().astype(np.float32)
     z0[~mask] = 0.0
     num = cv2.GaussianBlur(z0, (0, 0), sigma)
@@ -343,6 +345,25 @@ def internal_holes(container, known, P):
     cc = cv2.boxFilter(container.astype(np.float32), ddepth=-1, ksize=(k, k), normalize=False)
     dist = cv2.distanceTransform(container.astype(np.uint8) * 255, cv2.DIST_L2, 3)
     return holes & (ck / (cc + 1e-6) >= P.hole_frac) & (dist >= P.hole_min_dist)
+
+
+def fill_internal_holes(hm, rel, P):
+    """shape_ftp.py:1770-1801 — hole candidates inside the reliable mask, Telea fill (inpaint_only_mask :1178-1203).
+    Returns (height_rel_filled, hole_candidates, output_reliable)."""
+    h, w = hm.shape
+    known = rel & np.isfinite(hm)
+    filled = np.full((h, w), np.nan, np.float32)
+    filled[known] = hm[known]
+    holes = internal_holes(rel, known, P)
+    if holes.any():
+        tmp = filled.copy()
+        tmp[rel & ~known] = float(np.nanmedian(tmp[known])) if known.any() else 0.0
+        kn = rel & ~holes & np.isfinite(tmp)
+        zin = np.full_like(tmp, float(np.nanmedian(tmp[kn])) if kn.any() else 0.0)
+        zin[kn] = tmp[kn]
+        zo = cv2.inpaint(zin, holes.astype(np.uint8) * 255, float(P.inpaint_radius), cv2.INPAINT_TELEA)
+        filled[holes] = zo[holes]
+    return filled, holes, rel & np.isfinite(filled)
 
 
 def frontier(height, roi, rel, band, inside, outside):
@@ -550,19 +571,7 @@ def ftp_pair(ref_gray, def_gray, geom, P=None, ref=None, keep=False):
         if core.any() and float(np.median(hm[core])) > 0:
             hm = hm * -1.0
             flipped = True
-    known = rel & np.isfinite(hm)
-    filled = np.full((h, w), np.nan, np.float32)
-    filled[known] = hm[known]
-    holes = internal_holes(rel, known, P)
-    if holes.any():                                    # shape_ftp.py:1787-1799 (never taken: see DESIGN.md)
-        tmp = filled.copy()
-        tmp[rel & ~known] = float(np.nanmedian(tmp[known])) if known.any() else 0.0
-        kn = rel & ~holes & np.isfinite(tmp)
-        zin = np.full_like(tmp, float(np.nanmedian(tmp[kn])) if kn.any() else 0.0)
-        zin[kn] = tmp[kn]
-        zo = cv2.inpaint(zin, holes.astype(np.uint8) * 255, float(P.inpaint_radius), cv2.INPAINT_TELEA)
-        filled[holes] = zo[holes]
-    out_rel = rel & np.isfinite(filled)
+    filled, holes, out_rel = fill_internal_holes(hm, rel, P)   # holes: empty whenever smooth_sigma > 0
     filled = frontier(filled, roi, out_rel, P.frontier_band, True, False)
     hf_ = np.full((h, w), np.nan, np.float32)
     hf_[roi] = 0.0

@@ -20,22 +20,36 @@ def sha(m):
     return hashlib.sha1(np.packbits(np.asarray(m, bool)).tobytes()).hexdigest()
 
 
-def frames(case):
+def frames(case, sc=None):
     if case.startswith("demo_"):
-        return (cv2.imread(os.path.join(G, "FINAL_reference.jpg")),
-                cv2.imread(os.path.join(G, "FINAL_" + case[5:] + ".jpg")))
+        name = case[5:] + ("_deformed" if len(case) == 6 else "")
+        return (cv2.imread(os.path.join(G, "FINAL_reference.jpg")), cv2.imread(os.path.join(G, "FINAL_" + name + ".jpg")))
     # the golden run stored synthetic frames as PNG (lossless) -> identical bytes
+    if sc is not None and "gen" in sc[case]:
+        return S.make_frame(0, reference=True), S.make_frame(**sc[case]["gen"])
     return S.make_frame(0, reference=True), S.make_frame(int(case.split("_")[1]))
 
 
 CASES = ["demo_TEMP_DEMO", "demo_ROUND_METAL", "syn_3", "syn_15"]
+# round 2 (tools/make_golden_r2.py): phase amplitude up to 3 pi (wrap counts != 0), the three remaining demo pairs
+FTP_CASES = CASES + ["syn3pi_21", "syn3pi_56", "demo_E", "demo_F", "demo_P"]
+# ... a hot temperature field (blend band, isotonic clip), tilted stripes (warpAffine path of the oriented blur)
+TEMP_CASES = CASES + ["synhot_9", "synhot_12", "syntilt_5", "syntilt_6", "demo_E", "demo_F", "demo_P"]
 
 
-@pytest.mark.parametrize("case", CASES)
+def test_golden_environment(golden):
+    """The goldens and the oracle's bit-exact claims rest on NumPy >= 2 scalar semantics (float32 percentile virtual
+    index, float32 * python-float products): pin that here."""
+    sc, _ = golden
+    assert int(np.__version__.split(".")[0]) >= 2
+    assert int(sc["_versions"]["numpy"].split(".")[0]) >= 2
+
+
+@pytest.mark.parametrize("case", FTP_CASES)
 def test_ftp_oracle_matches_reference(case, golden):
     sc, arr = golden
     g = sc[case]["ftp"]
-    ref, de = frames(case)
+    ref, de = frames(case, sc)
     P = F.FtpParams(apply_global_shift=sc[case]["aligned"], use_ecc=sc[case]["aligned"])
     r = F.shape_pair_from_frames(ref, de, P)
     fr = F.force_readings(r)
@@ -55,11 +69,11 @@ def test_ftp_oracle_matches_reference(case, golden):
         assert fr[k] == pytest.approx(g[k], rel=2e-6), k
 
 
-@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("case", TEMP_CASES)
 def test_temperature_oracle_matches_reference(case, golden):
     sc, arr = golden
     g = sc[case]["temperature"]
-    _, de = frames(case)
+    _, de = frames(case, sc)
     r = T.temperature_frame(de)
     y0, y1, x0, x1 = r["bbox"]
     for k in ["roi", "roi_eff", "sat", "dark", "light", "color_support", "color_ok"]:
@@ -87,3 +101,36 @@ def test_stored_summary_anchor(name, golden):
     assert g["temperature"]["valid_pixels"] == st["temperature"]["valid_pixels"]
     assert g["ftp"]["force_N"] == pytest.approx(st["force"]["force_N"], rel=2e-3)
     assert g["ftp"]["mm_per_px"] == pytest.approx(st["force"]["scale_mm_per_px"], rel=1e-6)
+
+
+def test_lab8_integer_recipe_matches_cv2_on_all_colours():
+    """T7: the integer BGR->Lab recipe and the two tables shipped in calibration/lab_lut.json (uploaded to the GPU at plan
+    creation) equal cv2.cvtColor(BGR2LAB) on all 2^24 colours (temperature_sensor.py:284)."""
+    import _native as N
+    gam, cb = (np.asarray(t, np.int64) for t in N.lab_tables())
+    C = np.array([[1777, 1541, 778], [871, 2929, 296], [73, 448, 3575]], np.int64)
+    g_, r_ = np.meshgrid(np.arange(256, dtype=np.uint8), np.arange(256, dtype=np.uint8), indexing="ij")
+    bad = 0
+    for b0 in range(256):
+        img = np.stack([np.full_like(g_, b0), g_, r_], -1)
+        B, Gc, R = [gam[img[..., c]] for c in range(3)]
+        f = [cb[(R * C[r, 0] + Gc * C[r, 1] + B * C[r, 2] + 2048) >> 12] for r in range(3)]
+        L = (296 * f[1] - 1336934 + 16384) >> 15
+        a = (500 * (f[0] - f[1]) + 128 * 32768 + 16384) >> 15
+        b = (200 * (f[1] - f[2]) + 128 * 32768 + 16384) >> 15
+        lab = np.stack([np.clip(v, 0, 255) for v in (L, a, b)], -1).astype(np.uint8)
+        bad += int((lab != cv2.cvtColor(img, cv2.COLOR_BGR2LAB)).sum())
+    assert bad == 0
+
+
+def test_unwrap_oracle_wraps_and_is_path_independent_without_residues(golden):
+    """F10 where it does something: on the 3 pi case the heap flood's wrap counts reach |k| >= 1, and (no residues)
+    the field equals wrapped + 2 pi k for the k of ANY spanning order -- here a plain raster BFS."""
+    sc, _ = golden
+    ref, de = frames("syn3pi_21", sc)
+    r = F.shape_pair_from_frames(ref, de, F.FtpParams(apply_global_shift=False, use_ecc=False), keep=True)
+    rel = r["reliable"]
+    u = F.unwrap_quality_guided(r["wrapped"], rel, r["quality"])
+    k = np.rint((u - r["wrapped"]) / (2 * np.pi))
+    assert np.nanmax(np.abs(k[rel])) >= 1
+    assert np.nanmax(np.abs(u[rel] - (r["wrapped"][rel] + 2 * np.pi * k[rel]))) < 1e-5

@@ -17,7 +17,8 @@ MAX_TERMS, MAX_ISO = 35, 64
 
 ST_EMPTY_ROI, ST_NO_PEAK, ST_SATURATED, ST_ROTATED_CARRIER = 0x1, 0x2, 0x4, 0x8
 ST_RESIDUES, ST_FEW_RELIABLE, ST_SIGN_FLIPPED, ST_CONTACT_P95, ST_BG_FALLBACK = 0x10, 0x20, 0x40, 0x80, 0x100
-ST_SAT_UNFILLED, ST_SPLIT_RELIABLE, ST_TELEA_OVERFLOW = 0x200, 0x400, 0x8000
+ST_SAT_UNFILLED, ST_SPLIT_RELIABLE, ST_HOLES_FILLED, ST_TELEA_OVERFLOW = 0x200, 0x400, 0x800, 0x8000
+ST_RERUN_ALONE = ST_SAT_UNFILLED
 
 
 class PolyModel(C.Structure):
@@ -99,7 +100,10 @@ class FtpParams(C.Structure):
                 ("use_negated_height", C.c_int32),
                 ("blob_min_peak_mm", C.c_double), ("blob_rel_frac", C.c_double),
                 ("height_model", CurveModel), ("force_model", CurveModel),
-                ("grating_pitch_mm", C.c_double), ("depth_eps_mm", C.c_double)]
+                ("grating_pitch_mm", C.c_double), ("depth_eps_mm", C.c_double),
+                ("fill_internal_holes", C.c_int32), ("hole_neighborhood", C.c_int32),
+                ("hole_known_frac", C.c_float), ("hole_min_dist", C.c_float),
+                ("hole_inpaint_radius", C.c_int32), ("pad2_", C.c_int32)]
 
 
 class FtpRecord(C.Structure):
@@ -118,7 +122,7 @@ assert FTP_RECORD_DTYPE.itemsize == C.sizeof(FtpRecord) == 104
 
 class FtpOutputs(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("height_mm", "reliable", "output_reliable", "contact_dilated",
-                                          "contact_kept", "records")]
+                                          "contact_kept", "records", "hole_candidates")]
 
 
 class FtpReferenceInfo(C.Structure):
@@ -180,6 +184,12 @@ def lib():
         L.vistaf_ftp_batch_begin.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
         L.vistaf_ftp_batch_finish.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(FtpOutputs), C.c_void_p, C.c_size_t,
                                               C.c_void_p]
+        L.vistaf_ftp_fill_holes.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_size_t, C.c_void_p]
+        L.vistaf_ftp_unwrap.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                        C.c_void_p, C.c_size_t, C.c_void_p]
+        L.vistaf_ftp_set_debug.argtypes = [C.c_void_p, C.c_int]
+        L.vistaf_graph_replays.restype = C.c_longlong
         L.vistaf_ftp_masks.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.vistaf_ftp_workspace_plane.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.POINTER(C.c_size_t),
                                                  C.POINTER(C.c_size_t)]

@@ -45,7 +45,11 @@ struct BlurWindow {
   int x0, x1, y0, y1;
   int ry0, ry1;
   const float* fill; const float* rowfill; size_t stride;   // per-frame values: *(float*)((char*)fill + b * stride)
+  const unsigned int* gate; unsigned int gate_mask;         // optional: frame b runs only if (gate[b] (byte stride) & mask) != 0
 };
+__device__ __forceinline__ bool blur_gated_off(const BlurWindow& win, int b) {
+  return win.gate && !(*(const unsigned int*)((const char*)win.gate + (size_t)b * win.stride) & win.gate_mask);
+}
 __device__ __forceinline__ float blur_frame_const(const float* p, size_t stride, int b) {
   return p ? *(const float*)((const char*)p + (size_t)b * stride) : 0.f;
 }
@@ -73,6 +77,7 @@ __global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* 
   __shared__ float wk[BLUR_MAXK];
   const int b = blockIdx.z, y = blockIdx.y, x0 = blockIdx.x * BLUR_ROW_SEG;
   if (y < win.ry0 || y >= win.ry1 || x0 >= win.x1 + 32 || x0 + BLUR_ROW_SEG <= win.x0 - 32) return;
+  if (blur_gated_off(win, b)) return;
   const int rad = g.ksize >> 1;
   const int need = BLUR_ROW_SEG + g.kpad + 8;
   // inputs of outputs nobody reads (farther than the kernel radius from the window grown by one column block) stay 0
@@ -121,11 +126,11 @@ __global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int 
   __shared__ float wk[BLUR_MAXK];
   const int TY = 8 * blockDim.y;
   const int b = blockIdx.z, x = blockIdx.x * 32 + threadIdx.x, y0 = blockIdx.y * TY;
+  if (blur_gated_off(win, b)) return;
   if ((int)blockIdx.x * 32 >= win.x1 || (int)blockIdx.x * 32 + 32 <= win.x0 || y0 >= win.y1 || y0 + TY <= win.y0) {
     Store sto = st;                // block outside the window: nothing computed
     if (x < w) {
       const int r0o = threadIdx.y * 8;
-#pragma unroll
       const float fv = blur_frame_const(win.fill, win.stride, b);
 #pragma unroll
       for (int j = 0; j < 8; j++) { const int y = y0 + r0o + j; if (y < h) blur_outside(sto, b, y, x, fv, 0); }
@@ -182,7 +187,7 @@ static int gauss_blur(Load ld, Store st, float* tmp, int h, int w, int batch, co
                       const GaussKernel& gy, cudaStream_t stream, const BlurWindow* window = nullptr) {
   const long long plane = (long long)h * w;
   const int tyt = gy.ksize > 100 ? 32 : 16;
-  BlurWindow win = window ? *window : BlurWindow{0, w, 0, h, 0, h, nullptr, nullptr, 0};
+  BlurWindow win = window ? *window : BlurWindow{0, w, 0, h, 0, h, nullptr, nullptr, 0, nullptr, 0u};
   if (window && !window->rowfill) {           // rows the active column blocks (aligned to their own grid) read
     win.ry0 = win.y0 - (gy.ksize >> 1) - 8 * tyt;
     win.ry1 = win.y1 + (gy.ksize >> 1) + 8 * tyt;

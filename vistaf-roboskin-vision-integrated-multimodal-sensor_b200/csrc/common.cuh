@@ -7,8 +7,7 @@
 
 #define VISTAF_PI 3.14159265358979323846
 
-extern char g_vistaf_err[512];
-int vistaf_set_err(const char* what, cudaError_t e, const char* file, int line);
+int vistaf_set_err(const char* what, cudaError_t e, const char* file, int line);   // message kept per calling thread
 
 #define CK(call)                                                              \
   do {                                                                        \
@@ -18,9 +17,33 @@ int vistaf_set_err(const char* what, cudaError_t e, const char* file, int line);
 #define CKL() CK(cudaGetLastError())
 
 // launch accounting + stage timers (api.cu).  Every kernel launch in the library is written `VL(), k<<<...>>>(...)`.
-extern long long g_vistaf_launches;
-#define VL() ((void)++g_vistaf_launches)
+#include <atomic>
+#include <functional>
+extern std::atomic<long long> g_vistaf_launches;
+#define VL() ((void)g_vistaf_launches.fetch_add(1, std::memory_order_relaxed))
 void vistaf_stage_mark(const char* name, cudaStream_t st);      // "" closes the previous stage without opening one
+bool vistaf_profiling(void);
+
+// CUDA-graph replay cache (api.cu): v[0] = entry-point tag, v[1] = plan handle, the rest = the call's arguments.
+struct VistafGraphKey {
+  unsigned long long v[16];
+  bool operator<(const VistafGraphKey& o) const {
+    for (int i = 0; i < 16; i++) if (v[i] != o.v[i]) return v[i] < o.v[i];
+    return false;
+  }
+};
+template <class... A>
+static inline VistafGraphKey vistaf_graph_key(int tag, const void* plan, A... a) {
+  static_assert(sizeof...(A) <= 14, "too many key fields");
+  VistafGraphKey k;
+  for (int i = 0; i < 16; i++) k.v[i] = 0;
+  k.v[0] = (unsigned long long)tag; k.v[1] = (unsigned long long)(uintptr_t)plan;
+  const unsigned long long t[] = {(unsigned long long)a..., 0ull};
+  for (size_t i = 0; i < sizeof...(A); i++) k.v[2 + i] = t[i];
+  return k;
+}
+int vistaf_graph_run(const VistafGraphKey& key, cudaStream_t st, const std::function<int(cudaStream_t)>& body);
+void vistaf_graph_drop(const void* plan);                       // forget every graph recorded for a plan (plan_destroy)
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 static inline size_t align256(size_t x) { return (x + 255) & ~size_t(255); }

@@ -46,6 +46,8 @@ struct FtpScal {                  // per-frame scalars in the workspace
   ull seed_key;                   // (quality key << 32) | ~index
   ull best_cc;                    // (area << 32) | ~root
   unsigned int n_rel, n_bg, n_contact, n_contact_d, n_bad, n_kept, residues, uf_bad, status;
+  unsigned int n_holes, n_cand, n_outrel;      // F14: reliable pixels without a height, hole candidates, output_reliable pixels
+  float hole_med, hole_fill;
   int seed_root, seed_k;
   int bg_is_rel, flip, detrend1;
   unsigned int gmax_bits;         // blob filter: max depth (float bits, depth >= 0)
@@ -55,7 +57,7 @@ struct FtpScal {                  // per-frame scalars in the workspace
 
 struct FtpWs {                    // byte offsets into the chunk workspace
   size_t img, grad, bad0, bad, tmp, I, Iw, R, Pw, wrapped, qprod, quality, m1, m2, reliable, uf, area, unw,
-      contact, contact_d, hnum, hm, dist_in, dist_out, dtmp, snum, sm, peak, scal, sel, telea, total;
+      contact, contact_d, hnum, hm, dist_in, dist_out, dtmp, snum, sm, peak, scal, sel, telea, active, total;
 };
 
 }  // namespace vftp
@@ -71,14 +73,10 @@ struct VistafFtpPlan {
   bool have_ref;
   float2* cref;                   // reference-frame field (shape_ftp.py:1632-1639), device [h][w]
   float* amp_ref;
-  float peak_xf, peak_yf;
-  int pxi, pyi;
-  double kx, ky;
   float2 *rampx, *rampy;          // fractional demodulation ramps over padded coordinates, device [N]
   float* hann;                    // device [np]
   int* kxs; int* kys;             // device [np]: unsigned frequency index of every patch column / row
-  int roi_count;
-  int ref_bad;
+  int debug_flags;                // bit 0: run the sequential flood unwrap on every frame (parity tests)
   ull* peak_keys;                 // device [32]: top-n spectrum peaks of the reference frame
   void* peak_result;              // device PeakResult
 };
@@ -396,7 +394,11 @@ __global__ void k_ftp_pad(const float* __restrict__ Iw, const FtpScal* sc, float
 // ------------------------------------------------------------------ F6: carrier peak (shape_ftp.py:420-483) on the device
 // find_top_peaks: the n largest |F| outside the DC box of the fftshift-ed spectrum, ordered by (magnitude desc, raster
 // index asc).  One sweep per peak: round r takes the largest key strictly below the key of round r-1.
-struct PeakResult { float pxf, pyf; int bx, by; float mag; int ok; };
+struct PeakResult {             // device-resident carrier of the reference frame (no host round trip inside a step)
+  float pxf, pyf; int bx, by; float mag; int ok;
+  int pxi, pyi;                 // nearest integer bin (patch centre)
+  double kx, ky;                // signed carrier frequency in bins
+};
 __global__ void __launch_bounds__(256) k_ftp_peak_round(const float2* __restrict__ F, ull* __restrict__ keys, int round, int N,
                                                         int dc) {
   const ull limit = round ? keys[round - 1] : ~0ull;
@@ -458,6 +460,34 @@ __global__ void k_ftp_peak_choose(const float2* __restrict__ F, const ull* __res
   *out = r;
 }
 
+// Patch frequencies and fractional demodulation ramps from the refined peak (shape_ftp.py:929-961), on the device.
+__global__ void k_ftp_carrier_setup(PeakResult* pr, int* __restrict__ kxs, int* __restrict__ kys, float2* __restrict__ rampx,
+                                    float2* __restrict__ rampy, int N, int np) {
+  const int bw = np / 2, c = N / 2;
+  const float pxf = pr->pxf, pyf = pr->pyf;
+  const int pxi = __double2int_rn((double)pxf), pyi = __double2int_rn((double)pyf);
+  const bool fits = pr->ok && pxi - bw >= 0 && pxi + bw + 1 <= N && pyi - bw >= 0 && pyi + bw + 1 <= N;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) {
+    pr->pxi = pxi; pr->pyi = pyi;
+    pr->kx = (double)pxf - (double)c; pr->ky = (double)pyf - (double)c;
+    if (!fits) pr->ok = 0;        // carrier patch touches the spectrum border (unsupported): frames report NO_PEAK
+  }
+  if (i < np) {
+    kxs[i] = fits ? ((pxi - bw + i - c) % N + N) % N : 0;       // fftshift-ed column -> unsigned frequency index
+    kys[i] = fits ? ((pyi - bw + i - c) % N + N) % N : 0;
+  }
+  if (i < N) {
+    const double dpx = (double)pxf - (double)pxi, dpy = (double)pyf - (double)pyi;
+    const bool on = fabs(dpx) > 1e-6 || fabs(dpy) > 1e-6;
+    const double t = (double)i / (double)N;
+    const double ax = on ? __dmul_rn(__dmul_rn(-2.0 * VISTAF_PI, dpx), t) : 0.0;
+    const double ay = on ? __dmul_rn(__dmul_rn(-2.0 * VISTAF_PI, dpy), t) : 0.0;
+    rampx[i] = make_float2((float)cos(ax), (float)sin(ax));
+    rampy[i] = make_float2((float)cos(ay), (float)sin(ay));
+  }
+}
+
 // ------------------------------------------------------------------ F8: reliable mask (shape_ftp.py:739-776)
 struct RelRawLoad {             // roi & (q >= thr) & finite
   const float* q; const uint8_t* roi; const FtpScal* sc; long long plane; int w;
@@ -501,8 +531,9 @@ __global__ void k_ftp_seed(const float* __restrict__ q, const uint8_t* __restric
 struct PhaseEdge {
   const float* wr; long long plane;
   __device__ int operator()(int b, int p, int n) const {
+    // np.angle(np.exp(1j * d)) in complex64: sin(float32(pi)) < 0, so a step of exactly +-float32(pi) wraps as well
     const float d = __fsub_rn(wr[(long long)b * plane + n], wr[(long long)b * plane + p]);
-    return d > 3.14159274f ? -1 : (d < -3.14159274f ? 1 : 0);
+    return d >= 3.14159274f ? -1 : (d <= -3.14159274f ? 1 : 0);
   }
 };
 __global__ void k_ftp_residues(const float* __restrict__ wr, const uint8_t* __restrict__ rel, FtpScal* sc, int h, int w) {
@@ -528,6 +559,100 @@ __global__ void k_ftp_seed_root(const ull* __restrict__ uf, FtpScal* sc, int npi
   const ull v = uf[(size_t)blockIdx.x * npix + idx];
   s.seed_root = (int)uf_parent(v);
   s.seed_k = uf_delta(v);
+}
+// F10 on frames whose wrapped field is NOT path independent (phase residues inside the reliable mask, or a loop around
+// a hole of the mask that does not close): the reference's quality-guided flood itself (shape_ftp.py:1043-1080), run
+// sequentially by one thread per flagged frame.  The Python heap holds tuples (-q, y, x, py, px): a pixel is fixed at
+// its first pop, which happens when it is the best (largest q, then smallest raster index) pixel on the frontier, and
+// the tuple popped first is the one pushed by its lexicographically smallest (py, px) already-fixed neighbour.  So one
+// heap entry per frontier pixel, keyed (~key(q) << 32 | index), and a parent scan in (py, px) order reproduce the
+// flood exactly.  The wrap count of a pixel is its parent's plus the wrap of the step (PhaseEdge), the field is
+// written in the union-find format k_ftp_unwrap_apply reads: (root = seed pixel, delta = k).  The binary heap lives in
+// the frame's union-find plane (free at this point), its top UH_TOP entries in shared memory.  Seconds per flagged
+// frame -- the reference spends 32-42 s here on every frame.
+#define UH_TOP 4096
+__global__ void __launch_bounds__(32) k_ftp_unwrap_heap(const float* __restrict__ wr_all, const float* __restrict__ q_all,
+                                                         const uint8_t* __restrict__ rel_all, FtpScal* sc, ull* __restrict__ uf_all,
+                                                         unsigned int* __restrict__ aux_all, int h, int w, int force) {
+  __shared__ ull hs[UH_TOP];
+  const int b = blockIdx.x, lane = threadIdx.x, npix = h * w;
+  FtpScal& s = sc[b];
+  if (!(force || s.residues || s.uf_bad) || s.seed_key == 0) return;
+  const float* wr = wr_all + (size_t)b * npix;
+  const float* q = q_all + (size_t)b * npix;
+  const uint8_t* rel = rel_all + (size_t)b * npix;
+  ull* H = uf_all + (size_t)b * npix;
+  unsigned int* A = aux_all + (size_t)b * npix;        // (k << 2) | state: 0 untouched, 1 on the frontier, 2 fixed
+  for (int i = lane; i < npix; i += 32) A[i] = 0u;
+  __syncwarp();
+  const unsigned int seed = 0xffffffffu - (unsigned int)(s.seed_key & 0xffffffffull);
+  if (lane == 0) {
+    int n = 0;
+    auto hget = [&](int i) -> ull { return i < UH_TOP ? hs[i] : H[i]; };
+    auto hset = [&](int i, ull v) { if (i < UH_TOP) hs[i] = v; else H[i] = v; };
+    auto push = [&](ull key) {
+      int i = n++;
+      while (i > 0) {
+        const int p = (i - 1) >> 1;
+        const ull pv = hget(p);
+        if (pv <= key) break;
+        hset(i, pv);
+        i = p;
+      }
+      hset(i, key);
+    };
+    auto pop = [&]() -> ull {
+      const ull top = hs[0];
+      const ull last = hget(--n);
+      int i = 0;
+      for (;;) {
+        int c = 2 * i + 1;
+        if (c >= n) break;
+        ull cv = hget(c);
+        if (c + 1 < n) { const ull c2 = hget(c + 1); if (c2 < cv) { cv = c2; c++; } }
+        if (cv >= last) break;
+        hset(i, cv);
+        i = c;
+      }
+      if (n) hset(i, last);
+      return top;
+    };
+    auto visit = [&](int y, int x) {                     // push the untouched reliable neighbours of a fixed pixel
+      for (int dy = -1; dy <= 1; dy++)
+        for (int dx = -1; dx <= 1; dx++) {
+          const int ny = y + dy, nx = x + dx;
+          if ((dy | dx) == 0 || ny < 0 || ny >= h || nx < 0 || nx >= w) continue;
+          const int j = ny * w + nx;
+          if (!rel[j] || (A[j] & 3u)) continue;
+          A[j] = 1u;
+          push(((ull)(~f2key(__fadd_rn(q[j], 0.0f))) << 32) | (ull)(unsigned int)j);    // -0.0 and 0.0 compare equal in Python
+        }
+    };
+    PhaseEdge e{wr, 0};
+    A[seed] = 2u;
+    visit((int)(seed / (unsigned)w), (int)(seed % (unsigned)w));
+    while (n > 0) {
+      const int i = (int)(unsigned int)(pop() & 0xffffffffull);
+      const int y = i / w, x = i - y * w;
+      int kp = 0, p = -1;
+      for (int dy = -1; dy <= 1 && p < 0; dy++)          // first fixed neighbour in (py, px) order
+        for (int dx = -1; dx <= 1; dx++) {
+          const int ny = y + dy, nx = x + dx;
+          if ((dy | dx) == 0 || ny < 0 || ny >= h || nx < 0 || nx >= w) continue;
+          const unsigned int a = A[ny * w + nx];
+          if ((a & 3u) == 2u) { p = ny * w + nx; kp = (int)a >> 2; break; }
+        }
+      const int k = kp + e(0, p, i);
+      A[i] = ((unsigned int)k << 2) | 2u;
+      visit(y, x);
+    }
+  }
+  __syncwarp();
+  for (int i = lane; i < npix; i += 32) {
+    ull v = uf_pack(UF_BG, 0);
+    if (rel[i]) v = (A[i] & 3u) == 2u ? uf_pack(seed, (int)A[i] >> 2) : uf_pack((unsigned int)i, 0);   // unreached: own root
+    H[i] = v;
+  }
 }
 __global__ void k_ftp_unwrap_apply(const ull* __restrict__ uf, const float* __restrict__ wr, FtpScal* sc,
                                    float* __restrict__ unw, int npix) {
@@ -901,6 +1026,117 @@ struct CoreVal {                // hm over reliable & hm <= core_thr
   }
 };
 
+// ------------------------------------------------------------------ F14: internal holes of the reliable mask (shape_ftp.py:1153-1203, 1776-1801)
+// holes = reliable & ~isfinite(height).  A hole pixel is a candidate when >= frac_thr of the reliable pixels in its k x k
+// box (cv2.boxFilter, BORDER_REFLECT_101, un-normalised) have a height and it lies >= min_dist (3-4 chamfer) inside the
+// reliable mask.  Candidates are Telea-filled (r = 5) from tmp = height with the other holes set to the median of the
+// known heights, on a canvas that is the median of the non-candidate reliable pixels elsewhere (inpaint_only_mask).
+// Every kernel returns at once for frames without holes (all frames of the shipped configuration: with the reliable
+// smoothing on, masked_gaussian_smooth leaves no NaN inside the mask), so the stage costs a few empty launches.
+__global__ void k_holes_count(const float* __restrict__ hm, const uint8_t* __restrict__ rel, FtpScal* sc, int npix) {
+  const int b = blockIdx.y;
+  int c = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+    const size_t o = (size_t)b * npix + i;
+    c += rel[o] && !(fabsf(hm[o]) <= 3.4e38f);
+  }
+  c = warp_sum(c);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&sc[b].n_holes, (unsigned)c);
+}
+struct HoleGate {               // frames with holes (chamfer / union-find `active` convention: < 0 = skip)
+  const FtpScal* sc;
+  __device__ bool on(int b) const { return sc[b].n_holes != 0; }
+};
+__global__ void k_holes_active(const FtpScal* sc, int* active, int which) {
+  const FtpScal& s = sc[blockIdx.x];
+  active[blockIdx.x] = (which == 0 ? s.n_holes : s.n_cand) ? (int)blockIdx.x : -1;
+}
+__global__ void k_holes_candidates(const float* __restrict__ hm, const uint8_t* __restrict__ rel, const float* __restrict__ dist,
+                                   FtpScal* sc, uint8_t* __restrict__ cand, int h, int w, int k, float frac_thr, float min_dist) {
+  const int b = blockIdx.z, y = blockIdx.y, x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (sc[b].n_holes == 0) return;
+  int c = 0;
+  if (x < w) {
+    const size_t o = (size_t)b * h * w, i = (size_t)y * w + x;
+    if (rel[o + i] && !(fabsf(hm[o + i]) <= 3.4e38f) && dist[o + i] >= min_dist) {
+      float ck = 0.f, cc = 0.f;
+      const int r = k / 2;
+      for (int dy = -r; dy <= r; dy++) {
+        const size_t row = (size_t)reflect101(y + dy, h) * w;
+        for (int dx = -r; dx <= r; dx++) {
+          const size_t j = o + row + reflect101(x + dx, w);
+          if (rel[j]) { cc += 1.f; if (fabsf(hm[j]) <= 3.4e38f) ck += 1.f; }
+        }
+      }
+      c = __fdiv_rn(ck, __fadd_rn(cc, 1e-6f)) >= frac_thr;
+    }
+    cand[o + i] = (uint8_t)c;
+  }
+  c = warp_sum(c);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&sc[b].n_cand, (unsigned)c);
+}
+struct HoleKnownVal {           // heights of the known pixels (median #1), frames with candidates only
+  const float* hm; const uint8_t* rel; const FtpScal* sc; long long plane;
+  __device__ long long limit(int b) const { return sc[b].n_cand ? plane : 0; }
+  __device__ bool operator()(int b, long long i, float& v) const {
+    if (sc[b].n_cand == 0 || !rel[(long long)b * plane + i]) return false;
+    v = hm[(long long)b * plane + i];
+    return fabsf(v) <= 3.4e38f;
+  }
+};
+struct HoleTmpVal {             // tmp over reliable & ~candidate: known heights, other holes = hole_med (median #2)
+  const float* hm; const uint8_t* rel; const uint8_t* cand; const FtpScal* sc; long long plane;
+  __device__ long long limit(int b) const { return sc[b].n_cand ? plane : 0; }
+  __device__ bool operator()(int b, long long i, float& v) const {
+    const long long o = (long long)b * plane + i;
+    if (sc[b].n_cand == 0 || !rel[o] || cand[o]) return false;
+    v = hm[o];
+    if (!(fabsf(v) <= 3.4e38f)) v = sc[b].hole_med;
+    return true;
+  }
+};
+struct HoleGrab { FtpScal* sc; int which;
+  __device__ void operator()(int b, float r, unsigned int cnt) const {
+    if (which == 0) sc[b].hole_med = (cnt && r == r) ? r : 0.f; else sc[b].hole_fill = (cnt && r == r) ? r : 0.f;
+  }
+};
+__global__ void k_holes_canvas(const float* __restrict__ hm, const uint8_t* __restrict__ rel, const uint8_t* __restrict__ cand,
+                               const FtpScal* sc, float* __restrict__ zin, int npix) {
+  const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (sc[b].n_cand == 0 || i >= npix) return;
+  const size_t o = (size_t)b * npix + i;
+  float v = sc[b].hole_fill;
+  if (rel[o] && !cand[o]) { v = hm[o]; if (!(fabsf(v) <= 3.4e38f)) v = sc[b].hole_med; }
+  zin[o] = v;
+}
+struct HoleMask {
+  const uint8_t* cand; const FtpScal* sc; long long plane; int w;
+  __device__ bool operator()(int b, int y, int x) const { return sc[b].n_cand != 0 && cand[(long long)b * plane + (long long)y * w + x] != 0; }
+};
+// height[cand] = filled; output_reliable = reliable & isfinite(height)
+__global__ void k_holes_apply(float* __restrict__ hm, const uint8_t* __restrict__ rel, const uint8_t* __restrict__ cand,
+                              const float* __restrict__ zin, FtpScal* sc, uint8_t* __restrict__ outrel, int npix) {
+  const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  int c = 0;
+  if (i < npix) {
+    const size_t o = (size_t)b * npix + i;
+    if (sc[b].n_cand && cand[o]) hm[o] = zin[o];
+    c = rel[o] && fabsf(hm[o]) <= 3.4e38f;
+    outrel[o] = (uint8_t)c;
+  }
+  c = warp_sum(c);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&sc[b].n_outrel, (unsigned)c);
+  if (i == 0 && sc[b].n_cand) atomicOr(&sc[b].status, VISTAF_ST_HOLES_FILLED);
+}
+// sigma <= 0: masked_gaussian_smooth returns its input (shape_ftp.py:1140): hm = unw - fit - median on reliable, NaN elsewhere
+__global__ void k_ftp_hm_plain(const float* __restrict__ z, const uint8_t* __restrict__ rel, const FtpScal* sc, FitGeom g,
+                               float* __restrict__ hm, int npix) {
+  const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npix) return;
+  const size_t o = (size_t)b * npix + i;
+  hm[o] = rel[o] ? hm_at(z, sc[b], g, (long long)o, i) : FNAN;
+}
+
 // ------------------------------------------------------------------ F15: frontier, assembly (shape_ftp.py:1287-1330, 1803-1841)
 struct NotMaskZero {            // chamfer zero set = pixels outside the mask
   const uint8_t* m; long long plane; int w;
@@ -1058,11 +1294,12 @@ __global__ void __launch_bounds__(256) k_depth_reduce(const float* __restrict__ 
   }
 }
 
-__global__ void k_ftp_records(const FtpScal* sc, VistafFtpRecord* rec, int n, int w, double period_px, double pitch_mm,
+__global__ void k_ftp_records(const FtpScal* sc, VistafFtpRecord* rec, int n, int w, const PeakResult* pr, int N, double pitch_mm,
                               VistafCurveModel force_model) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const FtpScal& s = sc[i];
+  const double period_px = fabs(pr->kx) > 1e-9 ? (double)N / fabs(pr->kx) : 0.0;
   VistafFtpRecord r;
   memset(&r, 0, sizeof(r));
   const double mm_per_px = pitch_mm / period_px;
@@ -1076,7 +1313,7 @@ __global__ void k_ftp_records(const FtpScal* sc, VistafFtpRecord* rec, int n, in
   }
   r.force_N = curve_eval(force_model, r.volume_cm3);
   r.amp_thr = s.amp_thr; r.contact_thr = s.contact_thr; r.bg_median = s.bg_med; r.core_median = s.core_med;
-  r.reliable_px = (int)s.n_rel; r.output_reliable_px = (int)s.n_rel; r.contact_dilated_px = (int)s.n_contact_d;
+  r.reliable_px = (int)s.n_rel; r.output_reliable_px = (int)s.n_outrel; r.contact_dilated_px = (int)s.n_contact_d;
   r.contact_kept_px = (int)s.n_kept; r.bad_px = (int)s.n_bad; r.residues = (int)s.residues;
   if (s.seed_key) {
     const unsigned int idx = 0xffffffffu - (unsigned int)(s.seed_key & 0xffffffffull);
@@ -1084,6 +1321,7 @@ __global__ void k_ftp_records(const FtpScal* sc, VistafFtpRecord* rec, int n, in
   } else { r.seed_x = r.seed_y = -1; }
   unsigned int st = s.status;
   if (s.n_rel == 0) st |= VISTAF_ST_EMPTY_ROI;
+  if (!pr->ok) st |= VISTAF_ST_NO_PEAK;
   if (s.residues || s.uf_bad) st |= VISTAF_ST_RESIDUES;
   if (s.flip) st |= VISTAF_ST_SIGN_FLIPPED;
   r.status = (int)st;
@@ -1113,6 +1351,7 @@ static void ftp_layout(const VistafFtpPlan* p, int chunk, FtpWs& L) {
   L.dtmp = take(c * S * 4); L.snum = take(c * S * 4); L.sm = take(c * S * 4); L.peak = take(c * S * 4);
   L.scal = take(c * sizeof(FtpScal)); L.sel = take(sel_ws_bytes((int)c));
   L.telea = take(telea_ws_bytes(p->h, p->w, chunk));
+  L.active = take(c * 4 * 2);
   L.total = o;
 }
 
@@ -1140,7 +1379,8 @@ extern "C" int vistaf_ftp_plan_create(const VistafFtpParams* P, VistafFtpPlan** 
   const int np = 2 * (P->patch_half < 3 ? 3 : P->patch_half) + 1;
   if (np > NPATCH_MAX || P->crop_w > CH_THREADS * CH_MAXPT || (P->dilate_kernel | 1) > MORPH_MAXROWS ||
       (P->close_kernel | 1) > MORPH_MAXROWS || P->edge_margin > 15 || P->crop_w < 256 ||
-      (long long)P->crop_w * P->crop_h >= (1ll << 24) || P->bad_inpaint_radius < 1 || P->bad_inpaint_radius > 8)
+      (long long)P->crop_w * P->crop_h >= (1ll << 24) || P->bad_inpaint_radius < 1 || P->bad_inpaint_radius > 8 ||
+      (P->fill_internal_holes && (P->hole_inpaint_radius < 1 || P->hole_inpaint_radius > 8 || P->hole_neighborhood > 31)))
     return vistaf_set_err("unsupported FTP parameters", cudaErrorInvalidValue, __FILE__, __LINE__);
   VistafFtpPlan* p = new (std::nothrow) VistafFtpPlan();
   if (!p) return vistaf_set_err("out of host memory", cudaErrorMemoryAllocation, __FILE__, __LINE__);
@@ -1163,7 +1403,7 @@ extern "C" int vistaf_ftp_plan_create(const VistafFtpParams* P, VistafFtpPlan** 
   p->g_illum = make_gauss(P->illum_sigma);
   p->g_pre = make_gauss(P->pre_blur_sigma);
   p->g_qual = make_gauss(P->quality_sigma);
-  p->g_smooth = make_gauss(P->smooth_sigma);
+  p->g_smooth = make_gauss(P->smooth_sigma > 0.f ? P->smooth_sigma : 1.0);
   p->g_unrel = make_gauss(P->unrel_sigma);
   p->se_bad = se_ellipse(P->bad_dilate < 3 ? 3 : (P->bad_dilate | 1));
   p->se_close = se_ellipse(P->close_kernel < 3 ? 3 : (P->close_kernel | 1));
@@ -1197,6 +1437,7 @@ extern "C" int vistaf_ftp_plan_create(const VistafFtpParams* P, VistafFtpPlan** 
 
 extern "C" void vistaf_ftp_plan_destroy(VistafFtpPlan* p) {
   if (!p) return;
+  vistaf_graph_drop(p);
   fft1d_destroy(&p->fN);
   cudaFree(p->roi); cudaFree(p->circ); cudaFree(p->valid); cudaFree(p->apo); cudaFree(p->den9);
   cudaFree(p->cref); cudaFree(p->amp_ref); cudaFree(p->rampx); cudaFree(p->rampy); cudaFree(p->hann);
@@ -1294,40 +1535,8 @@ static int ftp_patch_field(VistafFtpPlan* p, int nb, char* ws, const FtpWs& L, b
   return 0;
 }
 
-static int ftp_set_carrier(VistafFtpPlan* p) {
-  const int N = p->N, np = p->np, bw = np / 2, cx = N / 2, cy = N / 2;
-  if (p->pxi - bw < 0 || p->pxi + bw + 1 > N || p->pyi - bw < 0 || p->pyi + bw + 1 > N)
-    return vistaf_set_err("carrier patch touches the spectrum border (unsupported)", cudaErrorInvalidValue, __FILE__, __LINE__);
-  std::vector<int> kxs(np), kys(np);
-  for (int j = 0; j < np; j++) {
-    kxs[j] = ((p->pxi - bw + j - cx) % N + N) % N;       // fftshift-ed column -> unsigned frequency index
-    kys[j] = ((p->pyi - bw + j - cy) % N + N) % N;
-  }
-  CK(cudaMemcpy(p->kxs, kxs.data(), sizeof(int) * np, cudaMemcpyHostToDevice));
-  CK(cudaMemcpy(p->kys, kys.data(), sizeof(int) * np, cudaMemcpyHostToDevice));
-  const double dpx = (double)p->peak_xf - p->pxi, dpy = (double)p->peak_yf - p->pyi;
-  const bool on = fabs(dpx) > 1e-6 || fabs(dpy) > 1e-6;
-  std::vector<float2> rx(N), ry(N);
-  for (int i = 0; i < N; i++) {
-    const double ax = on ? -2.0 * VISTAF_PI * dpx * ((double)i / N) : 0.0, ay = on ? -2.0 * VISTAF_PI * dpy * ((double)i / N) : 0.0;
-    rx[i] = make_float2((float)cos(ax), (float)sin(ax));
-    ry[i] = make_float2((float)cos(ay), (float)sin(ay));
-  }
-  CK(cudaMemcpy(p->rampx, rx.data(), sizeof(float2) * N, cudaMemcpyHostToDevice));
-  CK(cudaMemcpy(p->rampy, ry.data(), sizeof(float2) * N, cudaMemcpyHostToDevice));
-  return 0;
-}
-
-extern "C" int vistaf_ftp_set_reference(VistafFtpPlan* p, const uint8_t* ref_gray, void* workspace, size_t ws_bytes,
-                                        VistafFtpReferenceInfo* info, void* stream) {
-  if (!p || !ref_gray || !workspace) return vistaf_set_err("vistaf_ftp_set_reference: null argument", cudaErrorInvalidValue, __FILE__, __LINE__);
-  cudaStream_t st = (cudaStream_t)stream;
-  FtpWs L;
-  ftp_layout(p, 1, L);
+static int ftp_reference_issue(VistafFtpPlan* p, const uint8_t* ref_gray, char* ws, const FtpWs& L, cudaStream_t st) {
   const int N = p->N;
-  const size_t dense = align256((size_t)N * N * 4) + align256((size_t)N * N * 8);
-  if (L.total + dense > ws_bytes) return vistaf_set_err("vistaf_ftp_set_reference: workspace too small", cudaErrorInvalidValue, __FILE__, __LINE__);
-  char* ws = (char*)workspace;
   if (ftp_preprocess(p, ref_gray, 1, ws, L, st, true)) return 1;
   float* Ip = (float*)(ws + L.total);
   float2* F = (float2*)(ws + L.total + align256((size_t)N * N * 4));
@@ -1341,26 +1550,38 @@ extern "C" int vistaf_ftp_set_reference(VistafFtpPlan* p, const uint8_t* ref_gra
   for (int r = 0; r < npk; r++) VL(), k_ftp_peak_round<<<296, 256, 0, st>>>(F, p->peak_keys, r, N, p->P.dc_exclusion);
   VL(), k_ftp_peak_choose<<<1, 1, 0, st>>>(F, p->peak_keys, npk, N, p->P.peak_max_dy_frac, (PeakResult*)p->peak_result);
   CKL();
-  PeakResult pr;
-  CK(cudaMemcpyAsync(&pr, p->peak_result, sizeof(pr), cudaMemcpyDeviceToHost, st));
-  FtpScal hs;
-  CK(cudaMemcpyAsync(&hs, ws + L.scal, sizeof(FtpScal), cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  if (!pr.ok) return vistaf_set_err("no carrier peak", cudaErrorInvalidValue, __FILE__, __LINE__);
-  p->peak_xf = pr.pxf; p->peak_yf = pr.pyf;
-  p->kx = (double)pr.pxf - N / 2; p->ky = (double)pr.pyf - N / 2;
-  p->pxi = (int)nearbyint((double)pr.pxf); p->pyi = (int)nearbyint((double)pr.pyf);
-  if (ftp_set_carrier(p)) return 1;
+  VL(), k_ftp_carrier_setup<<<cdiv(N > p->np ? N : p->np, 256), 256, 0, st>>>((PeakResult*)p->peak_result, p->kxs, p->kys, p->rampx,
+                                                                        p->rampy, N, p->np);
+  CKL();
   if (ftp_patch_field(p, 1, ws, L, true, st)) return 1;
   vistaf_stage_mark("", st);
-  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" int vistaf_ftp_set_reference(VistafFtpPlan* p, const uint8_t* ref_gray, void* workspace, size_t ws_bytes,
+                                        VistafFtpReferenceInfo* info, void* stream) {
+  if (!p || !ref_gray || !workspace) return vistaf_set_err("vistaf_ftp_set_reference: null argument", cudaErrorInvalidValue, __FILE__, __LINE__);
+  cudaStream_t st = (cudaStream_t)stream;
+  FtpWs L;
+  ftp_layout(p, 1, L);
+  const int N = p->N;
+  const size_t dense = align256((size_t)N * N * 4) + align256((size_t)N * N * 8);
+  if (L.total + dense > ws_bytes) return vistaf_set_err("vistaf_ftp_set_reference: workspace too small", cudaErrorInvalidValue, __FILE__, __LINE__);
+  // the carrier stays on the device, so the call is asynchronous (and replayable) unless the caller asks for `info`
+  const VistafGraphKey key = vistaf_graph_key(1, p, ref_gray, workspace, ws_bytes);
+  if (vistaf_graph_run(key, st, [&](cudaStream_t s) { return ftp_reference_issue(p, ref_gray, (char*)workspace, L, s); })) return 1;
   p->have_ref = true;
-  p->ref_bad = (int)hs.n_bad;
   if (info) {
-    info->peak_x = p->peak_xf; info->peak_y = p->peak_yf; info->fft_h = N; info->fft_w = N;
-    info->kx = (float)p->kx; info->ky = (float)p->ky;
-    info->period_px = fabs(p->kx) > 1e-9 ? (float)((double)N / fabs(p->kx)) : 0.f;
-    info->bad_px = p->ref_bad;
+    PeakResult pr;
+    FtpScal hs;
+    CK(cudaMemcpyAsync(&pr, p->peak_result, sizeof(pr), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&hs, (char*)workspace + L.scal, sizeof(FtpScal), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (!pr.ok) return vistaf_set_err("no carrier peak (or its patch touches the spectrum border)", cudaErrorInvalidValue, __FILE__, __LINE__);
+    info->peak_x = pr.pxf; info->peak_y = pr.pyf; info->fft_h = N; info->fft_w = N;
+    info->kx = (float)pr.kx; info->ky = (float)pr.ky;
+    info->period_px = fabs(pr.kx) > 1e-9 ? (float)((double)N / fabs(pr.kx)) : 0.f;
+    info->bad_px = (int)hs.n_bad;
   }
   return 0;
 }
@@ -1406,6 +1627,40 @@ static int irls_fit(VistafFtpPlan* p, const float* z, FitMask fm, FtpScal* sc, S
       if (select_quantile_out(r3, GrabOut{scg, G_IRLS_MAD}, selg, listg, npix, ng, -1.0f, st)) return 1;
     }
   }
+  CKL();
+  return 0;
+}
+
+// F14 on a batch: hm [nb][h][w] in / out (NaN = no height), rel in, outrel = output_reliable out, cand = hole candidates
+// (written for every frame only when cand_is_output).  Scratch: zin, dist (float planes), dtmp (uint plane), the Telea
+// workspace, two int arrays of nb entries.
+static int ftp_fill_holes(VistafFtpPlan* p, float* hm, const uint8_t* rel, uint8_t* outrel, uint8_t* cand, bool cand_is_output,
+                          float* zin, float* dist, unsigned int* dtmp, char* telea_ws, int* active, FtpScal* sc, SelectState* sel,
+                          int nb, cudaStream_t st, bool search = true) {   // search = false: the caller knows there is no hole
+  const VistafFtpParams& P = p->P;
+  const int h = p->h, w = p->w, npix = h * w;
+  const long long plane = npix;
+  const dim3 gpix(cdiv(npix, 256), nb);
+  int* act_holes = active;
+  int* act_cand = active + nb;
+  if (P.fill_internal_holes && search) {
+    VL(), k_holes_count<<<dim3(64, nb), 256, 0, st>>>(hm, rel, sc, npix);
+    VL(), k_holes_active<<<nb, 1, 0, st>>>(sc, act_holes, 0);
+    if (cand_is_output) CK(cudaMemsetAsync(cand, 0, (size_t)npix * nb, st));
+    if (chamfer_dt(NotMaskZero{rel, plane, w}, dist, dtmp, h, w, nb, st, act_holes)) return 1;
+    const int k = (P.hole_neighborhood < 3 ? 3 : P.hole_neighborhood) | 1;
+    VL(), k_holes_candidates<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(hm, rel, dist, sc, cand, h, w, k, P.hole_known_frac,
+                                                                    P.hole_min_dist);
+    VL(), k_holes_active<<<nb, 1, 0, st>>>(sc, act_cand, 1);
+    unsigned int* lists = sel_lists(sel, nb);
+    if (select_quantile_out(HoleKnownVal{hm, rel, sc, plane}, HoleGrab{sc, 0}, sel, lists, npix, nb, -1.0f, st)) return 1;
+    if (select_quantile_out(HoleTmpVal{hm, rel, cand, sc, plane}, HoleGrab{sc, 1}, sel, lists, npix, nb, -1.0f, st)) return 1;
+    VL(), k_holes_canvas<<<gpix, 256, 0, st>>>(hm, rel, cand, sc, zin, npix);
+    if (telea_inpaint(HoleMask{cand, sc, plane, w}, zin, (size_t)npix, &sc[0].status, sizeof(FtpScal), telea_ws, h, w, nb,
+                      P.hole_inpaint_radius, st, 0, act_cand))
+      return 1;
+  }
+  VL(), k_holes_apply<<<gpix, 256, 0, st>>>(hm, rel, cand, zin, sc, outrel, npix);
   CKL();
   return 0;
 }
@@ -1463,6 +1718,8 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   VL(), k_ftp_residues<<<dim3(cdiv(w, 256), h, nb), 256, 0, st>>>(wrapped, rel, sc, h, w);
   if (uf_label(MaskFg{rel, plane, w}, PhaseEdge{wrapped, plane}, uf, (unsigned int*)nullptr, &sc[0].uf_bad, sizeof(FtpScal), h, w, nb, st))
     return 1;
+  // frames with residues (or a loop around a mask hole that does not close): the reference's sequential flood
+  VL(), k_ftp_unwrap_heap<<<nb, 32, 0, st>>>(wrapped, quality, rel, sc, uf, area, h, w, p->debug_flags & 1);
   VL(), k_ftp_seed_root<<<nb, 1, 0, st>>>(uf, sc, npix);
   VL(), k_ftp_unwrap_apply<<<gpix, 256, 0, st>>>(uf, wrapped, sc, unw, npix);
   CKL();
@@ -1499,19 +1756,33 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   CKL();
   vistaf_stage_mark("F.smooth_sign", st);
   // ---- E: masked smoothing (sigma 2.5) and sign
-  if (gauss_blur(HmNumLoad{unw, rel, sc, g, plane, w}, PlaneStore{hnum, plane, w}, tmp, h, w, nb, p->g_smooth, p->g_smooth, st)) return 1;
-  if (gauss_blur(HmDenLoad{unw, rel, plane, w}, RatioStore{hnum, hm, plane, w}, tmp, h, w, nb, p->g_smooth, p->g_smooth, st)) return 1;
+  if (P.smooth_sigma > 0.f) {
+    if (gauss_blur(HmNumLoad{unw, rel, sc, g, plane, w}, PlaneStore{hnum, plane, w}, tmp, h, w, nb, p->g_smooth, p->g_smooth, st)) return 1;
+    if (gauss_blur(HmDenLoad{unw, rel, plane, w}, RatioStore{hnum, hm, plane, w}, tmp, h, w, nb, p->g_smooth, p->g_smooth, st)) return 1;
+  } else {
+    VL(), k_ftp_hm_plain<<<gpix, 256, 0, st>>>(unw, rel, sc, g, hm, npix);
+  }
   if (select_grab(MaskedValB{hm, rel, plane}, sc, G_CORETHR, sel, npix, nb, P.core_pct, st)) return 1;
   if (select_grab(CoreVal{hm, rel, sc, plane}, sc, G_COREMED, sel, npix, nb, -1.0f, st)) return 1;
   CKL();
+  vistaf_stage_mark("F.internal_holes", st);
+  // ---- F14: internal holes (gated: no frame of the shipped configuration has any), output_reliable
+  uint8_t* outrel = O.output_reliable ? O.output_reliable + f0 * (size_t)npix : m2;
+  uint8_t* cand = O.hole_candidates ? O.hole_candidates + f0 * (size_t)npix : contact;
+  // with the reliable smoothing on, masked_gaussian_smooth (num / (den + 1e-6)) is finite on every pixel: no hole can
+  // exist and only output_reliable (= reliable) is written
+  if (O.hole_candidates && P.smooth_sigma > 0.f) CK(cudaMemsetAsync(cand, 0, (size_t)npix * nb, st));
+  if (ftp_fill_holes(p, hm, rel, outrel, cand, O.hole_candidates != nullptr, hnum, dist_in, dtmp, ws + L.telea, (int*)(ws + L.active),
+                     sc, sel, nb, st, !(P.smooth_sigma > 0.f)))
+    return 1;
   vistaf_stage_mark("F.chamfer_frontier_assemble", st);
-  // ---- F: frontier taper, assembly, sigma-9 fill of the unreliable part, phase -> mm
-  if (chamfer_dt2(NotMaskZero{rel, plane, w}, dist_in, dtmp, MaskZero{rel, plane, w}, dist_out, (unsigned int*)sm, h, w, nb, st))
+  // ---- F: frontier taper, assembly, sigma-9 fill of the unreliable part, phase -> mm (on output_reliable, :1803-1841)
+  if (chamfer_dt2(NotMaskZero{outrel, plane, w}, dist_in, dtmp, MaskZero{outrel, plane, w}, dist_out, (unsigned int*)sm, h, w, nb, st))
     return 1;                                     // sm (written by the sigma-9 blur below) doubles as the second scratch plane
-  if (gauss_blur(AsmLoad{hm, dist_in, rel, p->roi, sc, plane, w, P.frontier_band}, Den9Store{p->den9, sm, plane, w}, tmp, h, w,
+  if (gauss_blur(AsmLoad{hm, dist_in, outrel, p->roi, sc, plane, w, P.frontier_band}, Den9Store{p->den9, sm, plane, w}, tmp, h, w,
                  nb, p->g_unrel, p->g_unrel, st))
     return 1;
-  VL(), k_ftp_assemble<<<gpix, 256, 0, st>>>(hm, dist_in, dist_out, sm, rel, p->roi, sc, out, npix, P.frontier_band,
+  VL(), k_ftp_assemble<<<gpix, 256, 0, st>>>(hm, dist_in, dist_out, sm, outrel, p->roi, sc, out, npix, P.frontier_band,
                                        P.height_model, P.use_negated_height);
   CKL();
   vistaf_stage_mark("F.blob_filter_force", st);
@@ -1524,13 +1795,18 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   VL(), k_depth_sign<<<dim3(64, nb), 256, 0, st>>>(out, nullptr, &sc[0].pos_sum, &sc[0].neg_sum, sizeof(FtpScal), npix);
   VL(), k_depth_reduce<<<dim3(64, nb), 256, 0, st>>>(out, nullptr, &sc[0].pos_sum, &sc[0].neg_sum, sizeof(FtpScal), &sc[0].vol_sum,
                                                &sc[0].vol_cnt, &sc[0].vol_max_bits, npix, (float)P.depth_eps_mm);
-  if (O.output_reliable && O.output_reliable != rel)
-    CK(cudaMemcpyAsync(O.output_reliable + f0 * (size_t)npix, rel, (size_t)npix * nb, cudaMemcpyDeviceToDevice, st));
-  const double period = fabs(p->kx) > 1e-9 ? (double)p->N / fabs(p->kx) : 0.0;
-  VL(), k_ftp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, O.records + f0, nb, w, period, P.grating_pitch_mm, P.force_model);
+  VL(), k_ftp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, O.records + f0, nb, w, (const PeakResult*)p->peak_result, p->N,
+                                                P.grating_pitch_mm, P.force_model);
   CKL();
   vistaf_stage_mark("", st);
   return 0;
+}
+
+static unsigned long long out_hash(const VistafFtpOutputs& o) {       // FNV-1a over the output pointers
+  unsigned long long h = 1469598103934665603ull;
+  const unsigned char* c = (const unsigned char*)&o;
+  for (size_t i = 0; i < sizeof(o); i++) { h ^= c[i]; h *= 1099511628211ull; }
+  return h;
 }
 
 extern "C" int vistaf_ftp_batch(VistafFtpPlan* p, const uint8_t* def_gray, int batch, const VistafFtpOutputs* out,
@@ -1542,12 +1818,17 @@ extern "C" int vistaf_ftp_batch(VistafFtpPlan* p, const uint8_t* def_gray, int b
   int chunk = batch;
   while (chunk >= 1) { ftp_layout(p, chunk, L); if (L.total <= ws_bytes) break; chunk = chunk > 8 ? chunk - chunk / 8 : chunk - 1; }
   if (chunk < 1) return vistaf_set_err("vistaf_ftp_batch: workspace too small for one frame", cudaErrorInvalidValue, __FILE__, __LINE__);
-  for (int f0 = 0; f0 < batch; f0 += chunk) {
-    int nb = batch - f0 < chunk ? batch - f0 : chunk;
-    if (nb != chunk) ftp_layout(p, nb, L);
-    if (ftp_chunk(p, def_gray, nb, *out, (size_t)f0, (char*)workspace, L, (cudaStream_t)stream)) return 1;
-  }
-  return 0;
+  const VistafFtpOutputs O = *out;
+  const VistafGraphKey key = vistaf_graph_key(2, p, def_gray, batch, out_hash(O), O.height_mm, O.records, workspace, ws_bytes, p->debug_flags);
+  return vistaf_graph_run(key, (cudaStream_t)stream, [&](cudaStream_t st) {
+    FtpWs Lc = L;
+    for (int f0 = 0; f0 < batch; f0 += chunk) {
+      int nb = batch - f0 < chunk ? batch - f0 : chunk;
+      if (nb != chunk) ftp_layout(p, nb, Lc);
+      if (ftp_chunk(p, def_gray, nb, O, (size_t)f0, (char*)workspace, Lc, st)) return 1;
+    }
+    return 0;
+  });
 }
 
 // Split form of vistaf_ftp_batch for ONE chunk: _begin runs the part of the chain that does not need the reference
@@ -1560,7 +1841,9 @@ extern "C" int vistaf_ftp_batch_begin(VistafFtpPlan* p, const uint8_t* def_gray,
   FtpWs L;
   ftp_layout(p, batch, L);
   if (L.total > ws_bytes) return vistaf_set_err("vistaf_ftp_batch_begin: workspace too small for the batch in one chunk", cudaErrorInvalidValue, __FILE__, __LINE__);
-  return ftp_preprocess(p, def_gray, batch, (char*)workspace, L, (cudaStream_t)stream);
+  const VistafGraphKey key = vistaf_graph_key(3, p, def_gray, batch, workspace, ws_bytes);
+  return vistaf_graph_run(key, (cudaStream_t)stream,
+                          [&](cudaStream_t st) { return ftp_preprocess(p, def_gray, batch, (char*)workspace, L, st); });
 }
 extern "C" int vistaf_ftp_batch_finish(VistafFtpPlan* p, const uint8_t* def_gray, int batch, const VistafFtpOutputs* out,
                                        void* workspace, size_t ws_bytes, void* stream) {
@@ -1570,7 +1853,67 @@ extern "C" int vistaf_ftp_batch_finish(VistafFtpPlan* p, const uint8_t* def_gray
   FtpWs L;
   ftp_layout(p, batch, L);
   if (L.total > ws_bytes) return vistaf_set_err("vistaf_ftp_batch_finish: workspace too small for the batch in one chunk", cudaErrorInvalidValue, __FILE__, __LINE__);
-  return ftp_chunk(p, def_gray, batch, *out, 0, (char*)workspace, L, (cudaStream_t)stream, true);
+  const VistafFtpOutputs O = *out;
+  const VistafGraphKey key = vistaf_graph_key(4, p, def_gray, batch, out_hash(O), O.height_mm, O.records, workspace, ws_bytes, p->debug_flags);
+  return vistaf_graph_run(key, (cudaStream_t)stream,
+                          [&](cudaStream_t st) { return ftp_chunk(p, def_gray, batch, O, 0, (char*)workspace, L, st, true); });
+}
+
+extern "C" int vistaf_ftp_set_debug(VistafFtpPlan* p, int flags) {
+  if (!p) return vistaf_set_err("vistaf_ftp_set_debug: null plan", cudaErrorInvalidValue, __FILE__, __LINE__);
+  p->debug_flags = flags;
+  return 0;
+}
+
+// F14 on caller planes (see include/vistaf.h)
+extern "C" int vistaf_ftp_fill_holes(VistafFtpPlan* p, float* height, const uint8_t* reliable, int batch, uint8_t* output_reliable,
+                                     uint8_t* hole_candidates, void* workspace, size_t ws_bytes, void* stream) {
+  if (!p || !height || !reliable || !output_reliable || !hole_candidates || !workspace || batch < 1)
+    return vistaf_set_err("vistaf_ftp_fill_holes: bad argument", cudaErrorInvalidValue, __FILE__, __LINE__);
+  FtpWs L;
+  ftp_layout(p, batch, L);
+  if (L.total > ws_bytes) return vistaf_set_err("vistaf_ftp_fill_holes: workspace too small", cudaErrorInvalidValue, __FILE__, __LINE__);
+  char* ws = (char*)workspace;
+  cudaStream_t st = (cudaStream_t)stream;
+  FtpScal* sc = (FtpScal*)(ws + L.scal);
+  SelectState* sel = (SelectState*)(ws + L.sel);
+  if (sel_reset(sel, batch, st)) return 1;
+  VL(), k_ftp_init<<<cdiv(batch, 128), 128, 0, st>>>(sc, batch);
+  return ftp_fill_holes(p, height, reliable, output_reliable, hole_candidates, true, (float*)(ws + L.hnum), (float*)(ws + L.dist_in),
+                        (unsigned int*)(ws + L.dtmp), ws + L.telea, (int*)(ws + L.active), sc, sel, batch, st, true);
+}
+
+// F10 on caller planes (see include/vistaf.h)
+__global__ void k_ftp_residue_out(const FtpScal* sc, int* out, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (int)(sc[i].residues + sc[i].uf_bad);
+}
+extern "C" int vistaf_ftp_unwrap(VistafFtpPlan* p, const float* wrapped, const float* quality, const uint8_t* reliable, int batch,
+                                 float* unwrapped, int32_t* residues, int mode, void* workspace, size_t ws_bytes, void* stream) {
+  if (!p || !wrapped || !quality || !reliable || !unwrapped || !workspace || batch < 1)
+    return vistaf_set_err("vistaf_ftp_unwrap: bad argument", cudaErrorInvalidValue, __FILE__, __LINE__);
+  FtpWs L;
+  ftp_layout(p, batch, L);
+  if (L.total > ws_bytes) return vistaf_set_err("vistaf_ftp_unwrap: workspace too small", cudaErrorInvalidValue, __FILE__, __LINE__);
+  char* ws = (char*)workspace;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int h = p->h, w = p->w, npix = h * w;
+  const long long plane = npix;
+  FtpScal* sc = (FtpScal*)(ws + L.scal);
+  ull* uf = (ull*)(ws + L.uf);
+  unsigned int* area = (unsigned int*)(ws + L.area);
+  VL(), k_ftp_init<<<cdiv(batch, 128), 128, 0, st>>>(sc, batch);
+  VL(), k_ftp_seed<<<dim3(64, batch), 256, 0, st>>>(quality, reliable, sc, npix);
+  VL(), k_ftp_residues<<<dim3(cdiv(w, 256), h, batch), 256, 0, st>>>(wrapped, reliable, sc, h, w);
+  if (uf_label(MaskFg{reliable, plane, w}, PhaseEdge{wrapped, plane}, uf, (unsigned int*)nullptr, &sc[0].uf_bad, sizeof(FtpScal), h, w,
+               batch, st))
+    return 1;
+  VL(), k_ftp_unwrap_heap<<<batch, 32, 0, st>>>(wrapped, quality, reliable, sc, uf, area, h, w, mode == 1);
+  VL(), k_ftp_seed_root<<<batch, 1, 0, st>>>(uf, sc, npix);
+  VL(), k_ftp_unwrap_apply<<<dim3(cdiv(npix, 256), batch), 256, 0, st>>>(uf, wrapped, sc, unwrapped, npix);
+  if (residues) VL(), k_ftp_residue_out<<<cdiv(batch, 128), 128, 0, st>>>(sc, residues, batch);
+  CKL();
+  return 0;
 }
 
 // force_sensor.depth_map_to_volume_cm3 on device maps: out3[b] = (volume_cm3, area_mm2, max_depth_mm)

@@ -209,7 +209,8 @@ __device__ __forceinline__ void chamfer_body(Zero zero, float* __restrict__ out,
 
 template <class Zero>
 __global__ void __launch_bounds__(CH_THREADS) k_chamfer(Zero zero, float* __restrict__ out, unsigned int* __restrict__ tmp,
-                                                         int h, int w) {
+                                                         int h, int w, const int* __restrict__ active) {
+  if (active && active[blockIdx.x] < 0) return;      // frame skipped (its plane stays undefined)
   chamfer_body(zero, out, tmp, h, w);
 }
 // two independent transforms in one launch (grid.y selects): the row walk is a serial chain, so running both side by
@@ -318,9 +319,10 @@ static int chamfer_dt2(ZeroA za, float* outa, unsigned int* tmpa, ZeroB zb, floa
   return 0;
 }
 template <class Zero>
-static int chamfer_dt(Zero zero, float* out, unsigned int* tmp, int h, int w, int batch, cudaStream_t st) {
+static int chamfer_dt(Zero zero, float* out, unsigned int* tmp, int h, int w, int batch, cudaStream_t st,
+                      const int* active = nullptr) {
   if (w > CH_THREADS * CH_MAXPT) return vistaf_set_err("chamfer_dt: row too long", cudaErrorInvalidValue, __FILE__, __LINE__);
-  VL(), k_chamfer<Zero><<<batch, CH_THREADS, sizeof(unsigned int) * 2 * (size_t)(w + 2), st>>>(zero, out, tmp, h, w);
+  VL(), k_chamfer<Zero><<<batch, CH_THREADS, sizeof(unsigned int) * 2 * (size_t)(w + 2), st>>>(zero, out, tmp, h, w, active);
   CKL();
   return 0;
 }

@@ -27,6 +27,7 @@ struct Cand { float mag; int ky, kx; int pad; };
 struct TempWs {               // per-chunk workspace layout (byte offsets), planes are [chunk][...]
   size_t gray8, satraw, sat, norm, tmp, A, G, maskA, m1, m2, cand, scal, sel, total;
   size_t t10_frame, t10_stat, t10_wide, t10_color, t10_telea;      // T10 slots (saturated frames only)
+  size_t t12_frame;                                                // T12 slots (frames with a tilted carrier)
   int t10_slots;
 };
 
@@ -49,6 +50,7 @@ struct TempScal {             // per-frame scalars living in the workspace
   float blur_rc, blur_cc;       // sigma-20 blur of the constant background: row pass R(median), column pass C(R(median))
   int t10_slot;                 // T10 slot of a saturated frame (-1: none free, the fill is skipped and flagged)
   unsigned int wmin_key, wmax_key, pad2;      // ordered keys of min / max of the raw wide-model map over roi_eff
+  double aff_f[6], aff_b[6];    // T12 on a tilted carrier: dst -> src maps of the forward / backward warpAffine
 };
 
 struct VistafTempPlan {
@@ -714,6 +716,7 @@ struct FeatArgs {
   // T10 (saturated frames that own a slot): raw wide-model map and clamped colour map on the ROI window
   float *t10_wide, *t10_color; const int* t10_frame; unsigned int* t10_stat;
   int wx0, wy0, ww, wh;
+  int tile_x0, tile_y0;          // first tile of the launch grid (T10 instance: only the tiles over the ROI window are launched)
 };
 
 // fusion of the wide and colour maps at one pixel (temperature_sensor.py:594-641); wide / colour are clamped already
@@ -749,7 +752,7 @@ __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
   __shared__ uint8_t tile[(FT_H + 4) * (FT_W + 4) * 3];
   const int b = T10 ? a.t10_frame[blockIdx.z] : (int)blockIdx.z;
   if (T10 && b < 0) return;
-  const int x0 = blockIdx.x * FT_W, y0 = blockIdx.y * FT_H, h = a.h, w = a.w;
+  const int x0 = ((int)blockIdx.x + (T10 ? a.tile_x0 : 0)) * FT_W, y0 = ((int)blockIdx.y + (T10 ? a.tile_y0 : 0)) * FT_H, h = a.h, w = a.w;
   const size_t plane = (size_t)h * w;
   const uint8_t* img = a.frames + (size_t)b * plane * 3;
   const int tid = threadIdx.y * FT_W + threadIdx.x;
@@ -879,7 +882,7 @@ __global__ void k_t10_slots(TempScal* sc, int nb, int* slot_frame, unsigned int*
     if (sat) {
       const int at = n + __popc(bits & ((1u << lane) - 1u));
       if (at < slots) { slot_frame[at] = b; sc[b].t10_slot = at; }
-      else sc[b].status |= VISTAF_ST_SAT_UNFILLED;
+      else sc[b].status |= VISTAF_ST_RERUN_ALONE;
     }
     n += __popc(bits);
   }
@@ -970,7 +973,8 @@ struct FinalStore {
   __device__ void operator()(int b, int y, int x, float v) {
     long long i = (long long)y * w + x;
     float r = __int_as_float(0x7fc00000);
-    if (roi[i]) {
+    // a frame with a tilted carrier gets its ROI values (and statistics) from the warpAffine path below (k_t12_back)
+    if (roi[i] && (sc[b].status & (VISTAF_ST_ROTATED_CARRIER | VISTAF_ST_RERUN_ALONE)) != VISTAF_ST_ROTATED_CARRIER) {
       r = fminf(fmaxf(v, lo), hi);
       s1 += (double)r; s2 += (double)r * (double)r;
       mn = fminf(mn, r); mx = fmaxf(mx, r); cnt++;
@@ -1007,6 +1011,136 @@ struct FinalVal {              // value stream for the median: final map over th
     return v == v;
   }
 };
+
+// ------------------------------------------------------------------ T12 on a tilted carrier (temperature_sensor.py:705-742)
+// angle = atan2(dy, dx) of the integer carrier peak; the map is rotated by cv2.warpAffine (INTER_LINEAR, BORDER_REFLECT)
+// so the stripes' normal lies along +x, blurred with sigma (across, along), rotated back; the ROI takes the same two
+// warps with INTER_NEAREST / constant 0 and blanks what falls outside.  cv2.warpAffine arithmetic (imgwarp.cpp,
+// WarpAffineInvoker), reproduced here: the 2x3 matrix is inverted in float64, source coordinates are 22.10 fixed point
+// (X0 = rint((M1 y + M2) 1024) + delta, adelta = rint(M0 x 1024)), the bilinear weights are the 1/32-pixel table
+// (1 - a/32, a/32) multiplied in float32, the four taps summed left to right.  Verified bit-exact against cv2 4.13 on
+// the host restatement (tests/test_temperature_gpu.py compares the device result with cv2 through the oracle).
+__device__ __forceinline__ void t12_rotation(double cx, double cy, double angle_deg, double* m) {
+  const double a = __dmul_rn(angle_deg, VISTAF_PI / 180.0);
+  const double alpha = cos(a), beta = sin(a);
+  double M0 = alpha, M1 = beta, M2 = __dsub_rn(__dmul_rn(__dsub_rn(1.0, alpha), cx), __dmul_rn(beta, cy));
+  double M3 = -beta, M4 = alpha, M5 = __dadd_rn(__dmul_rn(beta, cx), __dmul_rn(__dsub_rn(1.0, alpha), cy));
+  // warpAffine without WARP_INVERSE_MAP inverts the matrix first
+  double D = __dsub_rn(__dmul_rn(M0, M4), __dmul_rn(M1, M3));
+  D = D != 0.0 ? __ddiv_rn(1.0, D) : 0.0;
+  const double A11 = __dmul_rn(M4, D), A22 = __dmul_rn(M0, D);
+  M0 = A11; M1 = __dmul_rn(M1, -D); M3 = __dmul_rn(M3, -D); M4 = A22;
+  const double b1 = __dsub_rn(__dmul_rn(-M0, M2), __dmul_rn(M1, M5));
+  const double b2 = __dsub_rn(__dmul_rn(-M3, M2), __dmul_rn(M4, M5));
+  m[0] = M0; m[1] = M1; m[2] = b1; m[3] = M3; m[4] = M4; m[5] = b2;
+}
+// tilted frames of a chunk -> slots (frame list + 0/1 gate per slot), like k_t10_slots
+__global__ void k_t12_slots(TempScal* sc, int nb, int* slot_frame, unsigned int* slot_on, int slots) {
+  const int lane = threadIdx.x;
+  int n = 0;
+  for (int b0 = 0; b0 < nb; b0 += 32) {
+    const int b = b0 + lane;
+    const bool rot = b < nb && (sc[b].status & VISTAF_ST_ROTATED_CARRIER) != 0;
+    const unsigned int bits = __ballot_sync(0xffffffffu, rot);
+    if (rot) {
+      const int at = n + __popc(bits & ((1u << lane) - 1u));
+      if (at < slots) slot_frame[at] = b;
+      else sc[b].status |= VISTAF_ST_RERUN_ALONE;      // its final map keeps the axis-aligned blur until it is re-run
+    }
+    n += __popc(bits);
+  }
+  for (int s = lane; s < slots; s += 32) { slot_on[s] = s < n ? 1u : 0u; if (s >= n) slot_frame[s] = -1; }
+}
+__global__ void k_t12_setup(TempScal* sc, int h, int w) {
+  TempScal& s = sc[blockIdx.x];
+  if (!(s.status & VISTAF_ST_ROTATED_CARRIER)) return;
+  const double dx = (double)(s.peak_x - w / 2), dy = (double)(s.peak_y - h / 2);
+  const double angle_rad = atan2(dy, dx);
+  const double deg = __ddiv_rn(__dmul_rn(-angle_rad, 180.0), VISTAF_PI);
+  t12_rotation((double)((float)w / 2.0f), (double)((float)h / 2.0f), deg, s.aff_f);
+  t12_rotation((double)((float)w / 2.0f), (double)((float)h / 2.0f), -deg, s.aff_b);
+}
+// fixed-point source coordinates of destination pixel (x, y): `shift` = 5 (bilinear, 1/32 px) or 10 (nearest)
+__device__ __forceinline__ void t12_src(const double* m, int x, int y, int shift, int delta, int& X, int& Y) {
+  const int ad = __double2int_rn(__dmul_rn(__dmul_rn(m[0], (double)x), 1024.0));
+  const int bd = __double2int_rn(__dmul_rn(__dmul_rn(m[3], (double)x), 1024.0));
+  const int X0 = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(m[1], (double)y), m[2]), 1024.0)) + delta;
+  const int Y0 = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(m[4], (double)y), m[5]), 1024.0)) + delta;
+  X = (X0 + ad) >> shift; Y = (Y0 + bd) >> shift;
+}
+template <class Src>
+__device__ __forceinline__ float t12_bilinear(const Src& src, const double* m, int x, int y, int h, int w) {
+  int X, Y;
+  t12_src(m, x, y, 5, 16, X, Y);
+  const int sx = X >> 5, sy = Y >> 5;
+  const float fx = (float)(X & 31) * (1.0f / 32.0f), fy = (float)(Y & 31) * (1.0f / 32.0f);
+  const float tx0 = __fsub_rn(1.0f, fx), ty0 = __fsub_rn(1.0f, fy);
+  const int xa = reflect(sx, w), xb = reflect(sx + 1, w), ya = reflect(sy, h), yb = reflect(sy + 1, h);
+  float v = __fmul_rn(src(ya, xa), __fmul_rn(ty0, tx0));
+  v = __fadd_rn(v, __fmul_rn(src(ya, xb), __fmul_rn(ty0, fx)));
+  v = __fadd_rn(v, __fmul_rn(src(yb, xa), __fmul_rn(fy, tx0)));
+  v = __fadd_rn(v, __fmul_rn(src(yb, xb), __fmul_rn(fy, fx)));
+  return v;
+}
+struct T12Fused {               // map0 = fused with non-finite -> 0
+  const float* p; int w;
+  __device__ float operator()(int y, int x) const { const float v = p[(size_t)y * w + x]; return fabsf(v) <= 3.4e38f ? v : 0.f; }
+};
+struct T12Plane { const float* p; int w; __device__ float operator()(int y, int x) const { return p[(size_t)y * w + x]; } };
+__global__ void __launch_bounds__(256) k_t12_forward(const float* __restrict__ fused, float* __restrict__ rot, const TempScal* sc,
+                                                      const int* __restrict__ slot_frame, int h, int w) {
+  const int s = blockIdx.z, b = slot_frame[s], y = blockIdx.y, x = blockIdx.x * 256 + threadIdx.x;
+  if (b < 0 || x >= w) return;
+  rot[(size_t)s * h * w + (size_t)y * w + x] = t12_bilinear(T12Fused{fused + (size_t)b * h * w, w}, sc[b].aff_f, x, y, h, w);
+}
+// nearest-neighbour warp of the ROI, twice (forward then back), evaluated on the fly
+__device__ __forceinline__ bool t12_back_roi(const uint8_t* __restrict__ roi, const TempScal& S, int x, int y, int h, int w) {
+  int X, Y;
+  t12_src(S.aff_b, x, y, 10, 512, X, Y);            // pixel of rot_roi read by back_roi(x, y)
+  if (X < 0 || X >= w || Y < 0 || Y >= h) return false;
+  int X2, Y2;
+  t12_src(S.aff_f, X, Y, 10, 512, X2, Y2);          // pixel of roi read by rot_roi(X, Y)
+  if (X2 < 0 || X2 >= w || Y2 < 0 || Y2 >= h) return false;
+  return roi[(size_t)Y2 * w + X2] != 0;
+}
+__global__ void __launch_bounds__(256) k_t12_back(const float* __restrict__ blurred, const uint8_t* __restrict__ roi,
+                                                   float* __restrict__ fin, TempScal* sc, const int* __restrict__ slot_frame, int h,
+                                                   int w, int bx0, int bx1, int by0, float lo, float hi) {
+  __shared__ double sh[3 * 32];
+  __shared__ float shm[2 * 32];
+  const int slot = blockIdx.z, b = slot_frame[slot], y = by0 + blockIdx.y, x = bx0 + blockIdx.x * 256 + threadIdx.x;
+  if (b < 0) return;
+  TempScal& S = sc[b];
+  double v[3] = {0.0, 0.0, 0.0};
+  float mn = 3.0e38f, mx = 0.f;
+  if (x < bx1) {
+    const size_t i = (size_t)y * w + x, fr = (size_t)b * h * w;
+    float r = __int_as_float(0x7fc00000);
+    if (roi[i] && t12_back_roi(roi, S, x, y, h, w)) {
+      r = fminf(fmaxf(t12_bilinear(T12Plane{blurred + (size_t)slot * h * w, w}, S.aff_b, x, y, h, w), lo), hi);
+      v[0] = (double)r; v[1] = (double)r * (double)r; v[2] = 1.0;
+      mn = r; mx = r;
+    }
+    fin[fr + i] = r;
+  }
+  block_sum<3>(v, sh);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float a = warp_min(mn), c = warp_max(mx);
+  __syncthreads();
+  if (lane == 0) { shm[wid] = a; shm[32 + wid] = c; }
+  __syncthreads();
+  if (threadIdx.x == 0 && v[2] > 0.0) {
+    for (int k = 1; k < 8; k++) { a = fminf(a, shm[k]); c = fmaxf(c, shm[32 + k]); }
+    atomicAdd(&S.t_sum, v[0]); atomicAdd(&S.t_sumsq, v[1]); atomicAdd(&S.t_count, (unsigned)v[2]);
+    atomicMin((int*)&S.t_min, __float_as_int(a));
+    atomicMax((int*)&S.t_max, __float_as_int(c));
+  }
+}
+struct T12Load { const float* p; long long plane; int w;
+  __device__ float operator()(int b, int y, int x) const { return p[(long long)b * plane + (long long)y * w + x]; } };
+struct T12Store { float* p; long long plane; int w;
+  __device__ void operator()(int b, int y, int x, float v) { p[(long long)b * plane + (long long)y * w + x] = v; }
+  __device__ void finish(int) {} };
 
 __global__ void k_temp_init(TempScal* sc, int n) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1071,8 +1205,9 @@ static void temp_layout(const VistafTempPlan* p, int chunk, TempWs& L) {
   L.cand = take(c * (size_t)p->nblk_cols * TOPK * sizeof(Cand));
   L.scal = take(c * sizeof(TempScal));
   L.sel = take(sel_ws_bytes((int)c, TEMP_SEL_CAP));
-  // T10 works on the ROI window of at most an eighth of the chunk's frames at a time (saturated frames are rare; every
-  // slot costs a round of empty launches on frames without glare)
+  // T10 (and the warpAffine path of T12) work on at most an eighth of the chunk's frames at a time, compacted into slots
+  // (saturated / tilted frames are rare; every slot costs a round of early-exit blocks on the other frames).  A frame
+  // beyond the slots comes back with VISTAF_ST_RERUN_ALONE.
   const T10Win wn = t10_window(p);
   const size_t ts = (size_t)((chunk + 7) / 8), wpix = (size_t)wn.h * wn.w;
   L.t10_slots = (int)ts;
@@ -1081,6 +1216,7 @@ static void temp_layout(const VistafTempPlan* p, int chunk, TempWs& L) {
   L.t10_wide = take(ts * wpix * 4);
   L.t10_color = take(ts * wpix * 4);
   L.t10_telea = take(telea_ws_bytes(wn.h, wn.w, (int)ts));
+  L.t12_frame = take(ts * 4 * 2);
   L.total = o;
 }
 
@@ -1186,6 +1322,7 @@ extern "C" int vistaf_temp_plan_create(const VistafTempParams* P, VistafTempPlan
 
 extern "C" void vistaf_temp_plan_destroy(VistafTempPlan* p) {
   if (!p) return;
+  vistaf_graph_drop(p);
   fft1d_destroy(&p->fw); fft1d_destroy(&p->fh);
   cudaFree(p->roi); cudaFree(p->models); cudaFree(p->lab_gamma); cudaFree(p->lab_cbrt);
   delete p;
@@ -1313,13 +1450,16 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   int* t10_frame = (int*)(ws + L.t10_frame);
   fa.t10_frame = t10_frame; fa.t10_stat = (unsigned int*)(ws + L.t10_stat);
   fa.wx0 = wn.x0; fa.wy0 = wn.y0; fa.ww = wn.w; fa.wh = wn.h;
+  fa.tile_x0 = 0; fa.tile_y0 = 0;
   VL(), k_t10_slots<<<1, 32, 0, st>>>(sc, nb, t10_frame, fa.t10_stat, ts);
   VL(), k_temp_features<false><<<dim3(cdiv(W, FT_W), cdiv(H, FT_H), nb), dim3(FT_W, FT_H), 0, st>>>(fa);
   CKL();
   vistaf_stage_mark("T.sat_telea_fill", st);
   {
     const dim3 gw(cdiv(wn.w, 256), wn.h, ts);
-    VL(), k_temp_features<true><<<dim3(cdiv(W, FT_W), cdiv(H, FT_H), ts), dim3(FT_W, FT_H), 0, st>>>(fa);
+    fa.tile_x0 = std::max(wn.x0, p->x0) / FT_W; fa.tile_y0 = std::max(wn.y0, p->y0) / FT_H;
+    const int tx1 = cdiv(std::min(wn.x0 + wn.w, p->x1), FT_W), ty1 = cdiv(std::min(wn.y0 + wn.h, p->y1), FT_H);
+    VL(), k_temp_features<true><<<dim3(tx1 - fa.tile_x0, ty1 - fa.tile_y0, ts), dim3(FT_W, FT_H), 0, st>>>(fa);
     VL(), k_t10_quant<<<gw, 256, 0, st>>>(fa);
     CKL();
     if (telea_inpaint(T10Mask{t10_frame, p->roi, sat, sc, (size_t)npix, W, wn.x0, wn.y0}, fa.t10_wide, (size_t)wn.h * wn.w,
@@ -1333,7 +1473,23 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   FusedLoad fl{fa.fused, plane, W};
   FinalStore fs{p->roi, fin, sc, plane, W, P.final_t_min, P.final_t_max, 0.0, 0.0, 3.0e38f, 0.f, 0u};
   const BlurWindow fwin{p->x0, p->x1, p->y0, p->y1, 0, 0, nullptr, nullptr, 0};      // the final map is NaN outside the ROI whatever the blur gives
+  // frames with a tilted carrier (status bit set by k_temp_peak_select) are compacted into slots first: the axis-aligned
+  // pass below skips their statistics, the warpAffine pass after it redoes their ROI
+  int* t12_frame = (int*)(ws + L.t12_frame);
+  unsigned int* t12_on = (unsigned int*)(t12_frame + ts);
+  VL(), k_t12_slots<<<1, 32, 0, st>>>(sc, nb, t12_frame, t12_on, ts);
   if (gauss_blur(fl, fs, tmp, H, W, nb, p->g_across, p->g_along, st, &fwin)) return 1;
+  {
+    // warp, blur, warp back over the full frame on slot planes carved from the illumination planes `norm` / `tmp`, free by
+    // now.  Every block of an empty slot returns at once.
+    VL(), k_t12_setup<<<nb, 1, 0, st>>>(sc, H, W);
+    VL(), k_t12_forward<<<dim3(cdiv(W, 256), H, ts), 256, 0, st>>>(fa.fused, norm, sc, t12_frame, H, W);
+    const BlurWindow gwin{0, W, 0, H, 0, H, nullptr, nullptr, sizeof(unsigned int), t12_on, 1u};
+    if (gauss_blur(T12Load{norm, plane, W}, T12Store{norm, plane, W}, tmp, H, W, ts, p->g_across, p->g_along, st, &gwin)) return 1;
+    VL(), k_t12_back<<<dim3(cdiv(p->x1 - p->x0, 256), p->y1 - p->y0, ts), 256, 0, st>>>(norm, p->roi, fin, sc, t12_frame, H, W, p->x0,
+                                                                                   p->x1, p->y0, P.final_t_min, P.final_t_max);
+    CKL();
+  }
   vistaf_stage_mark("T.stats_median", st);
   FinalVal fv{fin, p->roi, plane, (long long)p->y0 * W};
   const long long nsel = (long long)(p->y1 - p->y0) * W;
@@ -1349,15 +1505,21 @@ extern "C" int vistaf_temp_batch(VistafTempPlan* p, const uint8_t* frames, int b
                                  void* workspace, size_t ws_bytes, void* stream) {
   if (!p || !frames || !out || !out->fused || !out->final_map || !out->records || !workspace)
     return vistaf_set_err("vistaf_temp_batch: null argument", cudaErrorInvalidValue, __FILE__, __LINE__);
-  TempWs L1, L;
-  temp_layout(p, 1, L1);
-  int chunk = (int)(ws_bytes / L1.total) + 1;        // per-plane alignment padding makes layout(n) <= n*layout(1)
-  if (chunk > batch) chunk = batch;
-  while (chunk >= 1) { temp_layout(p, chunk, L); if (L.total <= ws_bytes) break; chunk--; }
+  TempWs L;
+  int chunk = batch;                                   // largest chunk the workspace holds, searched downward from the batch
+  while (chunk >= 1) { temp_layout(p, chunk, L); if (L.total <= ws_bytes) break; chunk = chunk > 8 ? chunk - (chunk + 15) / 16 : chunk - 1; }
   if (chunk < 1) return vistaf_set_err("vistaf_temp_batch: workspace too small for one frame", cudaErrorInvalidValue, __FILE__, __LINE__);
-  for (int f0 = 0; f0 < batch; f0 += chunk) {
-    int nb = batch - f0 < chunk ? batch - f0 : chunk;
-    if (temp_chunk(p, frames, nb, *out, (size_t)f0, (char*)workspace, L, (cudaStream_t)stream)) return 1;
-  }
-  return 0;
+  const VistafTempOutputs O = *out;
+  unsigned long long oh = 1469598103934665603ull;
+  for (size_t i = 0; i < sizeof(O); i++) { oh ^= ((const unsigned char*)&O)[i]; oh *= 1099511628211ull; }
+  const VistafGraphKey key = vistaf_graph_key(10, p, frames, batch, oh, O.fused, O.final_map, O.records, workspace, ws_bytes);
+  return vistaf_graph_run(key, (cudaStream_t)stream, [&](cudaStream_t st) {
+    for (int f0 = 0; f0 < batch; f0 += chunk) {
+      const int nb = batch - f0 < chunk ? batch - f0 : chunk;
+      TempWs Lc = L;
+      if (nb != chunk) temp_layout(p, nb, Lc);
+      if (temp_chunk(p, frames, nb, O, (size_t)f0, (char*)workspace, Lc, st)) return 1;
+    }
+    return 0;
+  });
 }

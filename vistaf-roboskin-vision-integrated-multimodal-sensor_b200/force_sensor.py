@@ -42,14 +42,13 @@ def ensure_dir(p: str):
     os.makedirs(p, exist_ok=True)
 
 
-def safe_float(x, fallback=np.nan):
+def safe_float(x, fallback=np.nan) -> float:
+    """float(x) when that is a finite number, else the fallback."""
     try:
         v = float(x)
-        if np.isfinite(v):
-            return v
-    except Exception:
-        pass
-    return float(fallback)
+    except (TypeError, ValueError):
+        return float(fallback)
+    return v if np.isfinite(v) else float(fallback)
 
 
 # ---------------------------------------------------------------- volume integration on the device

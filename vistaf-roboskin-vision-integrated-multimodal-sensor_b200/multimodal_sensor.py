@@ -15,7 +15,6 @@ rank 0.
 """
 from __future__ import annotations
 
-import glob
 import json
 import os
 import shutil
@@ -53,35 +52,22 @@ TEMP_SUBDIR = os.path.join(SESSION_DIR, "temperature_sensing")
 COMBINED_SUBDIR = os.path.join(SESSION_DIR, "combined_outputs")
 
 
-def ensure_dir(p: str):
-    os.makedirs(p, exist_ok=True)
+ensure_dir = force_sensor.ensure_dir
 
 
-def safe_float(x, fallback=np.nan):
-    try:
-        v = float(x)
-        if np.isfinite(v):
-            return v
-    except Exception:
-        pass
-    return float(fallback)
+safe_float = force_sensor.safe_float          # finite float or the fallback (one definition, force_sensor.py)
 
 
 def load_json_safe(path: str) -> Optional[Dict[str, Any]]:
-    if not os.path.exists(path):
-        print(f"[WARN] Calibration JSON not found: {path}")
-        return None
+    """A calibration-metrics JSON, or None (with a console note) when it is missing or unreadable."""
     try:
-        with open(path, "r", encoding="utf-8") as f:
-            return json.load(f)
-    except Exception as e:
+        with open(path, "r", encoding="utf-8") as fh:
+            return json.load(fh)
+    except FileNotFoundError:
+        print(f"[WARN] Calibration JSON not found: {path}")
+    except (OSError, ValueError) as e:
         print(f"[ERROR] Failed to load {path}: {e}")
-        return None
-
-
-def find_file_recursive(root_dir: str, filename: str) -> Optional[str]:
-    matches = glob.glob(os.path.join(root_dir, "**", filename), recursive=True)
-    return max(matches, key=os.path.getmtime) if matches else None
+    return None
 
 
 # ---------------------------------------------------------------- metric extraction (multimodal_sensor.py:214-281)
@@ -288,7 +274,7 @@ class MultimodalPlan:
 
     def step(self, ref_frame_dev, frames_dev, masks: bool = False, reuse_outputs: bool = True, ready=None, ref_ready=None) -> dict:
         """One batch against a (new) reference frame.  The reference-frame half (demodulation of one frame: a short,
-        latency-bound chain of kernels plus one small device->host read of the carrier peak) runs on a side stream
+        latency-bound chain of kernels; the carrier peak stays on the device) runs on a side stream
         while the temperature half of the batch runs on the current stream; the FTP batch follows both."""
         t = self.torch
         if self._side is None:
@@ -297,6 +283,8 @@ class MultimodalPlan:
             if self.ftp is not None:
                 gray = self.ftp.begin(frames_dev=frames_dev, ready=ready)
                 self.set_reference(ref_frame_dev)
+                for s in self.ftp.lane_streams:       # the reference is set asynchronously on the current stream
+                    s.wait_stream(t.cuda.current_stream())
                 B = int(frames_dev.shape[0])
                 key = (B, bool(masks))
                 cache = self._out.get(key) if reuse_outputs else None
@@ -319,7 +307,7 @@ class MultimodalPlan:
         with t.cuda.stream(self._side):
             if ref_ready is not None:
                 self._side.wait_event(ref_ready)
-            self.set_reference(ref_frame_dev)     # host returns when the side stream has the carrier
+            self.set_reference(ref_frame_dev)     # asynchronous: the carrier stays on the device
         main.wait_stream(self._side)
         for s in self.ftp.lane_streams:
             s.wait_stream(self._side)
@@ -327,10 +315,14 @@ class MultimodalPlan:
         main.wait_stream(tstream)
         return self._finish(res, B, cache, key, reuse_outputs)
 
-    def set_reference(self, ref_frame_dev):
-        """ref_frame_dev: uint8 CUDA [H,W,3] reference (undeformed) frame."""
+    def set_reference(self, ref_frame_dev, sync_info: bool = False):
+        """ref_frame_dev: uint8 CUDA [H,W,3] reference (undeformed) frame.  Asynchronous by default: the carrier stays on the
+        device (a reference without a carrier peak shows as ST_NO_PEAK in the frames' records)."""
         if self.ftp is not None:
-            return self.ftp.set_reference(self.ftp.crop_gray(ref_frame_dev[None])[0].contiguous())
+            if getattr(self, "_ref_gray", None) is None:       # fixed buffer: the same call is replayed from its CUDA graph
+                self._ref_gray = self.torch.empty((1, self.ftp.h, self.ftp.w), dtype=self.torch.uint8, device="cuda")
+            self.ftp.crop_gray(ref_frame_dev[None], out=self._ref_gray)
+            return self.ftp.set_reference(self._ref_gray[0], sync_info=sync_info)
 
     def run(self, frames_dev, masks: bool = False, reuse_outputs: bool = True, ready=None) -> dict:
         """frames_dev: uint8 CUDA [B,H,W,3].  Returns {"ftp": {...}, "temp": {...}, "records": uint8 [B,184]}."""
@@ -369,6 +361,21 @@ class MultimodalPlan:
         return res
 
 
+def _records_host(self, res, frames_dev) -> np.ndarray:
+    """Records of a finished step on the host (synchronises).  Temperature frames that found no T10 / T12 slot in their
+    chunk (ST_RERUN_ALONE: more than an eighth of a chunk saturated or tilted) are re-run alone first and patched into
+    `res`, so a caller of the batched API never consumes a frame that skipped a step."""
+    rec = records_to_numpy(res["records"])
+    if self.temp is not None and any(int(r["temp"]["status"]) & N.ST_RERUN_ALONE for r in rec):
+        self.temp.redo_flagged(frames_dev, res["temp"])
+        res["records"][:, 104:].copy_(res["temp"]["records"])
+        rec = records_to_numpy(res["records"])
+    return rec
+
+
+MultimodalPlan.records_host = _records_host
+
+
 def records_to_numpy(rec) -> np.ndarray:
     a = rec.cpu().numpy() if hasattr(rec, "cpu") else np.asarray(rec)
     return np.ascontiguousarray(a).view(RECORD_DTYPE).reshape(-1)
@@ -387,7 +394,7 @@ def run_batch(reference_bgr, frames_bgr, chunk: int = 8, masks: bool = False, mo
     plan = MultimodalPlan(int(fr.shape[1]), int(fr.shape[2]), chunk, chunk, mode)
     plan.set_reference(ref)
     out = plan.run(fr, masks=masks, reuse_outputs=False)
-    out["records_np"] = records_to_numpy(out["records"])
+    out["records_np"] = plan.records_host(out, fr)
     return out
 
 

@@ -62,6 +62,12 @@ BAD_INTENSITY_PERCENTILE = 99.9
 BAD_GRADIENT_PERCENTILE = 99.7
 BAD_DILATE_KSIZE = 5
 BAD_INPAINT_RADIUS = 3
+FILL_INTERNAL_HOLES_IN_RELIABLE = True
+HOLE_NEIGHBORHOOD_PX = 11
+HOLE_KNOWN_FRACTION = 0.70
+HOLE_MIN_DIST_FROM_RELIABLE_EDGE_PX = 4
+INPAINT_RADIUS = 5
+INPAINT_METHOD = "telea"
 CONTACT_CORE_PERCENTILE = 8.0
 CONTACT_PERCENTILE = 92
 DILATE_KERNEL_SIZE = 15
@@ -155,10 +161,15 @@ def _params(geom: dict, calibration_json: str, force_json: str) -> N.FtpParams:
     P.height_model = N.curve_model(model)
     P.force_model = N.curve_model(force_model["best_model"])
     P.grating_pitch_mm, P.depth_eps_mm = float(GRATING_PITCH_MM), float(DEPTH_EPS_MM)
+    if str(INPAINT_METHOD).lower() != "telea":
+        raise RuntimeError("B200 path implements INPAINT_METHOD='telea'")
+    P.fill_internal_holes, P.hole_neighborhood = int(bool(FILL_INTERNAL_HOLES_IN_RELIABLE)), int(HOLE_NEIGHBORHOOD_PX)
+    P.hole_known_frac, P.hole_min_dist = float(HOLE_KNOWN_FRACTION), float(HOLE_MIN_DIST_FROM_RELIABLE_EDGE_PX)
+    P.hole_inpaint_radius = int(INPAINT_RADIUS)
     return P
 
 
-MASK_NAMES = ("reliable", "output_reliable", "contact_dilated", "contact_kept")
+MASK_NAMES = ("reliable", "output_reliable", "contact_dilated", "contact_kept", "hole_candidates")
 
 
 class FtpPlan:
@@ -199,23 +210,25 @@ class FtpPlan:
     def _stream(self):
         return C.c_void_p(self.torch.cuda.current_stream().cuda_stream)
 
-    def crop_gray(self, frames_dev):
-        """cv2 BGR2GRAY of the ROI crop (shape_ftp.py:1508-1511): uint8 [B,H,W,3] -> uint8 [B,h,w]."""
+    def crop_gray(self, frames_dev, out=None):
+        """cv2 BGR2GRAY of the ROI crop (shape_ftp.py:1508-1511): uint8 [B,H,W,3] -> uint8 [B,h,w] (into `out` if given)."""
         t, g = self.torch, self.geom
         assert frames_dev.is_cuda and frames_dev.dtype == t.uint8 and frames_dev.is_contiguous()
         B = frames_dev.shape[0]
-        gray = t.empty((B, self.h, self.w), dtype=t.uint8, device="cuda")
+        gray = out if out is not None else t.empty((B, self.h, self.w), dtype=t.uint8, device="cuda")
         N.check(N.lib().vistaf_crop_gray(frames_dev.data_ptr(), B, self.H, self.W, g["x1"], g["y1"], self.h, self.w,
                                          gray.data_ptr(), self._stream()), "crop_gray")
         return gray
 
-    def set_reference(self, ref_gray_dev) -> N.FtpReferenceInfo:
-        """ref_gray_dev: uint8 CUDA [h,w] crop of the reference frame."""
+    def set_reference(self, ref_gray_dev, sync_info: bool = True):
+        """ref_gray_dev: uint8 CUDA [h,w] crop of the reference frame.  sync_info=True waits for the carrier and returns it
+        (VistafFtpReferenceInfo; raises when no carrier peak is found); False leaves the carrier on the device -- the
+        call is then asynchronous, and frames of a reference without a carrier come back with ST_NO_PEAK."""
         assert tuple(ref_gray_dev.shape) == (self.h, self.w) and ref_gray_dev.is_contiguous()
-        info = N.FtpReferenceInfo()
+        info = N.FtpReferenceInfo() if sync_info else None
         N.check(N.lib().vistaf_ftp_set_reference(self.handle, ref_gray_dev.data_ptr(), self.ref_ws.data_ptr(), self.ref_ws_bytes,
-                                                 C.byref(info), self._stream()), "ftp_set_reference")
-        self.ref_info = info
+                                                 C.byref(info) if sync_info else None, self._stream()), "ftp_set_reference")
+        self.ref_info = info if sync_info else True
         return info
 
     def masks(self):
@@ -328,7 +341,9 @@ def _config_key():
             RELIABLE_EDGE_MARGIN_PX, RELIABLE_SMOOTH_SIGMA_PX, FRONTIER_ZERO_BAND_PX, ILLUM_SIGMA_PX, VALID_CLOSE_KERNEL,
             BAD_INTENSITY_PERCENTILE, BAD_GRADIENT_PERCENTILE, BAD_DILATE_KSIZE, BAD_INPAINT_RADIUS,
             CONTACT_CORE_PERCENTILE, CONTACT_PERCENTILE, DILATE_KERNEL_SIZE, DILATE_ITERS, UNRELIABLE_SMOOTH_SIGMA_PX,
-            CONTACT_BLOB_MIN_PEAK_MM, CONTACT_BLOB_MIN_PEAK_REL_FRAC, CALIBRATION_JSON, FORCE_CALIBRATION_JSON)
+            CONTACT_BLOB_MIN_PEAK_MM, CONTACT_BLOB_MIN_PEAK_REL_FRAC, CALIBRATION_JSON, FORCE_CALIBRATION_JSON,
+            FILL_INTERNAL_HOLES_IN_RELIABLE, HOLE_NEIGHBORHOOD_PX, HOLE_KNOWN_FRACTION, HOLE_MIN_DIST_FROM_RELIABLE_EDGE_PX,
+            INPAINT_RADIUS)
 
 
 def get_plan(H: int, W: int, chunk: int = 8) -> FtpPlan:
@@ -464,9 +479,8 @@ def main(reference_path=None, deformed_path=None, output_dir=None, calibration_j
             f = np.full((H, W), fill, dtype)
             f[y1:y2, x1:x2] = a
             return f
-        hole = np.zeros_like(roi_eroded)
         crop_masks = {"roi_eroded": roi_eroded, "reliable": m["reliable"], "output_reliable": m["output_reliable"],
-                      "circ_mask": circ_mask, "contact_kept_by_depth": m["contact_kept"], "hole_candidates": hole,
+                      "circ_mask": circ_mask, "contact_kept_by_depth": m["contact_kept"], "hole_candidates": m["hole_candidates"],
                       "contact_dilated": m["contact_dilated"]}
         export_heightmap_files(OUTPUT_DIR, HEIGHTMAP_EXPORT_BASENAME, height, full(height, np.nan, np.float32), crop_masks,
                                {k: full(v) for k, v in crop_masks.items()},

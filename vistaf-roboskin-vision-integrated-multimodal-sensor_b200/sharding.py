@@ -58,7 +58,11 @@ def run_sharded(plan, make_frames, n_frames: int, step_frames: int = 64, group=N
     parts = []
     for a in range(lo, hi, step_frames):
         b = min(hi, a + step_frames)
-        parts.append(plan.run(make_frames(a, b), masks=masks, reuse_outputs=False)["records"])
+        frames = make_frames(a, b)
+        res = plan.run(frames, masks=masks, reuse_outputs=False)
+        if hasattr(plan, "records_host"):
+            plan.records_host(res, frames)        # re-runs frames that found no T10 / T12 slot (ST_RERUN_ALONE)
+        parts.append(res["records"])
     width = parts[0].shape[1] if parts else 184
     local = torch.cat(parts, dim=0) if parts else torch.zeros((0, width), dtype=torch.uint8, device="cuda")
     return gather_records(local, n_frames, 0, group)

@@ -34,16 +34,20 @@ def _palette():
     return _PAL
 
 
-def frame_params(seed: int, reference: bool = False, amp_max: float = 1.3) -> dict:
-    """Scene parameters drawn from default_rng(seed); the reference frame has no indentation."""
+def frame_params(seed: int, reference: bool = False, amp_max: float = 1.3, sigma_min: float = 60.0,
+                 dT_max: float = 10.0) -> dict:
+    """Scene parameters drawn from default_rng(seed); the reference frame has no indentation.  The keyword ranges
+    widen single draws without changing the draw sequence, so the default frames keep their bytes: amp_max up to
+    3 pi brings wrap counts k != 0 into the unwrap, sigma_min keeps the carrier deviation inside
+    the +-10-bin patch for such amplitudes, dT_max = 35 reaches the 32-34 degC blend band of the fusion."""
     rng = np.random.default_rng(int(seed) + (1 << 20 if reference else 0))
     ang = rng.uniform(0, 2 * np.pi)
     rad = rng.uniform(0, 250.0)
     p = dict(
         A=0.0 if reference else float(rng.uniform(0.1, amp_max)),
-        sigma=float(rng.uniform(60.0, 160.0)),
+        sigma=float(rng.uniform(sigma_min, 160.0)),
         x0=float(DISC_C[0] + rad * np.cos(ang)), y0=float(DISC_C[1] + rad * np.sin(ang)),
-        T0=float(rng.uniform(20.5, 28.0)), dT=float(rng.uniform(0.0, 10.0)),
+        T0=float(rng.uniform(20.5, 28.0)), dT=float(rng.uniform(0.0, dT_max)),
         sT=float(rng.uniform(150.0, 400.0)),
         tx=float(DISC_C[0] + rng.uniform(-300, 300)), ty=float(DISC_C[1] + rng.uniform(-300, 300)),
         glare=(not reference) and (int(seed) % 16 == 15),
@@ -54,9 +58,10 @@ def frame_params(seed: int, reference: bool = False, amp_max: float = 1.3) -> di
     return p
 
 
-def make_frame(seed: int, reference: bool = False, amp_max: float = 1.3, h: int = H, w: int = W) -> np.ndarray:
-    """BGR uint8 (h, w, 3)."""
-    p = frame_params(seed, reference, amp_max)
+def make_frame(seed: int, reference: bool = False, amp_max: float = 1.3, h: int = H, w: int = W,
+               sigma_min: float = 60.0, dT_max: float = 10.0, tilt_deg: float = 0.0) -> np.ndarray:
+    """BGR uint8 (h, w, 3).  tilt_deg rotates the stripes (carrier angle != 0: the oriented blur of T12)."""
+    p = frame_params(seed, reference, amp_max, sigma_min, dT_max)
     rng = np.random.default_rng(p["noise_seed"])
     img = np.full((h, w, 3), 25.0, np.float32)
     # work inside the disc's bounding box only
@@ -66,7 +71,11 @@ def make_frame(seed: int, reference: bool = False, amp_max: float = 1.3, h: int 
     r2 = (xx - DISC_C[0]) ** 2 + (yy - DISC_C[1]) ** 2
     inside = r2 <= DISC_R ** 2
     phi = -p["A"] * np.exp(-((xx - p["x0"]) ** 2 + (yy - p["y0"]) ** 2) / (2.0 * p["sigma"] ** 2))
-    theta = (2.0 * np.pi / PERIOD_PX) * xx + phi
+    if tilt_deg:
+        ct, st = np.float32(np.cos(np.deg2rad(tilt_deg))), np.float32(np.sin(np.deg2rad(tilt_deg)))
+        theta = (2.0 * np.pi / PERIOD_PX) * (xx * ct + (yy - DISC_C[1]) * st) + phi
+    else:
+        theta = (2.0 * np.pi / PERIOD_PX) * xx + phi
     wl = 0.5 * (1.0 + np.tanh(np.sin(theta) / (2.0 * np.pi * 3.0 / PERIOD_PX)))      # light-stripe weight
     T = p["T0"] + p["dT"] * np.exp(-((xx - p["tx"]) ** 2 + (yy - p["ty"]) ** 2) / (2.0 * p["sT"] ** 2))
     pt, pl, pd = _palette()

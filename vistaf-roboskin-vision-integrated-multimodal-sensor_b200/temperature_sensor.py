@@ -206,6 +206,22 @@ class TempPlan:
             cur.wait_stream(s)
         return out
 
+    def redo_flagged(self, frames_dev, out) -> np.ndarray:
+        """T10 (saturated frames) and the warpAffine path of T12 (tilted carrier) run on at most an eighth of a chunk's
+        frames; a frame beyond that comes back with ST_RERUN_ALONE.  Here such frames are run again alone (a one-frame
+        chunk always has a slot) and patched into `out`.  Reads the records, i.e. synchronises; returns them as numpy."""
+        rec = records_to_numpy(out["records"])
+        redo = [i for i, r in enumerate(rec) if int(r["status"]) & N.ST_RERUN_ALONE]
+        if redo:
+            one = get_plan(self.h, self.w, 1)
+            masks = all(k in out for k in MASK_NAMES)
+            for i in redo:
+                o1 = one.run(frames_dev[i:i + 1].contiguous(), masks=masks)
+                for k, v in o1.items():
+                    out[k][i:i + 1].copy_(v)
+            rec = records_to_numpy(out["records"])
+        return rec
+
 
 def get_plan(h: int, w: int, chunk: int = 8) -> TempPlan:
     key = (h, w, chunk, OUTER_CIRCLE_P1, OUTER_CIRCLE_P2, OUTER_CIRCLE_P3, SEG_BAND_RADIUS, SEG_DC_EXCLUSION,
@@ -229,17 +245,7 @@ def run_batch(frames_bgr, chunk: int = 8, masks: bool = True) -> dict:
         frames_bgr = t.from_numpy(np.ascontiguousarray(frames_bgr)).pin_memory().cuda(non_blocking=True)
     plan = get_plan(int(frames_bgr.shape[1]), int(frames_bgr.shape[2]), chunk)
     out = plan.run(frames_bgr, masks=masks)
-    out["records_np"] = records_to_numpy(out["records"])
-    # T10 runs on at most an eighth of a chunk's frames; a frame beyond that comes back with ST_SAT_UNFILLED and is redone
-    # here on its own (a one-frame chunk always has a slot), so the synchronous wrapper never returns an unfilled frame.
-    redo = [i for i, r in enumerate(out["records_np"]) if int(r["status"]) & N.ST_SAT_UNFILLED]
-    if redo:
-        one = get_plan(int(frames_bgr.shape[1]), int(frames_bgr.shape[2]), 1)
-        for i in redo:
-            o1 = one.run(frames_bgr[i:i + 1].contiguous(), masks=masks)
-            for k, v in o1.items():
-                out[k][i:i + 1].copy_(v)
-        out["records_np"] = records_to_numpy(out["records"])
+    out["records_np"] = plan.redo_flagged(frames_bgr, out)     # frames that found no T10 / T12 slot are redone alone
     return out
 
 
