@@ -206,6 +206,10 @@ class TempPlan:
             cur.wait_stream(s)
         return out
 
+    def roi_bbox(self):
+        """(y0, y1, x0, x1) of the outer ROI in frame coordinates (no padding)."""
+        return bbox_from_mask(roi_mask_from_circle(self.h, self.w, OUTER_CIRCLE_P1, OUTER_CIRCLE_P2, OUTER_CIRCLE_P3), pad=0)
+
     def redo_flagged(self, frames_dev, out) -> np.ndarray:
         """T10 (saturated frames) and the warpAffine path of T12 (tilted carrier) run on at most an eighth of a chunk's
         frames; a frame beyond that comes back with ST_RERUN_ALONE.  Here such frames are run again alone (a one-frame
