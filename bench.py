@@ -33,7 +33,7 @@ sys.path.insert(0, PKG)
 METRIC = "multimodal frames/sec (FTP+force+temp) at 1/2/4/8 B200; % HBM roofline"
 # algorithmic bytes per frame (a property of the work, not of the implementation), and their split
 # over the pipeline stages the library marks with CUDA events (DESIGN.md "Stage table").  MB per frame.
-B_ALG = {"temperature": 1000e6, "ftp": 760e6, "multimodal": 1760e6}
+B_ALG = {"temperature": 1000e6, "ftp": 760e6, "multimodal": 1760e6, "ftp4k": 8300e6}
 STAGE_MB = {
     "F.crop_gray": 5.6, "F.sobel_percentiles_bad": 9.1, "F.telea_inpaint": 3.5, "F.illum_blur45": 22.4,
     "F.preblur_apo_median": 11.2, "F.carrier_dft_field": 109.0, "F.quality_reliable_mask": 35.0,
@@ -87,6 +87,36 @@ def _cpu_init():
     import ftp_oracle as FO
     import temperature_oracle as TO
     _W.update(cv2=cv2, S=S, FO=FO, TO=TO, frames={})
+
+
+def _cpu4k_prepare(seed):
+    if not _W:
+        _cpu_init()
+    S, FO = _W["S"], _W["FO"]
+    if "refp4k" not in _W:
+        g = S.CROP4K
+        P = FO.FtpParams(apply_global_shift=False, use_ecc=False)
+        disc = FO.disc(g["h"], g["w"], g["cx"], g["cy"], g["r"])
+        geom = dict(g, circ=disc, roi=disc, apo=FO.apodization(g["h"], g["w"], g["cx"], g["cy"], g["r"], P.apod_taper))
+        ref = S.make_crop4k(0, reference=True)
+        _W.update(P4k=P, geom4k=geom, ref4k=ref, refp4k=FO.reference_products(ref, geom, P), crops={})
+    if seed not in _W["crops"]:
+        _W["crops"][seed] = S.make_crop4k(seed)
+    return seed
+
+
+def _cpu4k_process(args):
+    seed, _ = args
+    _cpu4k_prepare(seed)
+    FO = _W["FO"]
+    t = time.perf_counter()
+    r = FO.ftp_pair(_W["ref4k"], _W["crops"][seed], _W["geom4k"], _W["P4k"], ref=_W["refp4k"])
+    out = {"seed": seed}
+    if r is not None:
+        fr = FO.force_readings(r)
+        out.update(force_N=fr["force_N"], volume_cm3=fr["volume_cm3"], reliable_px=int(r["reliable"].sum()),
+                   output_reliable_px=int(r["output_reliable"].sum()), contact_dilated_px=int(r["contact_dilated"].sum()))
+    return time.perf_counter() - t, out
 
 
 def _cpu_prepare(seed):
@@ -204,6 +234,10 @@ class CpuArm:
         self.frames = int(frames_per_step or self.workers)
         self.workload, self.kind = workload, kind
         self._prep, self._proc = (_ref_prepare, _ref_process) if kind == "reference" else (_cpu_prepare, _cpu_process)
+        if workload == "ftp4k":               # 3904^2 crops: ~45 s and a few GB per frame and process
+            self._prep, self._proc = _cpu4k_prepare, _cpu4k_process
+            self.workers = int(workers or max(1, min(avail, 8)))
+            self.frames = int(frames_per_step or self.workers)
         self.pool = mp.get_context("spawn").Pool(self.workers, initializer=_ref_init if kind == "reference" else _cpu_init)
         self.seeds = list(range(1, self.frames + 1))
         self.pool.map(self._prep, self.seeds, chunksize=max(1, self.frames // self.workers))     # untimed: generation + reference products
@@ -229,7 +263,7 @@ class CpuArm:
 
 
 def run_reference(a, config):
-    kind = "reference" if have_reference() and not a.cpu_port else "port"
+    kind = "reference" if have_reference() and not a.cpu_port and a.workload != "ftp4k" else "port"   # the reference's ROI constants are fixed
     arm = CpuArm(a.workload, a.cpu_workers, a.cpu_frames, kind)
     try:
         # bounded sample: the reference needs ~45 s per frame and process (pure-Python heap unwrap), so one frame per
@@ -270,7 +304,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default=os.environ.get("VISTAF_WORKLOAD", "multimodal"),
-                    choices=["multimodal", "ftp", "temperature"])
+                    choices=["multimodal", "ftp", "temperature", "ftp4k"])
     ap.add_argument("--frames", type=int, default=256, help="frames per GPU per step")
     ap.add_argument("--chunk", type=int, default=256, help="FTP frames per library chunk (workspace size)")
     ap.add_argument("--chunk-temp", type=int, default=64, help="temperature frames per library chunk")
@@ -305,6 +339,8 @@ def main():
         emit(run_reference(a, config))
         return
 
+    if a.workload == "ftp4k":
+        return main_ftp4k(a, rank, world, local)
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -550,6 +586,136 @@ def main():
                         + abs(int(t["color_ok_pixels"]) - o["color_ok_px"])
             par["bars"] = {"force_rel": 1e-3, "T_abs_C": 1e-2, "mask_px": 0}
             par["ok"] = bool(par["frames"] > 0 and par["max_rel_force"] <= 1e-3 and par["max_abs_T"] <= 1e-2)
+            line["parity"] = par
+        emit(line)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main_ftp4k(a, rank, world, local):
+    """BASELINE.json configs[4]: FTP-only on 3904^2 gray crops (4096^2 FFT grid), phase amplitude up to 3 pi, frames
+    streamed in steps of F crops per GPU: the reference crop is demodulated every step, the crops are staged from pinned
+    host memory on a copy stream while the previous step computes (e2e), or resident (value)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import synthetic as S
+    import _native as N
+    import shape_ftp as SF
+    import sharding as SH
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    F = a.frames if a.frames != 256 else 32
+    nd = min(8, max(1, a.distinct))
+    g = S.CROP4K
+    config = {"workload": f"ftp4k: {F} synthetic 3904x3904 gray fringe crops per GPU per step ({nd} distinct seeds per rank tiled to "
+                          f"the batch; phase amplitude up to 3 pi, wrap counts != 0) against one reference crop, FFT grid 4096^2, "
+                          f"ROI radius 1951 px; FTP + force only",
+              "frames_per_gpu": F, "lanes_ftp": 2, "resolution": "3904x3904 crop",
+              "l2": f"inputs {F * 15.2:.0f} MB per step, larger than the 126 MB L2 (no flush needed)"}
+    seeds = [rank * 100003 + s + 21 for s in range(nd)]
+    host = np.stack([S.make_crop4k(sd) for sd in seeds])
+    pinned = torch.from_numpy(host).pin_memory()
+    ref_pinned = torch.from_numpy(S.make_crop4k(0, reference=True)).pin_memory()
+    dev = pinned.cuda().repeat((F + nd - 1) // nd, 1, 1)[:F].contiguous()
+    ref_dev = ref_pinned.cuda()
+    plan = SF.FtpPlan(g["h"], g["w"], chunk=F, lanes=2, geom=g)
+    out = {"height_mm": torch.empty((F, g["h"], g["w"]), dtype=torch.float32, device="cuda"),
+           "records": torch.empty((F, 104), dtype=torch.uint8, device="cuda")}
+    for k in SF.MASK_NAMES:
+        out[k] = torch.empty((F, g["h"], g["w"]), dtype=torch.uint8, device="cuda")
+
+    def gather(rec):
+        return SH.gather_records(rec, world * F, 0) if world > 1 else rec
+
+    def step(frames, ref):
+        gray = plan.begin(def_gray_dev=frames)
+        plan.set_reference(ref, sync_info=False)
+        for s in plan.lane_streams:
+            s.wait_stream(torch.cuda.current_stream())
+        return gather(plan.run(gray, masks=True, out=out)["records"])
+
+    dev2, ref2 = torch.empty_like(dev), torch.empty_like(ref_dev)
+
+    def step_e2e():
+        ref2.copy_(ref_pinned, non_blocking=True)
+        for c in range(0, F, nd):
+            n = min(nd, F - c)
+            dev2[c:c + n].copy_(pinned[:n], non_blocking=True)
+        r = step(dev2, ref2)
+        return r.cpu() if r is not None else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    W = max(a.warmup, 3)
+    for _ in range(W):
+        step(dev, ref_dev)
+    stop, samples = threading.Event(), []
+    th = threading.Thread(target=clocks_sampler, args=(stop, samples, world), daemon=True) if rank == 0 else None
+    if th:
+        th.start()
+    l0 = N.launch_count()
+    ms = timed(lambda: step(dev, ref_dev), a.steps)
+    launches = N.launch_count() - l0
+    stop.set()
+    if th:
+        th.join()
+    step_e2e()
+    e2e_steps = max(1, a.steps // 2)
+    ms_e2e = timed(step_e2e, e2e_steps)
+    rec = step(dev, ref_dev)
+    if rank == 0:
+        recs = SF.records_to_numpy(out["records"])
+        fps, fps_e2e = world * F * a.steps / (ms / 1000.0), world * F * e2e_steps / (ms_e2e / 1000.0)
+        pk_path = os.path.join(REPO, "MEASURED_PEAKS.json")
+        peaks = json.load(open(pk_path)) if os.path.exists(pk_path) else {}
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        ach = B_ALG["ftp4k"] * (fps / world) / 1e9
+        line = {"metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": a.steps, "warmup": W,
+                "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": config, "clocks": summarize_clocks(samples),
+                "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": int(dev.numel() + ref_dev.numel()),
+                        "d2h_bytes_per_step": int(out["records"].numel())},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                             "kernel": "whole pipeline (every kernel of the step)", "alg_bytes_per_frame": B_ALG["ftp4k"],
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy bandwidth)" if peaks else "fallback from B200_PROFILING.md"},
+                "check": {"force_N_first": float(recs[0]["force_N"]), "status_or": int(np.bitwise_or.reduce(recs["status"])),
+                          "residue_frames": int((recs["residues"] > 0).sum())}}
+        if world == 1 and not a.no_cpu:
+            arm = CpuArm("ftp4k", a.cpu_workers, a.cpu_frames)
+            arm.seeds = seeds[:arm.frames]
+            try:
+                arm.pool.map(arm._prep, arm.seeds)
+                dt = arm.step()
+            finally:
+                arm.close()
+            line["cpu_baseline"] = {"value": len(arm.seeds) / dt, "unit": "frames/s", "cores": arm.workers, "kind": "port",
+                                    "sample": arm.describe(dt, 1)}
+            par = {"frames": 0, "max_rel_force": 0.0, "mask_px_diff": 0}
+            for o in arm.readings:
+                i = seeds.index(o["seed"])
+                if "force_N" in o:
+                    par["frames"] += 1
+                    par["max_rel_force"] = max(par["max_rel_force"], abs(float(recs[i]["force_N"]) - o["force_N"]) / max(1e-9, abs(o["force_N"])))
+                    par["mask_px_diff"] += abs(int(recs[i]["reliable_px"]) - o["reliable_px"]) + abs(int(recs[i]["contact_dilated_px"]) - o["contact_dilated_px"])
             line["parity"] = par
         emit(line)
     if world > 1:

@@ -550,9 +550,11 @@ def ftp_pair(ref_gray, def_gray, geom, P=None, ref=None, keep=False):
         contact = (abs_res >= float(t)) & rel & np.isfinite(abs_res)
         frac = contact.sum() / max(1, rel.sum())
         if frac < P.min_contact_frac:
-            contact = (abs_res >= float(pct(abs_res, 95, rel, t))) & rel & np.isfinite(abs_res)
+            t = pct(abs_res, 95, rel, t)
+            contact = (abs_res >= float(t)) & rel & np.isfinite(abs_res)
         elif frac > P.max_contact_frac:
-            contact = (abs_res >= float(pct(abs_res, 98, rel, t))) & rel & np.isfinite(abs_res)
+            t = pct(abs_res, 98, rel, t)
+            contact = (abs_res >= float(t)) & rel & np.isfinite(abs_res)
     contact_d = (cv2.dilate(contact.astype(np.uint8) * 255, ellipse(P.dilate_kernel), iterations=P.dilate_iters) > 0) & rel
     bg = rel & ~contact_d
     if bg.sum() < int(0.15 * rel.sum()):
@@ -593,7 +595,8 @@ def ftp_pair(ref_gray, def_gray, geom, P=None, ref=None, keep=False):
                peak_f=ref["peak_f"])
     if keep:
         res.update(wrapped=wrapped, quality=quality, unwrapped=unw, height_unitless=hf_, cdef=de["c"],
-                   cref=ref["c"], bad_def=de["bad"], Iw_def=de["Iw"], img_inp_def=de["img_inpainted"], hm=hm)
+                   cref=ref["c"], bad_def=de["bad"], Iw_def=de["Iw"], img_inp_def=de["img_inpainted"], hm=hm,
+                   abs_res=abs_res, contact_thr=float(t))
     return res
 
 

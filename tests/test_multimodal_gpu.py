@@ -99,16 +99,14 @@ def test_lane_step_matches_oracle_on_one_frame(env):
     P = FO.FtpParams(apply_global_shift=False, use_ecc=False)
     g = FO.geometry(H, W, P)
     crop = lambda f: cv2.cvtColor(f[g["y1"]:g["y2"], g["x1"]:g["x2"]], cv2.COLOR_BGR2GRAY)
-    fo = FO.ftp_pair(crop(ref), crop(frames[i]), g, P)
+    fo = FO.ftp_pair(crop(ref), crop(frames[i]), g, P, keep=True)
     hm = out["ftp"]["height_mm"][i].cpu().numpy()
-    assert np.array_equal(np.isnan(hm), np.isnan(fo["height_mm"]))
-    assert float(np.nanmax(np.abs(hm - fo["height_mm"]))) <= 1e-3          # mm (north_star tolerance)
-    # Masks on THIS seed (not one of the seeds the bit-exact parity tests pin): thresholds applied to float fields leave a
-    # handful of isolated tie pixels (|value - threshold| below float32 rounding of the blur / fit sums) that flip with
-    # the summation order of any implementation -- measured 0..5 px per 1.4 M-px mask over seeds 2..11.
-    TIE_PX = 8
-    for k in ("reliable", "output_reliable", "contact_dilated", "contact_kept"):
-        assert int((out["ftp"][k][i].cpu().numpy().astype(bool) != fo[k]).sum()) <= TIE_PX, k
+    # Masks on THIS seed (not one of the seeds the bit-exact parity tests pin): identical except pixels PROVEN to be
+    # threshold ties (|value - threshold| <= 32 float32 ulps in the oracle's own field, tests/parity_util.py), and the
+    # height within 1e-3 mm (north_star tolerance) everywhere outside the frontier neighbourhood of such a tie.
+    from parity_util import check_ftp_masks
+    gm = {k: out["ftp"][k][i].cpu().numpy().astype(bool) for k in ("reliable", "output_reliable", "contact_dilated", "contact_kept")}
+    print("tie statistics:", check_ftp_masks(gm, hm, fo, P))
     to = TO.temperature_frame(frames[i])
     fin = out["temp"]["final"][i].cpu().numpy()
     assert np.array_equal(np.isnan(fin), np.isnan(to["final"]))

@@ -78,6 +78,7 @@ __global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* 
   const int b = blockIdx.z, y = blockIdx.y, x0 = blockIdx.x * BLUR_ROW_SEG;
   if (y < win.ry0 || y >= win.ry1 || x0 >= win.x1 + 32 || x0 + BLUR_ROW_SEG <= win.x0 - 32) return;
   if (blur_gated_off(win, b)) return;
+  if (blur_gated_off(win, b)) return;
   const int rad = g.ksize >> 1;
   const int need = BLUR_ROW_SEG + g.kpad + 8;
   // inputs of outputs nobody reads (farther than the kernel radius from the window grown by one column block) stay 0

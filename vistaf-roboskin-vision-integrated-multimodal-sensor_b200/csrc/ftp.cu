@@ -1295,7 +1295,7 @@ __global__ void __launch_bounds__(256) k_depth_reduce(const float* __restrict__ 
 }
 
 __global__ void k_ftp_records(const FtpScal* sc, VistafFtpRecord* rec, int n, int w, const PeakResult* pr, int N, double pitch_mm,
-                              VistafCurveModel force_model) {
+                              VistafCurveModel force_model, int count_outrel) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const FtpScal& s = sc[i];
@@ -1313,7 +1313,7 @@ __global__ void k_ftp_records(const FtpScal* sc, VistafFtpRecord* rec, int n, in
   }
   r.force_N = curve_eval(force_model, r.volume_cm3);
   r.amp_thr = s.amp_thr; r.contact_thr = s.contact_thr; r.bg_median = s.bg_med; r.core_median = s.core_med;
-  r.reliable_px = (int)s.n_rel; r.output_reliable_px = (int)s.n_outrel; r.contact_dilated_px = (int)s.n_contact_d;
+  r.reliable_px = (int)s.n_rel; r.output_reliable_px = (int)(count_outrel ? s.n_outrel : s.n_rel); r.contact_dilated_px = (int)s.n_contact_d;
   r.contact_kept_px = (int)s.n_kept; r.bad_px = (int)s.n_bad; r.residues = (int)s.residues;
   if (s.seed_key) {
     const unsigned int idx = 0xffffffffu - (unsigned int)(s.seed_key & 0xffffffffull);
@@ -1767,14 +1767,21 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   CKL();
   vistaf_stage_mark("F.internal_holes", st);
   // ---- F14: internal holes (gated: no frame of the shipped configuration has any), output_reliable
-  uint8_t* outrel = O.output_reliable ? O.output_reliable + f0 * (size_t)npix : m2;
-  uint8_t* cand = O.hole_candidates ? O.hole_candidates + f0 * (size_t)npix : contact;
   // with the reliable smoothing on, masked_gaussian_smooth (num / (den + 1e-6)) is finite on every pixel: no hole can
-  // exist and only output_reliable (= reliable) is written
-  if (O.hole_candidates && P.smooth_sigma > 0.f) CK(cudaMemsetAsync(cand, 0, (size_t)npix * nb, st));
-  if (ftp_fill_holes(p, hm, rel, outrel, cand, O.hole_candidates != nullptr, hnum, dist_in, dtmp, ws + L.telea, (int*)(ws + L.active),
-                     sc, sel, nb, st, !(P.smooth_sigma > 0.f)))
-    return 1;
+  // exist, output_reliable IS reliable and the stage is one copy of the mask when the caller asked for it
+  const uint8_t* outrel = rel;
+  if (P.smooth_sigma > 0.f) {
+    if (O.hole_candidates) CK(cudaMemsetAsync(O.hole_candidates + f0 * (size_t)npix, 0, (size_t)npix * nb, st));
+    if (O.output_reliable && O.output_reliable + f0 * (size_t)npix != rel)
+      CK(cudaMemcpyAsync(O.output_reliable + f0 * (size_t)npix, rel, (size_t)npix * nb, cudaMemcpyDeviceToDevice, st));
+  } else {
+    uint8_t* orl = O.output_reliable ? O.output_reliable + f0 * (size_t)npix : m2;
+    uint8_t* cand = O.hole_candidates ? O.hole_candidates + f0 * (size_t)npix : contact;
+    if (ftp_fill_holes(p, hm, rel, orl, cand, O.hole_candidates != nullptr, hnum, dist_in, dtmp, ws + L.telea, (int*)(ws + L.active),
+                       sc, sel, nb, st, true))
+      return 1;
+    outrel = orl;
+  }
   vistaf_stage_mark("F.chamfer_frontier_assemble", st);
   // ---- F: frontier taper, assembly, sigma-9 fill of the unreliable part, phase -> mm (on output_reliable, :1803-1841)
   if (chamfer_dt2(NotMaskZero{outrel, plane, w}, dist_in, dtmp, MaskZero{outrel, plane, w}, dist_out, (unsigned int*)sm, h, w, nb, st))
@@ -1796,7 +1803,7 @@ static int ftp_chunk(VistafFtpPlan* p, const uint8_t* gray_all, int nb, const Vi
   VL(), k_depth_reduce<<<dim3(64, nb), 256, 0, st>>>(out, nullptr, &sc[0].pos_sum, &sc[0].neg_sum, sizeof(FtpScal), &sc[0].vol_sum,
                                                &sc[0].vol_cnt, &sc[0].vol_max_bits, npix, (float)P.depth_eps_mm);
   VL(), k_ftp_records<<<cdiv(nb, 128), 128, 0, st>>>(sc, O.records + f0, nb, w, (const PeakResult*)p->peak_result, p->N,
-                                                P.grating_pitch_mm, P.force_model);
+                                                P.grating_pitch_mm, P.force_model, P.smooth_sigma > 0.f ? 0 : 1);
   CKL();
   vistaf_stage_mark("", st);
   return 0;

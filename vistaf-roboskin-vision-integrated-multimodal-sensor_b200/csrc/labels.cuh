@@ -177,7 +177,7 @@ static int uf_label(Fg fg, Edge edge, ull* uf, unsigned int* area, unsigned int*
 #define CH_DG 89739u      // round(1.3693 * 65536)
 #define CH_INF 0x1fffffffu
 #define CH_THREADS 512
-#define CH_MAXPT 4        // pixels per thread -> rows up to 2048
+#define CH_MAXPT 8        // pixels per thread -> rows up to 4096 (the 3904^2 streaming geometry of configs[4])
 
 __device__ __forceinline__ int block_prefix_min(int v, int* sh) {   // inclusive, in thread order
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;

@@ -176,10 +176,13 @@ class FtpPlan:
     """Owns the opaque library plan, its torch workspace for `chunk` frames and the cached reference frame."""
 
     def __init__(self, H: int, W: int, chunk: int = 8, calibration_json: Optional[str] = None,
-                 force_json: Optional[str] = None, lanes: int = 1):
+                 force_json: Optional[str] = None, lanes: int = 1, geom: Optional[dict] = None):
+        """geom: explicit crop geometry {h, w, cx, cy, r[, x1, y1]} for callers that bring their own gray crops (the
+        3904^2 / 4096^2-FFT streaming geometry of BASELINE.json configs[4]); default: the fixed 3-point circle in an
+        H x W camera frame (shape_ftp.py:1494-1516)."""
         self.torch = N.require_cuda()
         self.H, self.W, self.chunk = int(H), int(W), int(chunk)
-        self.geom = crop_geometry(H, W)
+        self.geom = dict(geom) if geom is not None else crop_geometry(H, W)
         self.h, self.w = self.geom["h"], self.geom["w"]
         self.params = _params(self.geom, calibration_json or CALIBRATION_JSON, force_json or FORCE_CALIBRATION_JSON)
         self.handle = C.c_void_p()

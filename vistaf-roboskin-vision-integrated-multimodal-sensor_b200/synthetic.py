@@ -93,3 +93,29 @@ def make_frame(seed: int, reference: bool = False, amp_max: float = 1.3, h: int 
 
 def make_batch(seeds, **kw) -> np.ndarray:
     return np.stack([make_frame(s, **kw) for s in seeds], axis=0)
+
+
+# ---------------------------------------------------------------- configs[4]: 4K-upscaled fringe crops (FTP only)
+CROP4K = dict(h=3904, w=3904, cx=1952, cy=1952, r=1951)        # 1182-px crop x 3.303; + 2 x 96 px of padding = 4096^2 FFT
+SCALE4K = 3904.0 / 1182.0
+
+
+def make_crop4k(seed: int, reference: bool = False, amp_max: float = float(3 * np.pi), size: int = 3904) -> np.ndarray:
+    """uint8 gray crop (size, size) of the skin disc upscaled by 3.303: stripes of period 65.84 x 3.303 px
+    phase-modulated by a Gaussian indentation of up to 3 pi rad (wrap counts k != 0), two grey levels with the same
+    illumination fall-off and noise model as make_frame.  Generated directly as the gray crop the FTP chain consumes."""
+    p = frame_params(seed, reference, amp_max, sigma_min=130.0)
+    rng = np.random.default_rng(p["noise_seed"])
+    sc = size / 1182.0
+    c = (size - 1) / 2.0
+    yy, xx = np.mgrid[0:size, 0:size].astype(np.float32)
+    r2 = (xx - c) ** 2 + (yy - c) ** 2
+    x0, y0 = c + (p["x0"] - DISC_C[0]) * sc, c + (p["y0"] - DISC_C[1]) * sc
+    phi = -p["A"] * np.exp(-((xx - x0) ** 2 + (yy - y0) ** 2) / (2.0 * (p["sigma"] * sc) ** 2))
+    theta = (2.0 * np.pi / (PERIOD_PX * sc)) * xx + phi
+    wl = 0.5 * (1.0 + np.tanh(np.sin(theta) / (2.0 * np.pi * 3.0 / PERIOD_PX)))
+    illum = 1.0 + 0.15 * np.cos(np.sqrt(r2) / (DISC_R * sc) * (np.pi / 2.0))
+    img = (60.0 + 95.0 * wl) * illum
+    img = np.where(r2 <= (DISC_R * sc) ** 2, img, 25.0).astype(np.float32)
+    img += 2.0 * rng.standard_normal((size, size), dtype=np.float32)
+    return np.clip(np.rint(img), 0, 255).astype(np.uint8)
