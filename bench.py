@@ -417,22 +417,28 @@ def main():
     box = (tb.roi_bbox() if tb is not None else None)
     pin = {}
 
+    out_stream = torch.cuda.Stream()
+
     def step_e2e_maps():
+        """e2e + the maps: device-side snapshots of the height crops and of the ROI window of both temperature maps are
+        copied to pinned host memory on a copy-out stream, so the transfer of step n overlaps the compute of step n+1
+        (the snapshot frees the plan's reused output buffers at once; the pinned buffers are the consumer's)."""
         res, rec = step_e2e()
         main = torch.cuda.current_stream()
+        snap = {}
         if "ftp" in res:
-            h = res["ftp"]["height_mm"]
-            if "height" not in pin:
-                pin["height"] = torch.empty(h.shape, dtype=h.dtype).pin_memory()
-            pin["height"].copy_(h, non_blocking=True)
+            snap["height"] = res["ftp"]["height_mm"].clone()
         if "temp" in res:
             y0, y1, x0, x1 = box
             for k in ("fused", "final"):
-                c = res["temp"][k][:, y0:y1, x0:x1].contiguous()
+                snap[k] = res["temp"][k][:, y0:y1, x0:x1].contiguous()
+        out_stream.wait_stream(main)
+        with torch.cuda.stream(out_stream):
+            for k, v in snap.items():
                 if k not in pin:
-                    pin[k] = torch.empty(c.shape, dtype=c.dtype).pin_memory()
-                pin[k].copy_(c, non_blocking=True)
-        main.synchronize()
+                    pin[k] = torch.empty(v.shape, dtype=v.dtype).pin_memory()
+                pin[k].copy_(v, non_blocking=True)
+                v.record_stream(out_stream)
         return rec
 
     def barrier():
@@ -442,7 +448,7 @@ def main():
 
     host_ms = [0.0]
 
-    def timed(fn, steps):
+    def timed(fn, steps, tail=None):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -450,6 +456,8 @@ def main():
         for _ in range(steps):
             fn()
         host_ms[0] = (time.perf_counter() - t0) * 1e3 / steps      # host time to ENQUEUE one step (no sync inside; includes launch-queue back-pressure)
+        if tail is not None:
+            tail()                                                 # e.g. the timed stream waits for the last copy-out
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
@@ -491,7 +499,8 @@ def main():
     ms_maps = None
     if not a.no_maps:
         step_e2e_maps()
-        ms_maps = timed(step_e2e_maps, e2e_steps)
+        torch.cuda.synchronize()
+        ms_maps = timed(step_e2e_maps, e2e_steps, tail=lambda: torch.cuda.current_stream().wait_stream(out_stream))
     res = plan.step(ref_dev, dev, masks=True)
     gathered = gather(res)
     rec = res["records"]

@@ -51,6 +51,7 @@ struct TempScal {             // per-frame scalars living in the workspace
   int t10_slot;                 // T10 slot of a saturated frame (-1: none free, the fill is skipped and flagged)
   unsigned int wmin_key, wmax_key, pad2;      // ordered keys of min / max of the raw wide-model map over roi_eff
   double aff_f[6], aff_b[6];    // T12 on a tilted carrier: dst -> src maps of the forward / backward warpAffine
+  unsigned int peak_floor, pad3;  // bits of a lower bound of the frame's 16th largest |F| (raised by the column blocks as they finish)
 };
 
 struct VistafTempPlan {
@@ -264,7 +265,7 @@ __device__ __forceinline__ bool dc_excluded(int x, int y, int h, int w, int dc) 
 // Column pass over the half spectrum + fused |F| and per-block top-16 (the dense spectrum is never
 // written: only the band around the carrier is needed later and is recomputed from A).
 __global__ void __launch_bounds__(512) k_temp_fft_cols_peaks(const float2* __restrict__ A, Cand* __restrict__ cand,
-                                                              Fft1D p, int w, int wh, int dc) {
+                                                              Fft1D p, int w, int wh, int dc, TempScal* sc) {
   extern __shared__ float2 sm[];
   const int n = p.n, lds = n + 1, b = blockIdx.y, c0 = blockIdx.x * COLS_PER_BLOCK;
   const int nc = min(COLS_PER_BLOCK, wh - c0);
@@ -321,6 +322,20 @@ __global__ void __launch_bounds__(512) k_temp_fft_cols_peaks(const float2* __res
   float mv[COLS_PT];
 #pragma unroll
   for (int j = 0; j < COLS_PT; j++) { const int t = threadIdx.x + j * COLS_THREADS; mv[j] = t < tot ? mag[t] : -3.f; }
+  // A block that has found 16 bins raises the frame's floor to its 16th largest magnitude: the frame's final 16th
+  // largest is at least that.  A block none of whose bins reaches the floor cannot contribute to the top 16 and skips
+  // the extraction (the low-|kx| blocks, scheduled first, hold the large magnitudes: almost every later block skips).
+  // The RESULT does not depend on the order the blocks run in, only the amount of work does.
+  {
+    const float floor_m = __uint_as_float(*(volatile unsigned int*)&sc[b].peak_floor);
+    int any = 0;
+#pragma unroll
+    for (int j = 0; j < COLS_PT; j++) any |= mv[j] >= floor_m;
+    if (!__syncthreads_or(any)) {
+      if (threadIdx.x < TOPK) { Cand cd; cd.mag = -1.f; cd.kx = -1; cd.ky = -1; cd.pad = 0; out[threadIdx.x] = cd; }
+      return;
+    }
+  }
   for (int round = 0; round < TOPK; round++) {
     float best = -4.f;
     int bt = 0x7fffffff;
@@ -369,6 +384,7 @@ __global__ void __launch_bounds__(512) k_temp_fft_cols_peaks(const float2* __res
         if (best >= 0.f) { const int c = bt / n; cd.kx = c0 + c; cd.ky = bt - c * n; }
         else { cd.kx = -1; cd.ky = -1; cd.mag = -1.f; }
         out[round] = cd;
+        if (round == TOPK - 1 && best > 0.f) atomicMax(&sc[b].peak_floor, __float_as_uint(best));
       }
     }
   }
@@ -1397,7 +1413,7 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   VL(), k_temp_fft_rows<<<dim3(cdiv(H, 2), nb), 256, (size_t)W * 16, st>>>(norm, A, sc, p->fw, H, Wh);
   vistaf_stage_mark("T.fft_cols_peaks", st);
   VL(), k_temp_fft_cols_peaks<<<dim3(p->nblk_cols, nb), COLS_THREADS, (size_t)COLS_PER_BLOCK * (H + 1) * 16, st>>>(A, cand, p->fh, W, Wh,
-                                                                                                  P.dc_exclusion);
+                                                                                                  P.dc_exclusion, sc);
   const int ncand = p->nblk_cols * TOPK;
   VL(), k_temp_peak_select<<<nb, 256, (size_t)2 * ncand * 4, st>>>(cand, sc, ncand, H, W, P.dc_exclusion, P.peak_max_dy_frac);
   CKL();
