@@ -97,6 +97,10 @@ typedef struct {
   uint8_t* color_ok;
   uint8_t* source;     /* 0 wide / 128 blend / 255 colour (debug_fused_source.png) */
   VistafTempRecord* records; /* [B] */
+  int32_t background_valid;  /* != 0: every map / mask plane above already holds its background (NaN / 0) outside the ROI
+                                bounding box -- e.g. the same buffers were filled by an earlier call of this plan -- so the
+                                ~76 % of each plane that lies outside the box is not written again */
+  int32_t pad_;
 } VistafTempOutputs;
 
 typedef struct VistafTempPlan VistafTempPlan;

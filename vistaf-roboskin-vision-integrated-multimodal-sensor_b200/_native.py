@@ -59,7 +59,7 @@ assert TEMP_RECORD_DTYPE.itemsize == C.sizeof(TempRecord) == 80
 
 class TempOutputs(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("fused", "final_map", "sat", "dark", "light", "color_support",
-                                          "color_ok", "source", "records")]
+                                          "color_ok", "source", "records")] + [("background_valid", C.c_int32), ("pad_", C.c_int32)]
 
 
 # ------------------------------------------------------------------ FTP shape + force path (include/vistaf.h)

@@ -43,13 +43,16 @@ static inline MorphSE se_rect(int kx, int ky) {
 #define MORPH_TH 128
 template <bool DILATE, class Load, class Post>
 __global__ void __launch_bounds__(128) k_morph(Load ld, Post post, uint8_t* __restrict__ dst, int h, int w, MorphSE se,
-                                               int4 win) {   // win = (x0, x1, y0, y1): the input is known to be 0 outside it
+                                               int4 win, int skip_out) {   // win = (x0, x1, y0, y1): the input is known to be 0 outside it
+  // skip_out: tiles whose whole neighbourhood lies outside the window are not written (their zeros are either never read:
+  // the loads below substitute 0 outside the window, or already in place: an output plane with a valid background)
   __shared__ unsigned long long Wd[MORPH_TH + MORPH_MAXROWS - 1];
   __shared__ unsigned int Rw[MORPH_TH];
   const int ry = se.rows / 2, nrow = MORPH_TH + se.rows - 1;
   const int b = blockIdx.z, x0 = blockIdx.x * MORPH_TW, y0 = blockIdx.y * MORPH_TH;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   if (x0 - 16 >= win.y || x0 + MORPH_TW + 16 <= win.x || y0 - ry >= win.w || y0 + MORPH_TH + ry <= win.z) {
+    if (skip_out) return;
     for (int ty = wid; ty < MORPH_TH; ty += 4) {     // all-zero neighbourhood: dilation and erosion both give 0
       const int y = y0 + ty, x = x0 + lane;
       if (y < h && x < w) dst[(size_t)b * h * w + (size_t)y * w + x] = (uint8_t)post(b, y, x, 0);
@@ -64,7 +67,7 @@ __global__ void __launch_bounds__(128) k_morph(Load ld, Post post, uint8_t* __re
     for (int hf = 0; hf < 2; hf++) {
       const int x = x0 - 16 + hf * 32 + lane;
       int v = DILATE ? 0 : 1;                       // border value
-      if (yin && x >= 0 && x < w) v = ld(b, y, x);
+      if (yin && x >= 0 && x < w) v = (x >= win.x && x < win.y && y >= win.z && y < win.w) ? ld(b, y, x) : 0;
       word[hf] = __ballot_sync(0xffffffffu, v != 0);
     }
     if (lane == 0) Wd[ty] = (unsigned long long)word[0] | ((unsigned long long)word[1] << 32);
@@ -96,13 +99,13 @@ __global__ void __launch_bounds__(128) k_morph(Load ld, Post post, uint8_t* __re
 
 template <bool DILATE, class Load, class Post>
 static int morph(Load ld, Post post, uint8_t* dst, int h, int w, int batch, const MorphSE& se, cudaStream_t st,
-                 const int4* window = nullptr) {
+                 const int4* window = nullptr, bool skip_outside = false) {
   for (int i = 0; i < se.rows; i++)
     if (se.half[i] > 16) return vistaf_set_err("morph: structuring element wider than 33", cudaErrorInvalidValue, __FILE__, __LINE__);
   if (se.rows > MORPH_MAXROWS) return vistaf_set_err("morph: structuring element taller than 33", cudaErrorInvalidValue, __FILE__, __LINE__);
   dim3 grid(cdiv(w, MORPH_TW), cdiv(h, MORPH_TH), batch);
   const int4 win = window ? *window : make_int4(0, w, 0, h);
-  VL(), k_morph<DILATE, Load, Post><<<grid, 128, 0, st>>>(ld, post, dst, h, w, se, win);
+  VL(), k_morph<DILATE, Load, Post><<<grid, 128, 0, st>>>(ld, post, dst, h, w, se, win, window && skip_outside ? 1 : 0);
   CKL();
   return 0;
 }

@@ -587,27 +587,32 @@ __global__ void __launch_bounds__(256) k_temp_ifft_rows(const float2* __restrict
 // A / B split by the sign of s = Re(z e^{-i phi0}) over roi_eff, and the mean gray of both classes
 // (temperature_sensor.py:475-489), from the analytic signal stored by k_temp_ifft_rows<1>.  maskA is written over
 // the ROI bounding box only (its readers test the ROI first).
+#define SPLIT_ROWS 8            // rows per block: one float64 block reduction per 8 x 256 pixels instead of per 256
 __global__ void __launch_bounds__(256) k_temp_split(const float2* __restrict__ Z, const uint8_t* __restrict__ gray8,
                                                      const uint8_t* __restrict__ roi, const uint8_t* __restrict__ sat,
                                                      uint8_t* __restrict__ maskA, TempScal* sc, int h, int w, int ybeg, int zx0,
                                                      int zw, int zrows) {
   __shared__ double red[4 * 32];
-  const int b = blockIdx.z, ry = blockIdx.y, y = ybeg + ry, xx = blockIdx.x * 256 + threadIdx.x;
+  const int b = blockIdx.z, xx = blockIdx.x * 256 + threadIdx.x;
   TempScal& S = sc[b];
   const bool has_sat = S.sat_raw_count != 0;
   const double cs = S.rot_c, sn = S.rot_s;
   double v[4] = {0.0, 0.0, 0.0, 0.0};
   if (xx < zw) {
     const int x = zx0 + xx;
-    const size_t row = (size_t)y * w, fr = (size_t)b * h * w;
-    int mA = 0;
-    if (roi[row + x] && !(has_sat && sat[fr + row + x])) {
-      const float2 z = Z[((size_t)b * zrows + ry) * zw + xx];
-      const float s = (float)((double)z.x * cs + (double)z.y * sn);
-      const float g = (float)gray8[fr + row + x];
-      if (s >= 0.f) { mA = 1; v[0] += g; v[1] += 1.0; } else { v[2] += g; v[3] += 1.0; }
+    const size_t fr = (size_t)b * h * w;
+    const int r1 = min(zrows, ((int)blockIdx.y + 1) * SPLIT_ROWS);
+    for (int ry = blockIdx.y * SPLIT_ROWS; ry < r1; ry++) {
+      const size_t row = (size_t)(ybeg + ry) * w;
+      int mA = 0;
+      if (roi[row + x] && !(has_sat && sat[fr + row + x])) {
+        const float2 z = Z[((size_t)b * zrows + ry) * zw + xx];
+        const float s = (float)((double)z.x * cs + (double)z.y * sn);
+        const float g = (float)gray8[fr + row + x];
+        if (s >= 0.f) { mA = 1; v[0] += g; v[1] += 1.0; } else { v[2] += g; v[3] += 1.0; }
+      }
+      maskA[fr + row + x] = (uint8_t)mA;
     }
-    maskA[fr + row + x] = (uint8_t)mA;
   }
   block_sum<4>(v, red);
   if (threadIdx.x == 0 && (v[1] != 0.0 || v[3] != 0.0)) {
@@ -732,7 +737,8 @@ struct FeatArgs {
   // T10 (saturated frames that own a slot): raw wide-model map and clamped colour map on the ROI window
   float *t10_wide, *t10_color; const int* t10_frame; unsigned int* t10_stat;
   int wx0, wy0, ww, wh;
-  int tile_x0, tile_y0;          // first tile of the launch grid (T10 instance: only the tiles over the ROI window are launched)
+  int tile_x0, tile_y0;          // first tile of the launch grid (only the tiles over the ROI window are launched then)
+  int skip_background;           // the output planes already hold NaN / 0 outside the ROI bounding box
 };
 
 // fusion of the wide and colour maps at one pixel (temperature_sensor.py:594-641); wide / colour are clamped already
@@ -768,12 +774,12 @@ __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
   __shared__ uint8_t tile[(FT_H + 4) * (FT_W + 4) * 3];
   const int b = T10 ? a.t10_frame[blockIdx.z] : (int)blockIdx.z;
   if (T10 && b < 0) return;
-  const int x0 = ((int)blockIdx.x + (T10 ? a.tile_x0 : 0)) * FT_W, y0 = ((int)blockIdx.y + (T10 ? a.tile_y0 : 0)) * FT_H, h = a.h, w = a.w;
+  const int x0 = ((int)blockIdx.x + a.tile_x0) * FT_W, y0 = ((int)blockIdx.y + a.tile_y0) * FT_H, h = a.h, w = a.w;
   const size_t plane = (size_t)h * w;
   const uint8_t* img = a.frames + (size_t)b * plane * 3;
   const int tid = threadIdx.y * FT_W + threadIdx.x;
   if (x0 >= a.bx1 || x0 + FT_W <= a.bx0 || y0 >= a.by1 || y0 + FT_H <= a.by0) {
-    if (T10) return;
+    if (T10 || a.skip_background) return;
     const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
     if (x < w && y < h) {
       const size_t bi = (size_t)b * plane + (size_t)y * w + x;
@@ -985,7 +991,7 @@ struct FusedLoad {
 };
 struct FinalStore {
   const uint8_t* roi; float* out; TempScal* sc; long long plane; int w; float lo, hi;
-  double s1, s2; float mn, mx; unsigned int cnt;
+  double s1, s2; float mn, mx; unsigned int cnt; int skip_bg;
   __device__ void operator()(int b, int y, int x, float v) {
     long long i = (long long)y * w + x;
     float r = __int_as_float(0x7fc00000);
@@ -997,7 +1003,9 @@ struct FinalStore {
     }
     out[(long long)b * plane + i] = r;
   }
-  __device__ void outside(int b, int y, int x, float) { out[(long long)b * plane + (long long)y * w + x] = __int_as_float(0x7fc00000); }
+  __device__ void outside(int b, int y, int x, float) {
+    if (!skip_bg) out[(long long)b * plane + (long long)y * w + x] = __int_as_float(0x7fc00000);
+  }
   __device__ void finish(int b) {
     __shared__ double sh[3 * 32];
     __shared__ float shm[2 * 32];
@@ -1429,7 +1437,7 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   VL(), k_temp_ifft_rows<1><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R,
                                                                       Z, p->x0, zw, nrows);
   VL(), k_temp_phi0<<<nb, 1, 0, st>>>(sc);
-  VL(), k_temp_split<<<dim3(cdiv(zw, 256), nrows, nb), 256, 0, st>>>(Z, gray8, p->roi, sat, maskA, sc, H, W, p->y0, p->x0, zw, nrows);
+  VL(), k_temp_split<<<dim3(cdiv(zw, 256), cdiv(nrows, SPLIT_ROWS), nb), 256, 0, st>>>(Z, gray8, p->roi, sat, maskA, sc, H, W, p->y0, p->x0, zw, nrows);
   VL(), k_temp_choose_dark<<<nb, 1, 0, st>>>(sc);
   CKL();
   vistaf_stage_mark("T.morph_close_open", st);
@@ -1439,10 +1447,13 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   uint8_t* dark = O.dark ? O.dark + f0 * (size_t)npix : maskA;      // final dark mask destination
   // every plane of this chain is 0 outside the ROI bounding box grown by the structuring elements (<= 15 + 3 rows)
   const int4 mwin = make_int4(p->x0 - 24, p->x1 + 24, p->y0 - 24, p->y1 + 24);
-  if (morph<true>(dl, PostId(), m1, H, W, nb, se_c, st, &mwin)) return 1;
-  if (morph<false>(MaskLoad{m1, plane, W}, PostId(), m2, H, W, nb, se_c, st, &mwin)) return 1;
-  if (morph<false>(MaskLoad{m2, plane, W}, PostId(), m1, H, W, nb, se_o, st, &mwin)) return 1;
-  if (morph<true>(MaskLoad{m1, plane, W}, PostRoiEff{p->roi, sat, sc, plane, W}, dark, H, W, nb, se_o, st, &mwin)) return 1;
+  // (the scratch planes m1 / m2 are never read outside the window: their far tiles are not written at all; the output
+  // plane keeps its zeros there when the caller says its background is valid)
+  const bool bg_ok = O.background_valid != 0;
+  if (morph<true>(dl, PostId(), m1, H, W, nb, se_c, st, &mwin, true)) return 1;
+  if (morph<false>(MaskLoad{m1, plane, W}, PostId(), m2, H, W, nb, se_c, st, &mwin, true)) return 1;
+  if (morph<false>(MaskLoad{m2, plane, W}, PostId(), m1, H, W, nb, se_o, st, &mwin, true)) return 1;
+  if (morph<true>(MaskLoad{m1, plane, W}, PostRoiEff{p->roi, sat, sc, plane, W}, dark, H, W, nb, se_o, st, &mwin, O.dark ? bg_ok : true)) return 1;
   vistaf_stage_mark("T.features_models_fuse", st);
   // features, models, fusion
   FeatArgs fa;
@@ -1466,9 +1477,14 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   int* t10_frame = (int*)(ws + L.t10_frame);
   fa.t10_frame = t10_frame; fa.t10_stat = (unsigned int*)(ws + L.t10_stat);
   fa.wx0 = wn.x0; fa.wy0 = wn.y0; fa.ww = wn.w; fa.wh = wn.h;
-  fa.tile_x0 = 0; fa.tile_y0 = 0;
+  fa.tile_x0 = 0; fa.tile_y0 = 0; fa.skip_background = bg_ok ? 1 : 0;
   VL(), k_t10_slots<<<1, 32, 0, st>>>(sc, nb, t10_frame, fa.t10_stat, ts);
-  VL(), k_temp_features<false><<<dim3(cdiv(W, FT_W), cdiv(H, FT_H), nb), dim3(FT_W, FT_H), 0, st>>>(fa);
+  if (bg_ok) {                  // only the tiles over the ROI bounding box
+    fa.tile_x0 = p->x0 / FT_W; fa.tile_y0 = p->y0 / FT_H;
+    VL(), k_temp_features<false><<<dim3(cdiv(p->x1, FT_W) - fa.tile_x0, cdiv(p->y1, FT_H) - fa.tile_y0, nb), dim3(FT_W, FT_H), 0, st>>>(fa);
+  } else {
+    VL(), k_temp_features<false><<<dim3(cdiv(W, FT_W), cdiv(H, FT_H), nb), dim3(FT_W, FT_H), 0, st>>>(fa);
+  }
   CKL();
   vistaf_stage_mark("T.sat_telea_fill", st);
   {
@@ -1487,7 +1503,7 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   // oriented smoothing (axis aligned) + statistics
   float* fin = O.final_map + f0 * (size_t)npix;
   FusedLoad fl{fa.fused, plane, W};
-  FinalStore fs{p->roi, fin, sc, plane, W, P.final_t_min, P.final_t_max, 0.0, 0.0, 3.0e38f, 0.f, 0u};
+  FinalStore fs{p->roi, fin, sc, plane, W, P.final_t_min, P.final_t_max, 0.0, 0.0, 3.0e38f, 0.f, 0u, bg_ok ? 1 : 0};
   const BlurWindow fwin{p->x0, p->x1, p->y0, p->y1, 0, 0, nullptr, nullptr, 0};      // the final map is NaN outside the ROI whatever the blur gives
   // frames with a tilted carrier (status bit set by k_temp_peak_select) are compacted into slots first: the axis-aligned
   // pass below skips their statistics, the warpAffine pass after it redoes their ROI

@@ -174,8 +174,13 @@ class TempPlan:
             if masks:
                 for k in MASK_NAMES:
                     out[k] = t.empty((B, self.h, self.w), dtype=t.uint8, device="cuda")
+        # output planes filled once by this plan keep their background (NaN / 0 outside the ROI bounding box): later calls on
+        # the same buffers tell the library not to write those three quarters of every plane again
+        bg_valid = int(bool(out.get("_background_written")))
+
         def call(lo, hi, ws, stream):
             O = N.TempOutputs()
+            O.background_valid = bg_valid
             O.fused, O.final_map, O.records = out["fused"][lo:].data_ptr(), out["final"][lo:].data_ptr(), out["records"][lo:].data_ptr()
             for k in MASK_NAMES:
                 setattr(O, k, out[k][lo:].data_ptr() if k in out else None)
@@ -187,6 +192,7 @@ class TempPlan:
         if L == 1 or B < 2 * L:
             N.wait_ready(cur, ready, 0, B)
             call(0, B, self.ws, cur)
+            out["_background_written"] = True
             return out
         per = -(-B // L)
         used = []
@@ -204,6 +210,7 @@ class TempPlan:
             used.append(s)
         for s in used:
             cur.wait_stream(s)
+        out["_background_written"] = True
         return out
 
     def roi_bbox(self):
@@ -222,7 +229,8 @@ class TempPlan:
             for i in redo:
                 o1 = one.run(frames_dev[i:i + 1].contiguous(), masks=masks)
                 for k, v in o1.items():
-                    out[k][i:i + 1].copy_(v)
+                    if hasattr(v, "shape"):
+                        out[k][i:i + 1].copy_(v)
             rec = records_to_numpy(out["records"])
         return rec
 
