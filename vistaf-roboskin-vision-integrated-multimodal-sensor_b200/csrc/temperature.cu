@@ -112,24 +112,30 @@ __global__ void k_temp_gray(const uint8_t* __restrict__ frames, const uint8_t* _
 }
 
 // dilate(sat, ellipse k) & roi — only when the frame has saturated pixels (temperature_sensor.py:381-386)
+#define SATD_ROWS 8
 __global__ void k_temp_sat_dilate(const uint8_t* __restrict__ satraw, const uint8_t* __restrict__ roi,
-                                  uint8_t* __restrict__ sat, TempScal* sc, int h, int w, MorphSE se) {
+                                  uint8_t* __restrict__ sat, TempScal* sc, int h, int w, MorphSE se, int y0, int y1) {
   const int b = blockIdx.z;
-  if (sc[b].sat_raw_count == 0) return;
-  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (sc[b].sat_raw_count == 0) return;             // the plane is never read for such a frame (sat_at)
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
   const bool inb = x < w;
   const uint8_t* s = satraw + (size_t)b * h * w;
-  int v = 0;
-  if (inb && roi[(size_t)y * w + x]) {
-    for (int i = 0; i < se.rows && !v; i++) {
-      int yy = y + i - se.rows / 2;
-      if (yy < 0 || yy >= h || se.half[i] < 0) continue;
-      for (int xx = max(0, x - se.half[i]); xx <= min(w - 1, x + se.half[i]); xx++)
-        if (s[(size_t)yy * w + xx]) { v = 1; break; }
+  int c = 0;
+  // rows [y0, y1) = the ROI bounding box: the mask is `& roi`, and its readers test the ROI first
+  for (int y = y0 + (int)blockIdx.y * SATD_ROWS; y < min(y1, y0 + ((int)blockIdx.y + 1) * SATD_ROWS); y++) {
+    int v = 0;
+    if (inb && roi[(size_t)y * w + x]) {
+      for (int i = 0; i < se.rows && !v; i++) {
+        int yy = y + i - se.rows / 2;
+        if (yy < 0 || yy >= h || se.half[i] < 0) continue;
+        for (int xx = max(0, x - se.half[i]); xx <= min(w - 1, x + se.half[i]); xx++)
+          if (s[(size_t)yy * w + xx]) { v = 1; break; }
+      }
     }
+    if (inb) sat[(size_t)b * h * w + (size_t)y * w + x] = (uint8_t)v;
+    c += v;
   }
-  if (inb) sat[(size_t)b * h * w + (size_t)y * w + x] = (uint8_t)v;
-  int c = warp_sum(v);
+  c = warp_sum(c);
   if ((threadIdx.x & 31) == 0 && c) atomicAdd(&sc[b].sat_count, (unsigned)c);
 }
 
@@ -139,7 +145,7 @@ __device__ __forceinline__ bool sat_at(const TempScal& s, const uint8_t* sat, si
 
 // histogram of gray over roi_eff -> exact median of integer-valued float32 (temperature_sensor.py:446-447)
 __global__ void k_temp_hist(const uint8_t* __restrict__ gray8, const uint8_t* __restrict__ roi,
-                            const uint8_t* __restrict__ sat, TempScal* sc, int npix) {
+                            const uint8_t* __restrict__ sat, TempScal* sc, int npix, int i0, int i1) {   // pixels [i0, i1): the ROI rows
   __shared__ unsigned int h[256];
   const int b = blockIdx.y;
   for (int i = threadIdx.x; i < 256; i += blockDim.x) h[i] = 0;
@@ -147,7 +153,7 @@ __global__ void k_temp_hist(const uint8_t* __restrict__ gray8, const uint8_t* __
   const uint8_t* g = gray8 + (size_t)b * npix;
   const uint8_t* s = sat + (size_t)b * npix;
   const bool has_sat = sc[b].sat_raw_count != 0;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x)
+  for (int i = i0 + blockIdx.x * blockDim.x + threadIdx.x; i < i1; i += gridDim.x * blockDim.x)
     if (roi[i] && !(has_sat && s[i])) atomicAdd(&h[g[i]], 1u);
   __syncthreads();
   for (int i = threadIdx.x; i < 256; i += blockDim.x)
@@ -1400,8 +1406,9 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   vistaf_stage_mark("T.gray_sat_median", st);
   VL(), k_temp_init<<<cdiv(nb, 128), 128, 0, st>>>(sc, nb);
   VL(), k_temp_gray<<<dim3(cdiv(npix / 4, 256), nb), 256, 0, st>>>(fr, p->roi, gray8, satraw, sc, npix, P.sat_thresh);
-  VL(), k_temp_sat_dilate<<<dim3(cdiv(W, 256), H, nb), 256, 0, st>>>(satraw, p->roi, sat, sc, H, W, p->se_sat);
-  VL(), k_temp_hist<<<dim3(296, nb), 256, 0, st>>>(gray8, p->roi, sat, sc, npix);
+  VL(), k_temp_sat_dilate<<<dim3(cdiv(W, 256), cdiv(p->y1 - p->y0, SATD_ROWS), nb), 256, 0, st>>>(satraw, p->roi, sat, sc, H, W, p->se_sat,
+                                                                                         p->y0, p->y1);
+  VL(), k_temp_hist<<<dim3(296, nb), 256, 0, st>>>(gray8, p->roi, sat, sc, npix, p->y0 * W, p->y1 * W);
   VL(), k_temp_median<<<nb, 32, 0, st>>>(sc);
   CKL();
   vistaf_stage_mark("T.illum_blur20", st);
