@@ -13,7 +13,7 @@ timeout 600 ncu --target-processes application-only --metrics gpu__time_duration
   --log-file gpurun_out/r02_multimodal_launches.csv python bench.py $ARGS > gpurun_out/prof_list.log 2>&1; echo "ncu list rc=$?"
 wc -l gpurun_out/r02_multimodal_launches.csv
 K='k_uf_merge|k_uf_flatten|k_ftp_unwrap_apply|k_ftp_unwrap_heap|k_chamfer2|k_ftp_field|k_ftp_rowdft|k_temp_fft_cols_peaks|k_temp_fft_rows|k_temp_ifft_rows|k_temp_split|k_temp_band|k_temp_features|k_irls_accum|k_irls_compact|k_blur_cols|k_blur_rows|k_sel_s1|k_sel_s2|k_morph|k_ftp_assemble|k_t12_forward'
-timeout 700 ncu --target-processes application-only --set full --clock-control none --kernel-name regex:"$K" --launch-skip 150 --launch-count 66 \
+timeout 700 ncu --target-processes application-only --set full --clock-control none --kernel-name regex:"$K" --launch-skip 150 --launch-count 44 \
   -f -o gpurun_out/r02_full python bench.py $ARGS > gpurun_out/prof_full.log 2>&1; echo "ncu full rc=$?"
 ls -la gpurun_out/*.ncu-rep 2>/dev/null
 # summaries are made on the box (the report itself may exceed what gpurun copies back)
