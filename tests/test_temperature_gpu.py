@@ -175,3 +175,28 @@ def test_fully_saturated_frame_is_flagged_and_isolated(mods):
     assert bool(((f_pair == a) | (f_pair.isnan() & a.isnan())).all())
     assert torch.equal(d_pair, alone["dark"][0])
     assert r_pair == alone["records_np"][0].tobytes()
+
+
+def test_workspace_for_n_frames_runs_them_in_one_chunk(mods):
+    """vistaf_temp_workspace_bytes(plan, n) must let vistaf_temp_batch process n frames as ONE chunk (the first round's chunk
+    search started from ws / layout(1) and split 32 frames into 23 + 9): the kernel-launch count of a batch of 6 in a
+    workspace sized for 6 equals that of a batch of 3 in a workspace sized for 3."""
+    import ctypes as C
+    import torch
+    import _native as N
+    S, TS, TO = mods
+    N.check(N.lib().vistaf_set_graphs(0))
+    try:
+        fr = torch.from_numpy(np.stack([S.make_frame(3)] * 6)).cuda()
+        counts = []
+        for n in (3, 6):
+            plan = TS.TempPlan(fr.shape[1], fr.shape[2], chunk=n)
+            plan.run(fr[:n].contiguous(), masks=False)
+            torch.cuda.synchronize()
+            l0 = N.launch_count()
+            plan.run(fr[:n].contiguous(), masks=False)
+            torch.cuda.synchronize()
+            counts.append(N.launch_count() - l0)
+        assert counts[0] == counts[1], counts
+    finally:
+        N.check(N.lib().vistaf_set_graphs(1))

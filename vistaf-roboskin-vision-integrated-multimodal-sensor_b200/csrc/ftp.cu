@@ -340,6 +340,21 @@ __device__ __forceinline__ float2 tw_inv(const float2* __restrict__ tw, int f, i
 // Inverse of the re-centred patch on the un-padded rows/columns, fractional ramp (:955-961), and either
 //   REF: store the reference field and its amplitude (:990-997), or
 //   DEF: ratio with the reference field -> wrapped phase (:1681-1689) and amp_ref * amp_def (:741).
+// The twiddle of tap f at position X is table entry (|f| X) mod N, conjugated for f >= 0 (tw_inv): walking f = -half ..
+// half, the index moves by -(X mod N) down to 0 and by +(X mod N) up again, so one modulo per pixel replaces one 64-bit
+// multiply + modulo per tap; the entries read are the same ones.
+struct TwWalk {
+  int idx, s, N, f;
+  __device__ TwWalk(int half, int X, int N_) : s(X % N_), N(N_), f(-half) { idx = (int)(((long long)half * s) % N_); }
+  __device__ __forceinline__ float2 next(const float2* __restrict__ tw) {
+    float2 t = __ldg(tw + idx);
+    if (f >= 0) t.y = -t.y;
+    if (f < 0) { idx -= s; if (idx < 0) idx += N; }
+    else { idx += s; if (idx >= N) idx -= N; }
+    f++;
+    return t;
+  }
+};
 template <bool REF>
 __global__ void __launch_bounds__(256) k_ftp_field(const float2* __restrict__ Pw, const float2* __restrict__ tw,
                                                     const float2* __restrict__ rampx, const float2* __restrict__ rampy,
@@ -351,9 +366,10 @@ __global__ void __launch_bounds__(256) k_ftp_field(const float2* __restrict__ Pw
   if (threadIdx.x < np) {
     const int j = threadIdx.x;
     float2 acc = make_float2(0.f, 0.f);
+    TwWalk wk(half, Y, N);
     for (int i = 0; i < np; i++) {
       const float2 p = Pw[((size_t)b * np + i) * np + j];
-      const float2 t = tw_inv(tw, i - half, Y, N);
+      const float2 t = wk.next(tw);
       acc.x = fmaf(p.x, t.x, fmaf(-p.y, t.y, acc.x));
       acc.y = fmaf(p.x, t.y, fmaf(p.y, t.x, acc.y));
     }
@@ -365,9 +381,10 @@ __global__ void __launch_bounds__(256) k_ftp_field(const float2* __restrict__ Pw
   for (int x = threadIdx.x; x < w; x += blockDim.x) {
     const int X = x + pad;
     float2 acc = make_float2(0.f, 0.f);
+    TwWalk wk(half, X, N);
     for (int j = 0; j < np; j++) {
       const float2 p = Tj[j];
-      const float2 t = tw_inv(tw, j - half, X, N);
+      const float2 t = wk.next(tw);
       acc.x = fmaf(p.x, t.x, fmaf(-p.y, t.y, acc.x));
       acc.y = fmaf(p.x, t.y, fmaf(p.y, t.x, acc.y));
     }

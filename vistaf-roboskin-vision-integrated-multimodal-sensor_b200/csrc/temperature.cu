@@ -501,9 +501,13 @@ __global__ void __launch_bounds__(256) k_temp_band(const float2* __restrict__ A,
     if (in) {
       int ky = ((ys - h / 2) % h + h) % h;
       int kq = twin ? (h - ky) % h : ky;            // F[ky,kx] = conj(F[-ky,-kx])
+      int idx = (int)(((long long)kq * lane) % h);  // (kq y) mod h, advanced by (32 kq) mod h per trip: the same entries
+      const int step = (int)(((long long)kq * 32) % h);
       for (int y = lane; y < h; y += 32) {
-        float2 t = __ldg(ph.tw + (int)(((long long)kq * y) % h));
+        float2 t = __ldg(ph.tw + idx);
         acc = cadd(acc, cmul(col[y], t));
+        idx += step;
+        if (idx >= h) idx -= h;
       }
     }
     acc.x = warp_sum(acc.x); acc.y = warp_sum(acc.y);
@@ -514,13 +518,18 @@ __global__ void __launch_bounds__(256) k_temp_band(const float2* __restrict__ A,
   const float scale = 1.0f / ((float)h * (float)w);
   for (int y = threadIdx.x; y < h; y += blockDim.x) {
     float2 acc = make_float2(0.f, 0.f);
+    // ky of consecutive rows of the box differ by one, so (ky y) mod h advances by y mod h per row
+    const int ky0 = ((py - R - h / 2) % h + h) % h;
+    int idx = (int)(((long long)ky0 * y) % h);
     for (int i = 0; i < nb; i++) {
       int ys = py + i - R;
-      if (ys < 0 || ys >= h) continue;
-      int ky = ((ys - h / 2) % h + h) % h;
-      float2 t = __ldg(ph.tw + (int)(((long long)ky * y) % h));
-      t.y = -t.y;                                   // e^{+i...}
-      acc = cadd(acc, cmul(Fd[i], t));
+      if (ys >= 0 && ys < h) {
+        float2 t = __ldg(ph.tw + idx);
+        t.y = -t.y;                                 // e^{+i...}
+        acc = cadd(acc, cmul(Fd[i], t));
+      }
+      idx += y;                                     // y < h
+      if (idx >= h) idx -= h;
     }
     G[((size_t)b * h + y) * MAXBAND + j] = make_float2(acc.x * scale, acc.y * scale);
   }
