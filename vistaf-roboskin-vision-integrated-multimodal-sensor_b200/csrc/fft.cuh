@@ -63,14 +63,20 @@ __device__ __forceinline__ void butterfly(float2 (&x)[R]) {
   }
 }
 
+// Index arithmetic of a pass without per-butterfly divisions: (sequence, butterfly) advance incrementally with the
+// thread stride, and k = j mod Ns is a mask when Ns is a power of two, else a multiply-shift by ceil(2^32 / Ns)
+// (exact for j < 2^16, Ns < 2^16).
 template <int SIGN, int R>
 __device__ __forceinline__ void stockham_pass(const float2* __restrict__ in, float2* __restrict__ out, int n,
                                               int Ns, int nseq, int ld, const float2* __restrict__ tw) {
   const int nb = n / R;              // butterflies per sequence
   const int stride = n / (Ns * R);   // twiddle index step
+  const bool pow2 = (Ns & (Ns - 1)) == 0;
+  const unsigned int magic = (unsigned int)((0x100000000ull + (unsigned)Ns - 1) / (unsigned)Ns);
+  int s = 0, j = threadIdx.x;
+  while (j >= nb) { j -= nb; s++; }
   for (int t = threadIdx.x; t < nb * nseq; t += blockDim.x) {
-    const int s = t / nb, j = t - s * nb;
-    const int k = j % Ns;
+    const int k = pow2 ? (j & (Ns - 1)) : j - (int)__umulhi((unsigned)j, magic) * Ns;
     const float2* src = in + s * ld;
     float2 x[R];
 #pragma unroll
@@ -82,6 +88,8 @@ __device__ __forceinline__ void stockham_pass(const float2* __restrict__ in, flo
     float2* dst = out + s * ld + (j - k) * R + k;
 #pragma unroll
     for (int q = 0; q < R; q++) dst[q * Ns] = x[q];
+    j += blockDim.x;
+    while (j >= nb) { j -= nb; s++; }
   }
 }
 
