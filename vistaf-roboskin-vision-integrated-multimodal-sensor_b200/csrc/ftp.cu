@@ -330,17 +330,10 @@ __global__ void __launch_bounds__(256) k_ftp_coldft(const float2* __restrict__ R
     }
   }
 }
-// e^{+2 pi i f X / N} from the forward table
-__device__ __forceinline__ float2 tw_inv(const float2* __restrict__ tw, int f, int X, int N) {
-  const int af = f < 0 ? -f : f;
-  float2 t = __ldg(tw + (int)(((long long)af * X) % N));
-  if (f >= 0) t.y = -t.y;
-  return t;
-}
 // Inverse of the re-centred patch on the un-padded rows/columns, fractional ramp (:955-961), and either
 //   REF: store the reference field and its amplitude (:990-997), or
 //   DEF: ratio with the reference field -> wrapped phase (:1681-1689) and amp_ref * amp_def (:741).
-// The twiddle of tap f at position X is table entry (|f| X) mod N, conjugated for f >= 0 (tw_inv): walking f = -half ..
+// The twiddle e^{+2 pi i f X / N} of tap f at position X is the forward-table entry (|f| X) mod N, conjugated for f >= 0: walking f = -half ..
 // half, the index moves by -(X mod N) down to 0 and by +(X mod N) up again, so one modulo per pixel replaces one 64-bit
 // multiply + modulo per tap; the entries read are the same ones.
 struct TwWalk {
