@@ -112,3 +112,43 @@ def test_lane_step_matches_oracle_on_one_frame(env):
     assert np.array_equal(np.isnan(fin), np.isnan(to["final"]))
     assert float(np.nanmax(np.abs(fin - to["final"]))) <= 1e-2             # degC
     assert int((out["temp"]["dark"][i].cpu().numpy().astype(bool) != to["dark"]).sum()) == 0
+
+
+def test_graph_replay_equals_eager_launches(env):
+    """The batch entry points replay a CUDA graph from the third call with identical arguments on: call 1 (eager), call 2
+    (capture + launch) and calls 3-4 (replays) must give identical bytes, with NEW frame contents in the same buffers on
+    call 4 (the graph carries pointers, not data), and the replay counter must move."""
+    import torch
+    import _native as N
+    import synthetic as SY
+    import multimodal_sensor as M
+    ref = torch.from_numpy(SY.make_frame(0, reference=True)).cuda()
+    a = torch.from_numpy(np.stack([SY.make_frame(3), SY.make_frame(15)])).cuda()
+    b = torch.from_numpy(np.stack([SY.make_frame(7), SY.make_frame(5)])).cuda()
+    buf = a.clone()
+    plan = M.MultimodalPlan(a.shape[1], a.shape[2], 2, 2, "multimodal")
+    snaps = []
+    r0 = int(N.lib().vistaf_graph_replays())
+    for call in range(4):
+        if call == 3:
+            buf.copy_(b)
+        res = plan.step(ref, buf, masks=True)
+        torch.cuda.synchronize()
+        snaps.append({"rec": res["records"].clone(), "h": res["ftp"]["height_mm"].clone(), "fin": res["temp"]["final"].clone(),
+                      "rel": res["ftp"]["reliable"].clone(), "dark": res["temp"]["dark"].clone()})
+    assert int(N.lib().vistaf_graph_replays()) > r0
+    for k in snaps[0]:
+        for c in (1, 2):
+            x, y = snaps[0][k], snaps[c][k]
+            assert bool(((x == y) | ((x != x) & (y != y))).all()), (k, c)
+    N.check(N.lib().vistaf_set_graphs(0))
+    try:
+        fresh = M.MultimodalPlan(a.shape[1], a.shape[2], 2, 2, "multimodal")
+        want = fresh.step(ref, b.clone(), masks=True)
+        torch.cuda.synchronize()
+        for k, w in (("rec", want["records"]), ("h", want["ftp"]["height_mm"]), ("fin", want["temp"]["final"]),
+                     ("rel", want["ftp"]["reliable"]), ("dark", want["temp"]["dark"])):
+            x = snaps[3][k]
+            assert bool(((x == w) | ((x != x) & (w != w))).all()), k
+    finally:
+        N.check(N.lib().vistaf_set_graphs(1))
