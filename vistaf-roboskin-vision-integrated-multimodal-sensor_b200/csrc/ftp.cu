@@ -803,7 +803,7 @@ __device__ void irls_solve_dev(FtpScal& s, int iter) {
 #define ACC_TILE 1024
 #define ACC_STAGES 3
 template <bool ORDER2>
-__global__ void __launch_bounds__(256) k_irls_accum(const float* __restrict__ zc, const unsigned int* __restrict__ pc,
+__global__ void __launch_bounds__(256, 3) k_irls_accum(const float* __restrict__ zc, const unsigned int* __restrict__ pc,
                                                      const float* __restrict__ rc, FtpScal* sc, FitGeom g, int npix, int iter) {
   constexpr int NC = ORDER2 ? 6 : 3, NV = NC * (NC + 1) / 2 + NC + 1;
   __shared__ double sh[NV * 32];

@@ -786,7 +786,10 @@ __device__ __forceinline__ float key_f32(unsigned int k) {
 // map on the slot's ROI window plus min / max of the raw wide map -- the inputs of k_t10_quant / k_t10_refuse.
 template <bool T10>
 __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
-  __shared__ uint8_t tile[(FT_H + 4) * (FT_W + 4) * 3];
+  // planar BGR tile with a 2-pixel halo, and its horizontal (1 4 6 4 1) sums: the 5x5 kernel is an outer product of
+  // integers, so rows-then-columns gives the same integer as the 25-tap sum with 10 taps per channel
+  __shared__ uint8_t tile[3][(FT_H + 4) * (FT_W + 4)];
+  __shared__ unsigned short hs[3][(FT_H + 4) * FT_W];
   const int b = T10 ? a.t10_frame[blockIdx.z] : (int)blockIdx.z;
   if (T10 && b < 0) return;
   const int x0 = ((int)blockIdx.x + a.tile_x0) * FT_W, y0 = ((int)blockIdx.y + a.tile_y0) * FT_H, h = a.h, w = a.w;
@@ -812,7 +815,16 @@ __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
     int ty = e / (FT_W + 4), tx = e - ty * (FT_W + 4);
     int y = reflect101(y0 - 2 + ty, h), x = reflect101(x0 - 2 + tx, w);
     const uint8_t* p = img + ((size_t)y * w + x) * 3;
-    tile[e * 3] = p[0]; tile[e * 3 + 1] = p[1]; tile[e * 3 + 2] = p[2];
+    tile[0][e] = p[0]; tile[1][e] = p[1]; tile[2][e] = p[2];
+  }
+  __syncthreads();
+  for (int e = tid; e < (FT_H + 4) * FT_W; e += FT_W * FT_H) {
+    const int ty = e / FT_W, tx = e - ty * FT_W;
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      const uint8_t* r = &tile[c][ty * (FT_W + 4) + tx];
+      hs[c][e] = (unsigned short)(r[0] + 4 * r[1] + 6 * r[2] + 4 * r[3] + r[4]);
+    }
   }
   __syncthreads();
   const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
@@ -832,16 +844,12 @@ __global__ void __launch_bounds__(FT_W * FT_H) k_temp_features(FeatArgs a) {
       light = roi_eff && !is_dark;
       n_dark += is_dark;
       // blurred BGR: ((1 4 6 4 1)x(1 4 6 4 1) * p + 128) >> 8
-      const int kw[5] = {1, 4, 6, 4, 1};
-      int s[3] = {0, 0, 0};
+      int s[3];
 #pragma unroll
-      for (int dy = 0; dy < 5; dy++)
-#pragma unroll
-        for (int dx = 0; dx < 5; dx++) {
-          const uint8_t* p = tile + ((threadIdx.y + dy) * (FT_W + 4) + threadIdx.x + dx) * 3;
-          int k = kw[dy] * kw[dx];
-          s[0] += k * p[0]; s[1] += k * p[1]; s[2] += k * p[2];
-        }
+      for (int c = 0; c < 3; c++) {
+        const unsigned short* q = &hs[c][threadIdx.y * FT_W + threadIdx.x];
+        s[c] = (int)q[0] + 4 * (int)q[FT_W] + 6 * (int)q[2 * FT_W] + 4 * (int)q[3 * FT_W] + (int)q[4 * FT_W];
+      }
       const int B = (s[0] + 128) >> 8, Gc = (s[1] + 128) >> 8, Rc = (s[2] + 128) >> 8;
       // OpenCV 8-bit BGR2Lab, integer path (tables verified on all 2^24 colours, tools/make_lab_lut.py)
       const int R = __ldg(a.gam + Rc), G = __ldg(a.gam + Gc), Bl = __ldg(a.gam + B);
