@@ -379,7 +379,10 @@ def main():
         res = plan.step(ref_dev, dev, masks=True)          # everything the module API returns: maps, all masks, records
         return gather(res)
 
-    dev2, ref2 = torch.empty_like(dev), torch.empty_like(ref_dev)
+    # two device staging buffers: the host->device copy of step n+1 runs while step n computes on the other buffer
+    stage = [(torch.empty_like(dev), torch.empty_like(ref_dev)) for _ in range(2)]
+    stage_free = [None, None]                      # event: the step that last read the buffer has finished
+    stage_turn = [0]
 
     copy_stream = torch.cuda.Stream()
     n_slices = 2 * max(1, a.lanes_ftp, a.lanes_temp)
@@ -388,7 +391,11 @@ def main():
         """Host -> device staging of the reference and of the frames in slices on a copy stream (events mark each slice
         ready, so a lane starts as soon as its frames have landed), the step through the public API, records to host."""
         main = torch.cuda.current_stream()
-        copy_stream.wait_stream(main)             # the previous step has finished reading dev2 / ref2
+        k = stage_turn[0]
+        stage_turn[0] ^= 1
+        dev2, ref2 = stage[k]
+        if stage_free[k] is not None:
+            copy_stream.wait_event(stage_free[k])  # the step two calls ago has finished reading this buffer
         ready = []
         with torch.cuda.stream(copy_stream):
             ref2.copy_(ref_pinned, non_blocking=True)
@@ -409,6 +416,8 @@ def main():
                 ev.record(copy_stream)
                 ready.append((lo, hi, ev))
         res = plan.step(ref2, dev2, masks=True, ready=ready, ref_ready=ev_ref)
+        stage_free[k] = torch.cuda.Event()
+        stage_free[k].record(main)
         g = gather(res)
         return res, (g.cpu() if g is not None else None)
 
