@@ -235,17 +235,23 @@ __device__ __forceinline__ void chamfer_body(Zero zero, float* __restrict__ out,
   const int xa = threadIdx.x * pt;
   for (int i = threadIdx.x; i < 2 * W2; i += CH_THREADS) rows[i] = CH_INF;
   __syncthreads();
-  // forward sweep: from above (three neighbours) then left-to-right
+  // forward sweep: from above (three neighbours) then left-to-right.  The zero-set flags of row y + 1 are fetched while
+  // row y goes through its barriers (the row walk is a serial chain: an exposed global load per row would dominate it).
+  bool zc[CH_MAXPT], zn[CH_MAXPT];
+#pragma unroll
+  for (int j = 0; j < CH_MAXPT; j++) { const int x = xa + j; zc[j] = (j < pt && x < w && h > 0) ? zero(b, 0, x) : false; }
   for (int y = 0; y < h; y++) {
     unsigned int t[CH_MAXPT];
     int run = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < CH_MAXPT; j++) { const int x = xa + j; zn[j] = (j < pt && x < w && y + 1 < h) ? zero(b, y + 1, x) : false; }
 #pragma unroll
     for (int j = 0; j < CH_MAXPT; j++) {
       const int x = xa + j;
       t[j] = CH_INF;
       if (j < pt && x < w) {
         unsigned int v = 0;
-        if (!zero(b, y, x)) v = min(min(prev[x] + CH_DG, prev[x + 1] + CH_HV), min(prev[x + 2] + CH_DG, CH_INF));
+        if (!zc[j]) v = min(min(prev[x] + CH_DG, prev[x + 1] + CH_HV), min(prev[x + 2] + CH_DG, CH_INF));
         t[j] = v;
         run = min(run, (int)v - (int)(CH_HV * (unsigned)x));   // t[x'] - a x'   (fits: |a x| < 2^28)
       }
@@ -267,21 +273,28 @@ __device__ __forceinline__ void chamfer_body(Zero zero, float* __restrict__ out,
         T[(size_t)y * w + x] = v;
       }
     }
+#pragma unroll
+    for (int j = 0; j < CH_MAXPT; j++) zc[j] = zn[j];
     __syncthreads();
     unsigned int* sw = prev; prev = cur; cur = sw;
   }
   // backward sweep
   for (int i = threadIdx.x; i < 2 * W2; i += CH_THREADS) rows[i] = CH_INF;
   __syncthreads();
+  unsigned int tc[CH_MAXPT], tn[CH_MAXPT];
+#pragma unroll
+  for (int j = 0; j < CH_MAXPT; j++) { const int x = w - 1 - (xa + j); tc[j] = (j < pt && x >= 0 && h > 0) ? T[(size_t)(h - 1) * w + x] : CH_INF; }
   for (int y = h - 1; y >= 0; y--) {
     unsigned int t[CH_MAXPT];
     int run = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < CH_MAXPT; j++) { const int x = w - 1 - (xa + j); tn[j] = (j < pt && x >= 0 && y > 0) ? T[(size_t)(y - 1) * w + x] : CH_INF; }
 #pragma unroll
     for (int j = 0; j < CH_MAXPT; j++) {
       const int x = w - 1 - (xa + j);                  // mirrored thread order: scan runs right-to-left
       t[j] = CH_INF;
       if (j < pt && x >= 0) {
-        unsigned int v = T[(size_t)y * w + x];
+        unsigned int v = tc[j];
         v = min(v, min(min(prev[x] + CH_DG, prev[x + 1] + CH_HV), prev[x + 2] + CH_DG));
         v = min(v, CH_INF);
         t[j] = v;
@@ -304,6 +317,8 @@ __device__ __forceinline__ void chamfer_body(Zero zero, float* __restrict__ out,
         out[(size_t)b * h * w + (size_t)y * w + x] = (float)v * (1.0f / 65536.0f);
       }
     }
+#pragma unroll
+    for (int j = 0; j < CH_MAXPT; j++) tc[j] = tn[j];
     __syncthreads();
     unsigned int* sw = prev; prev = cur; cur = sw;
   }
