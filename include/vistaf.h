@@ -244,6 +244,18 @@ int vistaf_ftp_workspace_plane(const VistafFtpPlan* plan, int chunk, const char*
 /* force_sensor.depth_map_to_volume_cm3 (:93-123) on DEVICE maps: out3 = DEVICE float64 [B][3] (volume_cm3, area_mm2, max_depth_mm) */
 int vistaf_depth_to_volume(const float* height_mm, const uint8_t* roi_or_null, int batch, long long npix, double mm_per_px,
                            double depth_eps_mm, double* out3, void* cuda_stream);
+/* vistaf_depth_to_volume WITHOUT any allocation.  No counterpart in the reference: added
+   for callers that cannot call cudaMalloc (stream capture, tight serving loops, harnesses that forbid it).
+   Same arguments, same kernels and same results as vistaf_depth_to_volume; the per-frame accumulators live in a
+   file-scope `static __device__` array of VISTAF_VOL_STATIC_MAX_BATCH entries (160 KiB, held by every GPU that loads
+   the library until exit) instead of a cudaMallocAsync block.  batch > VISTAF_VOL_STATIC_MAX_BATCH is rejected with an
+   error (split the call).  No cudaMalloc / cudaFree / allocating library routine is called.  Every call on a device
+   shares the array (cleared on `cuda_stream` at the start of each call): calls that overlap on the GPU -- different
+   streams with no ordering between them -- race on it; calls on one stream, or ordered by events, are safe. */
+#define VISTAF_VOL_STATIC_MAX_BATCH 4096
+int vistaf_depth_to_volume_static(const float* height_mm, const uint8_t* roi_or_null, int batch, long long npix, double mm_per_px,
+                                  double depth_eps_mm, double* out3, void* cuda_stream);
+int vistaf_depth_to_volume_static_max_batch(void);
 /* host-side scalar: force_sensor.predict_force_from_volume (:149-167); returns NaN for an unknown type */
 double vistaf_curve_predict(const VistafCurveModel* model, double x);
 

@@ -195,6 +195,8 @@ def lib():
                                                  C.POINTER(C.c_size_t)]
         L.vistaf_depth_to_volume.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_double, C.c_double,
                                              C.c_void_p, C.c_void_p]
+        L.vistaf_depth_to_volume_static.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_double, C.c_double,
+                                                    C.c_void_p, C.c_void_p]
         L.vistaf_profile_read.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int)]
         L.vistaf_launch_count.restype = C.c_longlong
         L.vistaf_curve_predict.restype = C.c_double

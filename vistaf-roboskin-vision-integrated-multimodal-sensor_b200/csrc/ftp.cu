@@ -24,6 +24,7 @@
 #include "telea.cuh"
 #include <cuda_pipeline.h>
 #include <string.h>
+#include <mutex>
 #include <new>
 #include <vector>
 #include <algorithm>
@@ -1959,5 +1960,59 @@ extern "C" int vistaf_depth_to_volume(const float* height_mm, const uint8_t* roi
   VL(), k_vol_finish<<<cdiv(batch, 128), 128, 0, st>>>(s, out3, batch, mm_per_px);
   CKL();
   CK(cudaFreeAsync(s, st));
+  return 0;
+}
+
+// ------------------------------------------------------------------ allocation-free variant of vistaf_depth_to_volume
+// Same three kernels, but the per-frame accumulators live in a file-scope device array instead of a cudaMallocAsync
+// block: nothing is allocated or freed, so the call is legal under stream capture and in loops that forbid cudaMalloc.
+// Every GPU that loads the library holds the array (VISTAF_VOL_STATIC_MAX_BATCH * 40 bytes = 160 KiB) until exit.  All
+// calls on a device share it: it is cleared on the caller's stream before use, and two calls that overlap on the GPU
+// (different streams, no ordering between them) race on it.
+static __device__ __align__(256) VolScratch g_vol_static[VISTAF_VOL_STATIC_MAX_BATCH];
+
+namespace {
+constexpr int kVolMaxDev = 64;
+std::mutex g_vol_static_mu;
+VolScratch* g_vol_static_ptr[kVolMaxDev] = {};
+// g_vol_static in HOST code is a stand-in symbol, not a device address: resolve it once per device, with that device current
+int vol_static_addr(VolScratch** out) {
+  int dev = -1;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kVolMaxDev)
+    return vistaf_set_err("vistaf_depth_to_volume_static: device ordinal out of range", cudaErrorInvalidDevice, __FILE__, __LINE__);
+  std::lock_guard<std::mutex> lk(g_vol_static_mu);
+  if (!g_vol_static_ptr[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_vol_static);
+    if (e != cudaSuccess || !p) return vistaf_set_err("vistaf_depth_to_volume_static: cudaGetSymbolAddress", e, __FILE__, __LINE__);
+    g_vol_static_ptr[dev] = (VolScratch*)p;
+  }
+  *out = g_vol_static_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" int vistaf_depth_to_volume_static_max_batch(void) { return VISTAF_VOL_STATIC_MAX_BATCH; }
+
+extern "C" int vistaf_depth_to_volume_static(const float* height_mm, const uint8_t* roi, int batch, long long npix, double mm_per_px,
+                                             double depth_eps_mm, double* out3, void* stream) {
+  if (!height_mm || !out3 || batch < 1 || npix < 1)
+    return vistaf_set_err("vistaf_depth_to_volume_static: bad argument", cudaErrorInvalidValue, __FILE__, __LINE__);
+  if (batch > VISTAF_VOL_STATIC_MAX_BATCH) {
+    char msg[160];
+    snprintf(msg, sizeof(msg), "vistaf_depth_to_volume_static: batch %d exceeds the static scratch (max %d frames per call)", batch,
+             VISTAF_VOL_STATIC_MAX_BATCH);
+    return vistaf_set_err(msg, cudaErrorInvalidValue, __FILE__, __LINE__);
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  VolScratch* s = nullptr;
+  if (vol_static_addr(&s)) return 1;
+  CK(cudaMemsetAsync(s, 0, sizeof(VolScratch) * batch, st));          // the array keeps the last call's sums
+  VL(), k_depth_sign<<<dim3(64, batch), 256, 0, st>>>(height_mm, roi, &s[0].pos, &s[0].neg, sizeof(VolScratch), npix);
+  VL(), k_depth_reduce<<<dim3(64, batch), 256, 0, st>>>(height_mm, roi, &s[0].pos, &s[0].neg, sizeof(VolScratch), &s[0].vsum,
+                                                  &s[0].vcnt, &s[0].vmax, npix, (float)depth_eps_mm);
+  VL(), k_vol_finish<<<cdiv(batch, 128), 128, 0, st>>>(s, out3, batch, mm_per_px);
+  CKL();
   return 0;
 }
