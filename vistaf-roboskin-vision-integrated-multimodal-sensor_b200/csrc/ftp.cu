@@ -208,12 +208,28 @@ __global__ void k_ftp_sobel(const uint8_t* __restrict__ gray, float* __restrict_
   grad[i] = sqrtf((float)(gx * gx + gy * gy));
 }
 
+// four mask bytes, then (only where one is set) four values: bit k of the result = element k is a finite masked sample
+__device__ __forceinline__ unsigned int masked_vec4(const float* p4, const uint8_t* m4, long long i, long long n, float v[4]) {
+  const uchar4 mm = *reinterpret_cast<const uchar4*>(m4);
+  unsigned int m = ((mm.x ? 1u : 0u) | (mm.y ? 2u : 0u) | (mm.z ? 4u : 0u) | (mm.w ? 8u : 0u)) & sel_tail_mask(i, n);
+  if (!m) return 0u;
+  const float4 f = *reinterpret_cast<const float4*>(p4);
+  v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
+#pragma unroll
+  for (int k = 0; k < 4; k++)
+    if (!(fabsf(v[k]) <= 3.4e38f)) m &= ~(1u << k);
+  return m;
+}
 struct MaskedVal {              // value stream: plane[b][i] where mask[i] (mask shared across frames)
   const float* p; const uint8_t* m; long long plane;
   __device__ bool operator()(int b, long long i, float& v) const {
     if (!m[i]) return false;
     v = p[(long long)b * plane + i];
     return fabsf(v) <= 3.4e38f;
+  }
+  __device__ bool vec_ok() const { return (plane & 3) == 0 && sel_aligned16(p) && ((unsigned long long)m & 3ull) == 0; }
+  __device__ unsigned int vec4(int b, long long i, long long n, float v[4]) const {
+    return masked_vec4(p + (long long)b * plane + i, m + i, i, n, v);
   }
 };
 struct MaskedValB {             // per-frame mask
@@ -222,6 +238,10 @@ struct MaskedValB {             // per-frame mask
     if (!m[(long long)b * plane + i]) return false;
     v = p[(long long)b * plane + i];
     return fabsf(v) <= 3.4e38f;
+  }
+  __device__ bool vec_ok() const { return (plane & 3) == 0 && sel_aligned16(p) && ((unsigned long long)m & 3ull) == 0; }
+  __device__ unsigned int vec4(int b, long long i, long long n, float v[4]) const {
+    return masked_vec4(p + (long long)b * plane + i, m + (long long)b * plane + i, i, n, v);
   }
 };
 
@@ -916,11 +936,38 @@ struct RFirst {
     rc[o] = v;
     return true;
   }
+  // 16-byte path (select.cuh): the compacted arrays are padded to the plane, so a group may over-read past n inside it
+  __device__ bool vec_ok() const { return (plane & 3) == 0 && sel_aligned16(zc) && sel_aligned16(pc) && sel_aligned16(rc); }
+  __device__ unsigned int vec4(int b, long long j, long long n, float v[4]) const {
+    const long long o = (long long)b * plane + j;
+    const float4 z4 = *reinterpret_cast<const float4*>(zc + o);
+    const uint4 p4 = *reinterpret_cast<const uint4*>(pc + o);
+    const unsigned int m = sel_tail_mask(j, n);
+    const float zz[4] = {z4.x, z4.y, z4.z, z4.w};
+    const unsigned int pp[4] = {p4.x, p4.y, p4.z, p4.w};
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      v[k] = 0.f;
+      if ((m >> k) & 1u) {
+        float xn, yn;
+        g.norm_packed(pp[k], xn, yn);
+        v[k] = __fsub_rn(zz[k], poly_fit(sc[b].coef, xn, yn, ORDER2));
+      }
+    }
+    *reinterpret_cast<float4*>(rc + o) = make_float4(v[0], v[1], v[2], v[3]);
+    return m;
+  }
 };
 struct RPlain {
   const float* rc; const FtpScal* sc; long long plane;
   __device__ long long limit(int b) const { return (long long)sc[b].nc; }
   __device__ bool operator()(int b, long long j, float& v) const { v = rc[(long long)b * plane + j]; return true; }
+  __device__ bool vec_ok() const { return (plane & 3) == 0 && sel_aligned16(rc); }
+  __device__ unsigned int vec4(int b, long long j, long long n, float v[4]) const {
+    const float4 r4 = *reinterpret_cast<const float4*>(rc + (long long)b * plane + j);
+    v[0] = r4.x; v[1] = r4.y; v[2] = r4.z; v[3] = r4.w;
+    return sel_tail_mask(j, n);
+  }
 };
 struct RAbs {
   const float* rc; const FtpScal* sc; long long plane;
@@ -928,6 +975,14 @@ struct RAbs {
   __device__ bool operator()(int b, long long j, float& v) const {
     v = fabsf(__fsub_rn(rc[(long long)b * plane + j], sc[b].med));
     return true;
+  }
+  __device__ bool vec_ok() const { return (plane & 3) == 0 && sel_aligned16(rc); }
+  __device__ unsigned int vec4(int b, long long j, long long n, float v[4]) const {
+    const float4 r4 = *reinterpret_cast<const float4*>(rc + (long long)b * plane + j);
+    const float med = sc[b].med;
+    v[0] = fabsf(__fsub_rn(r4.x, med)); v[1] = fabsf(__fsub_rn(r4.y, med));
+    v[2] = fabsf(__fsub_rn(r4.z, med)); v[3] = fabsf(__fsub_rn(r4.w, med));
+    return sel_tail_mask(j, n);
   }
 };
 __global__ void k_ftp_sub_fit1(float* __restrict__ unw, const FtpScal* sc, FitGeom g, int npix) {

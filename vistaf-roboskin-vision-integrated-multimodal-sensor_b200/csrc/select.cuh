@@ -15,6 +15,7 @@
 // workspace; P2 restores it).
 #pragma once
 #include "common.cuh"
+#include <stdlib.h>
 
 #define SEL_BINS 2048
 #define SEL_CAP (1 << 17)      // list capacity per frame (keys)
@@ -74,6 +75,25 @@ __device__ __forceinline__ auto sel_limit(const V& v, int b, long long n, int) -
 }
 template <class V>
 __device__ __forceinline__ long long sel_limit(const V&, int, long long n, long) { return n; }
+
+// Optional 16-byte path of a value functor over dense, aligned streams:
+//     __device__ bool vec_ok() const;                                              // alignment holds for this call
+//     __device__ unsigned int vec4(int b, long long i, long long n, float v[4]) const;   // i % 4 == 0; bit j = element i + j is a sample
+// The S1 / S2 sweeps then move four elements per load instruction (two such groups in flight per thread): same
+// samples, same histogram counts and list contents as the scalar sweep, only the order in which they are met differs.
+#ifndef VISTAF_SEL_VEC
+#define VISTAF_SEL_VEC 1
+#endif
+template <class V>
+struct sel_has_vec4 {
+  template <class U> static auto test(int) -> decltype(((const U*)nullptr)->vec_ok(), char());
+  template <class U> static long test(...);
+  static constexpr bool value = VISTAF_SEL_VEC && sizeof(test<V>(0)) == sizeof(char);
+};
+__device__ __forceinline__ unsigned int sel_tail_mask(long long i, long long n) {      // elements i .. i+3 below n
+  return n - i >= 4 ? 15u : ((1u << (int)(n - i)) - 1u);
+}
+__device__ __forceinline__ bool sel_aligned16(const void* a) { return ((unsigned long long)a & 15ull) == 0; }
 
 static __global__ void k_sel_zero(SelectState* st) {
   SelectState& s = st[blockIdx.x];
@@ -154,9 +174,29 @@ __global__ void __launch_bounds__(256) k_sel_s1(Val val, SelectState* st, long l
   for (int i = threadIdx.x; i < SEL_BINS; i += 256) h[i] = 0;
   __syncthreads();
   n = sel_limit(val, b, n, 0);
+  bool swept = false;
+  if constexpr (sel_has_vec4<Val>::value) {
+    if (val.vec_ok()) {                                  // two 16-byte groups per thread in flight, 2048 elements per block step
+      swept = true;
+      for (long long base = (long long)blockIdx.x * (2 * SEL_TILE); base < n; base += (long long)gridDim.x * (2 * SEL_TILE)) {
+        float v[2][4];
+        unsigned int m[2];
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+          const long long i = base + u * SEL_TILE + threadIdx.x * 4;
+          m[u] = i < n ? val.vec4(b, i, n, v[u]) : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 2; u++)
+#pragma unroll
+          for (int j = 0; j < 4; j++)
+            if ((m[u] >> j) & 1u) atomicAdd(&h[f2key(v[u][j]) >> 21], 1u);
+      }
+    }
+  }
   // four independent element fetches are in flight before the first histogram update (the value functors are
   // chains of dependent loads: mask byte, then sample)
-  for (long long i0 = (long long)blockIdx.x * SEL_TILE + threadIdx.x; i0 < n; i0 += (long long)gridDim.x * SEL_TILE) {
+  for (long long i0 = (long long)blockIdx.x * SEL_TILE + threadIdx.x; i0 < n && !swept; i0 += (long long)gridDim.x * SEL_TILE) {
     float v[SEL_U];
     bool ok[SEL_U];
 #pragma unroll
@@ -218,7 +258,46 @@ __global__ void __launch_bounds__(256) k_sel_s2(Val val, SelectState* st, unsign
   // warp-uniform trip count (ballots inside): lanes of a warp walk consecutive elements
   const long long stride = (long long)gridDim.x * SEL_TILE;
   const long long start = (long long)blockIdx.x * SEL_TILE + (threadIdx.x & ~31) * SEL_U;
-  for (long long i0 = start; i0 < n; i0 += stride) {
+  bool swept = false;
+  if constexpr (sel_has_vec4<Val>::value) {
+    if (val.vec_ok()) {                                  // block-uniform trip count (ballots inside)
+      swept = true;
+      for (long long base = (long long)blockIdx.x * (2 * SEL_TILE); base < n; base += (long long)gridDim.x * (2 * SEL_TILE)) {
+        float v[2][4];
+        unsigned int m[2];
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+          const long long i = base + u * SEL_TILE + threadIdx.x * 4;
+          m[u] = i < n ? val.vec4(b, i, n, v[u]) : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 2; u++)
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            unsigned int key = 0;
+            bool take = false;
+            if ((m[u] >> j) & 1u) {
+              key = f2key(v[u][j]);
+              const unsigned int bin = key >> 21;
+              take = bin == b1;
+              if (need_next && bin > b1) mn = min(mn, key);
+            }
+            if (take) atomicAdd(&h[(key >> 10) & 2047u], 1u);
+            if (!gather) continue;
+            const unsigned int bits = __ballot_sync(0xffffffffu, take);
+            if (!bits) continue;
+            unsigned int base_at = 0;
+            if (lane == 0) base_at = atomicAdd(&s.nlist, (unsigned int)__popc(bits));
+            base_at = __shfl_sync(0xffffffffu, base_at, 0);
+            if (take) {
+              const unsigned int at = base_at + (unsigned int)__popc(bits & ((1u << lane) - 1u));
+              if (at < cap) list[at] = key;
+            }
+          }
+      }
+    }
+  }
+  for (long long i0 = start; i0 < n && !swept; i0 += stride) {
     float v[SEL_U];
     bool ok[SEL_U];
 #pragma unroll
@@ -428,7 +507,9 @@ template <class Val1, class Val2, class Out>
 static int select_quantile_out2(Val1 val1, Val2 val2, Out out, SelectState* st, unsigned int* lists, long long n, int batch,
                                 float q, cudaStream_t stream, const float* qv = nullptr, size_t qstride = 0,
                                 unsigned int cap = SEL_CAP, bool heavy = false) {   // heavy: duplicated data expected
-  int gx = (148 * 12 + batch - 1) / batch;      // several waves of blocks per sweep: a short last wave
+  static int per_sm = 0;                        // blocks per SM over the whole grid (VISTAF_SEL_BLOCKS_PER_SM, default 16)
+  if (!per_sm) { const char* e = getenv("VISTAF_SEL_BLOCKS_PER_SM"); per_sm = e ? atoi(e) : 16; if (per_sm < 1) per_sm = 16; }
+  int gx = (148 * per_sm + batch - 1) / batch;  // several waves of blocks per sweep: a short last wave
   const int gmax = (int)((n + 1023) / 1024);
   if (gx > gmax) gx = gmax;
   if (gx > 592) gx = 592;

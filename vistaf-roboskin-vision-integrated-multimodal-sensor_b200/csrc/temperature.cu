@@ -1057,6 +1057,20 @@ struct FinalVal {              // value stream for the median: final map over th
     v = fin[(long long)b * plane + off + i];
     return v == v;
   }
+  __device__ bool vec_ok() const {
+    return ((plane | off) & 3) == 0 && sel_aligned16(fin) && ((unsigned long long)roi & 3ull) == 0;
+  }
+  __device__ unsigned int vec4(int b, long long i, long long n, float v[4]) const {
+    const uchar4 mm = *reinterpret_cast<const uchar4*>(roi + off + i);
+    unsigned int m = ((mm.x ? 1u : 0u) | (mm.y ? 2u : 0u) | (mm.z ? 4u : 0u) | (mm.w ? 8u : 0u)) & sel_tail_mask(i, n);
+    if (!m) return 0u;
+    const float4 f = *reinterpret_cast<const float4*>(fin + (long long)b * plane + off + i);
+    v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+      if (!(v[k] == v[k])) m &= ~(1u << k);
+    return m;
+  }
 };
 
 // ------------------------------------------------------------------ T12 on a tilted carrier (temperature_sensor.py:705-742)
