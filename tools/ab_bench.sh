@@ -16,8 +16,9 @@ PY
 cp $PK/lib/libvistaf.so /tmp/libvistaf_main.so
 for v in "$@"; do
   case $v in
-    novec) cp $PK/lib/libvistaf_novec.so $PK/lib/libvistaf.so; run novec; cp /tmp/libvistaf_main.so $PK/lib/libvistaf.so ;;
-    vec) run vec ;;
-    b*) run vec_$v VISTAF_SEL_BLOCKS_PER_SM=${v#b} ;;
+    alt:*) cp $PK/lib/libvistaf_${v#alt:}.so $PK/lib/libvistaf.so; run ${v#alt:}; cp /tmp/libvistaf_main.so $PK/lib/libvistaf.so ;;
+    main) run main ;;
+    main2) run main2 ;;
+    env:*) run main_${v#env:} ${v#env:} ;;
   esac
 done

@@ -270,29 +270,40 @@ __global__ void __launch_bounds__(256) k_sel_s2(Val val, SelectState* st, unsign
           const long long i = base + u * SEL_TILE + threadIdx.x * 4;
           m[u] = i < n ? val.vec4(b, i, n, v[u]) : 0u;
         }
+        // pass 1: level-2 histogram, smallest key above the bin, and how many keys this warp appends
+        unsigned int tot = 0;
+#pragma unroll
+        for (int u = 0; u < 2; u++)
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            bool take = false;
+            if ((m[u] >> j) & 1u) {
+              const unsigned int key = f2key(v[u][j]);
+              const unsigned int bin = key >> 21;
+              take = bin == b1;
+              if (take) atomicAdd(&h[(key >> 10) & 2047u], 1u);
+              if (need_next && bin > b1) mn = min(mn, key);
+            }
+            if (gather) tot += (unsigned int)__popc(__ballot_sync(0xffffffffu, take));
+          }
+        if (!gather || !tot) continue;                   // warp-uniform
+        // pass 2: ONE list reservation per warp and block step (up to 256 keys), slots filled group by group
+        unsigned int at0 = 0;
+        if (lane == 0) at0 = atomicAdd(&s.nlist, tot);
+        at0 = __shfl_sync(0xffffffffu, at0, 0);
 #pragma unroll
         for (int u = 0; u < 2; u++)
 #pragma unroll
           for (int j = 0; j < 4; j++) {
             unsigned int key = 0;
             bool take = false;
-            if ((m[u] >> j) & 1u) {
-              key = f2key(v[u][j]);
-              const unsigned int bin = key >> 21;
-              take = bin == b1;
-              if (need_next && bin > b1) mn = min(mn, key);
-            }
-            if (take) atomicAdd(&h[(key >> 10) & 2047u], 1u);
-            if (!gather) continue;
+            if ((m[u] >> j) & 1u) { key = f2key(v[u][j]); take = (key >> 21) == b1; }
             const unsigned int bits = __ballot_sync(0xffffffffu, take);
-            if (!bits) continue;
-            unsigned int base_at = 0;
-            if (lane == 0) base_at = atomicAdd(&s.nlist, (unsigned int)__popc(bits));
-            base_at = __shfl_sync(0xffffffffu, base_at, 0);
             if (take) {
-              const unsigned int at = base_at + (unsigned int)__popc(bits & ((1u << lane) - 1u));
+              const unsigned int at = at0 + (unsigned int)__popc(bits & ((1u << lane) - 1u));
               if (at < cap) list[at] = key;
             }
+            at0 += (unsigned int)__popc(bits);
           }
       }
     }
