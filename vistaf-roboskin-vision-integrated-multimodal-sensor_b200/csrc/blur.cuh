@@ -5,6 +5,7 @@
 // along the filter axis with a sliding register window (1 LDS per 8 FMA).
 #pragma once
 #include "common.cuh"
+#include <stdlib.h>
 
 #define BLUR_MAXK 368          // >= 361 taps (sigma 45), multiple of 8
 #define BLUR_ROW_SEG 1280      // outputs per row block (160 threads x 8)
@@ -71,7 +72,7 @@ __device__ __forceinline__ void blur_outside(S& s, int b, int y, int x, float v,
 
 // Row pass.  grid = (ceil(w/1280), h, batch), block = 160.  Load: float operator()(int b,int y,int x).
 template <class Load>
-__global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* __restrict__ tmp, int h, int w,
+__global__ void __launch_bounds__(BLUR_ROW_THREADS, 12) k_blur_rows(Load ld, float* __restrict__ tmp, int h, int w,
                                                                  long long plane, GaussKernel g, BlurWindow win) {
   __shared__ float s[8 * BLUR_ROW_PITCH];
   __shared__ float wk[BLUR_MAXK];
@@ -120,8 +121,12 @@ __global__ void __launch_bounds__(BLUR_ROW_THREADS) k_blur_rows(Load ld, float* 
 
 // Column pass.  grid = (ceil(w/32), ceil(h/(8*TYT)), batch), block = (32, TYT).
 // dynamic smem = (8*TYT + kpad + 8) * 32 floats.  Store: void operator()(int b,int y,int x,float v); void finish(int b).
+#ifndef VISTAF_BLUR_COLS_MINB
+#define VISTAF_BLUR_COLS_MINB 2     // resident column blocks per SM at 1024 threads: one block stages its tile while the other computes
+#endif
 template <class Store>
-__global__ void k_blur_cols(const float* __restrict__ tmp, Store st, int h, int w, long long plane, GaussKernel g,
+__global__ void __launch_bounds__(1024, VISTAF_BLUR_COLS_MINB)
+k_blur_cols(const float* __restrict__ tmp, Store st, int h, int w, long long plane, GaussKernel g,
                             BlurWindow win) {
   extern __shared__ float sc[];
   __shared__ float wk[BLUR_MAXK];
@@ -187,7 +192,9 @@ template <class Load, class Store>
 static int gauss_blur(Load ld, Store st, float* tmp, int h, int w, int batch, const GaussKernel& gx,
                       const GaussKernel& gy, cudaStream_t stream, const BlurWindow* window = nullptr) {
   const long long plane = (long long)h * w;
-  const int tyt = gy.ksize > 100 ? 32 : 16;
+  static int tyt_big = 0;                      // column-block height for long kernels: 8 * tyt rows (VISTAF_BLUR_TYT, default 32)
+  if (!tyt_big) { const char* e = getenv("VISTAF_BLUR_TYT"); tyt_big = e ? atoi(e) : 32; if (tyt_big != 16 && tyt_big != 32) tyt_big = 32; }
+  const int tyt = gy.ksize > 200 ? tyt_big : 16;         // measured: 161 taps run best at 128-row blocks, 361 taps at 256
   BlurWindow win = window ? *window : BlurWindow{0, w, 0, h, 0, h, nullptr, nullptr, 0, nullptr, 0u};
   if (window && !window->rowfill) {           // rows the active column blocks (aligned to their own grid) read
     win.ry0 = win.y0 - (gy.ksize >> 1) - 8 * tyt;
@@ -201,6 +208,7 @@ static int gauss_blur(Load ld, Store st, float* tmp, int h, int w, int batch, co
   static bool attr_done = false;   // per template instantiation
   if (!attr_done && sm > 48 * 1024) {
     CK(cudaFuncSetAttribute((const void*)k_blur_cols<Store>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CK(cudaFuncSetAttribute((const void*)k_blur_cols<Store>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     attr_done = true;
   }
   VL(), k_blur_cols<Store><<<g2, blk, sm, stream>>>(tmp, st, h, w, plane, gy, win);

@@ -1249,7 +1249,7 @@ struct AddEpsStore {
 };
 
 // final per-pixel assembly + phase -> mm (shape_ftp.py:1816-1851) + candidate statistics for the blob filter
-__global__ void k_ftp_assemble(const float* __restrict__ hm, const float* __restrict__ dist_in,
+__global__ void __launch_bounds__(256, 8) k_ftp_assemble(const float* __restrict__ hm, const float* __restrict__ dist_in,
                                const float* __restrict__ dist_out, const float* __restrict__ sm,
                                const uint8_t* __restrict__ rel, const uint8_t* __restrict__ roi, FtpScal* sc,
                                float* __restrict__ out, int npix, float band, VistafCurveModel model, int use_neg) {

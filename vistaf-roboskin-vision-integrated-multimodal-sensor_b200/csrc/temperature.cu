@@ -603,7 +603,7 @@ __global__ void __launch_bounds__(256) k_temp_ifft_rows(const float2* __restrict
 // (temperature_sensor.py:475-489), from the analytic signal stored by k_temp_ifft_rows<1>.  maskA is written over
 // the ROI bounding box only (its readers test the ROI first).
 #define SPLIT_ROWS 8            // rows per block: one float64 block reduction per 8 x 256 pixels instead of per 256
-__global__ void __launch_bounds__(256) k_temp_split(const float2* __restrict__ Z, const uint8_t* __restrict__ gray8,
+__global__ void __launch_bounds__(256, 8) k_temp_split(const float2* __restrict__ Z, const uint8_t* __restrict__ gray8,
                                                      const uint8_t* __restrict__ roi, const uint8_t* __restrict__ sat,
                                                      uint8_t* __restrict__ maskA, TempScal* sc, int h, int w, int ybeg, int zx0,
                                                      int zw, int zrows) {
