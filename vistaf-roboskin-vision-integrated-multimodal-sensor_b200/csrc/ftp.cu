@@ -261,7 +261,21 @@ __global__ void k_ftp_badraw(BadLoad ld, uint8_t* __restrict__ dst, int h, int w
 __global__ void k_ftp_count_mask(const uint8_t* __restrict__ m, FtpScal* sc, int npix, int which) {
   const int b = blockIdx.y;
   int c = 0;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) c += m[(size_t)b * npix + i] != 0;
+  const uint8_t* mb = m + (size_t)b * npix;
+  if ((npix & 3) == 0 && ((unsigned long long)m & 3ull) == 0) {       // four bytes per load, four loads in flight per thread
+    const unsigned int* m4 = reinterpret_cast<const unsigned int*>(mb);
+    const int n4 = npix >> 2, step = gridDim.x * blockDim.x;
+    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n4; i0 += 4 * step) {
+      unsigned int u[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) u[j] = i0 + j * step < n4 ? m4[i0 + j * step] : 0u;
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        c += ((u[j] & 0xffu) != 0) + ((u[j] & 0xff00u) != 0) + ((u[j] & 0xff0000u) != 0) + ((u[j] & 0xff000000u) != 0);
+    }
+  } else {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) c += mb[i] != 0;
+  }
   c = warp_sum(c);
   if ((threadIdx.x & 31) == 0 && c) {
     unsigned int* dst = which == 0 ? &sc[b].n_bad : which == 1 ? &sc[b].n_rel : which == 2 ? &sc[b].n_contact
@@ -574,11 +588,16 @@ __global__ void k_ftp_residues(const float* __restrict__ wr, const uint8_t* __re
     const size_t o = (size_t)b * h * w;
     const int p00 = y * w + x, p01 = p00 + 1, p10 = p00 + w, p11 = p10 + 1;
     const bool m00 = rel[o + p00], m01 = rel[o + p01], m10 = rel[o + p10], m11 = rel[o + p11];
-    PhaseEdge e{wr, (long long)h * w};
-    if (m00 && m01 && m11) bad += (e(b, p00, p01) + e(b, p01, p11) + e(b, p11, p00)) != 0;
-    if (m00 && m10 && m11) bad += (e(b, p00, p10) + e(b, p10, p11) + e(b, p11, p00)) != 0;
-    if (m00 && m01 && m10) bad += (e(b, p00, p01) + e(b, p01, p10) + e(b, p10, p00)) != 0;
-    if (m01 && m10 && m11) bad += (e(b, p01, p11) + e(b, p11, p10) + e(b, p10, p01)) != 0;
+    // the four phases are fetched whatever the masks say: eight independent loads in flight instead of two dependent rounds
+    const float w00 = wr[o + p00], w01 = wr[o + p01], w10 = wr[o + p10], w11 = wr[o + p11];
+    auto e = [](float from, float to) {               // PhaseEdge on values: wrap count of the step from -> to
+      const float d = __fsub_rn(to, from);
+      return d >= 3.14159274f ? -1 : (d <= -3.14159274f ? 1 : 0);
+    };
+    if (m00 && m01 && m11) bad += (e(w00, w01) + e(w01, w11) + e(w11, w00)) != 0;
+    if (m00 && m10 && m11) bad += (e(w00, w10) + e(w10, w11) + e(w11, w00)) != 0;
+    if (m00 && m01 && m10) bad += (e(w00, w01) + e(w01, w10) + e(w10, w00)) != 0;
+    if (m01 && m10 && m11) bad += (e(w01, w11) + e(w11, w10) + e(w10, w01)) != 0;
   }
   bad = warp_sum(bad);
   if ((threadIdx.x & 31) == 0 && bad) atomicAdd(&sc[b].residues, (unsigned)bad);
@@ -1013,10 +1032,12 @@ __global__ void k_ftp_contact(const float* __restrict__ z, const uint8_t* __rest
   int c = 0;
   if (i < npix) {
     const size_t o = (size_t)b * npix + i;
-    if (rel[o]) {
+    const uint8_t r = rel[o];
+    const float zz = z[o];                             // fetched beside the mask byte, not after it
+    if (r) {
       float xn, yn;
       g.norm(i, xn, yn);
-      const float v = fabsf(__fsub_rn(z[o], poly_fit(sc[b].coef, xn, yn, true)));
+      const float v = fabsf(__fsub_rn(zz, poly_fit(sc[b].coef, xn, yn, true)));
       c = (v >= sc[b].contact_thr && fabsf(v) <= 3.4e38f) ? 1 : 0;
     }
     contact[o] = (uint8_t)c;
@@ -1212,21 +1233,24 @@ struct MaskZero {               // chamfer zero set = the mask
   const uint8_t* m; long long plane; int w;
   __device__ bool operator()(int b, int y, int x) const { return m[(long long)b * plane + (long long)y * w + x] != 0; }
 };
-__device__ __forceinline__ float filled_at(const float* hm, const float* dist_in, const FtpScal& s, long long o, float band) {
-  float v = hm[o];
+__device__ __forceinline__ float filled_val(float v, float d, const FtpScal& s, float band) {
   if (s.flip) v = __fmul_rn(v, -1.0f);
-  const float d = dist_in[o];
   float t = __fdiv_rn(fmaxf(__fsub_rn(d, 1.0f), 0.f), fmaxf(1e-6f, band));
   t = fminf(fmaxf(t, 0.f), 1.f);
   const float wgt = __fmul_rn(__fmul_rn(t, t), __fsub_rn(3.0f, __fmul_rn(2.0f, t)));
   return __fmul_rn(v, wgt);
+}
+__device__ __forceinline__ float filled_at(const float* hm, const float* dist_in, const FtpScal& s, long long o, float band) {
+  const float v = hm[o], d = dist_in[o];
+  return filled_val(v, d, s, band);
 }
 struct AsmLoad {                // hf_ on the ROI before the sigma-9 smoothing: reliable -> filled, else 0
   const float* hm; const float* dist_in; const uint8_t* rel; const uint8_t* roi; const FtpScal* sc; long long plane; int w;
   float band;
   __device__ float operator()(int b, int y, int x) const {
     const long long i = (long long)y * w + x, o = (long long)b * plane + i;
-    if (!roi[i] || !rel[o]) return 0.f;
+    const uint8_t in_roi = roi[i], in_rel = rel[o];
+    if (!in_roi || !in_rel) return 0.f;
     return filled_at(hm, dist_in, sc[b], o, band);
   }
 };
@@ -1257,12 +1281,14 @@ __global__ void __launch_bounds__(256, 8) k_ftp_assemble(const float* __restrict
   float mm = FNAN;
   if (i < npix) {
     const size_t o = (size_t)b * npix + i;
-    if (roi[i] && !(sc[b].status & VISTAF_ST_EMPTY_ROI)) {
+    const uint8_t in_roi = roi[i], in_rel = rel[o];       // both mask bytes in flight, then the pixel's pair of planes together
+    if (in_roi && !(sc[b].status & VISTAF_ST_EMPTY_ROI)) {
+      const float a = (in_rel ? hm : sm)[o], d = (in_rel ? dist_in : dist_out)[o];
       float v;
-      if (rel[o]) v = filled_at(hm, dist_in, sc[b], o, band);
+      if (in_rel) v = filled_val(a, d, sc[b], band);
       else {
-        v = sm[o];
-        if (fmaxf(__fsub_rn(dist_out[o], 1.0f), 0.f) <= band) v = 0.f;
+        v = a;
+        if (fmaxf(__fsub_rn(d, 1.0f), 0.f) <= band) v = 0.f;
       }
       if (fabsf(v) <= 3.4e38f) v = fminf(v, 0.f);
       const double x = fmax((double)(use_neg ? -v : v), 0.0);
@@ -1285,8 +1311,10 @@ __global__ void k_ftp_blob_peak(const ull* __restrict__ uf, const float* __restr
   const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
   unsigned int root = UF_BG, bits = 0;
   if (i < npix) {
-    root = uf_parent(uf[(size_t)b * npix + i]);
-    if (root != UF_BG) bits = __float_as_uint(mm[(size_t)b * npix + i]);      // depth > 0: bit order == value order
+    const ull u = uf[(size_t)b * npix + i];
+    const float depth = mm[(size_t)b * npix + i];                             // fetched beside the label, not after it
+    root = uf_parent(u);
+    if (root != UF_BG) bits = __float_as_uint(depth);                         // depth > 0: bit order == value order
   }
   // lanes of one blob elect a leader that carries the group's maximum: one atomic per blob per warp
   const unsigned int grp = __match_any_sync(0xffffffffu, root);
