@@ -141,6 +141,95 @@ __device__ float2* fft_smem(float2* a, float2* b, const Fft1D& p, int nseq, int 
   return a;
 }
 
+// Two consecutive radix-4 passes (sequence sizes Ns and 4 Ns) as one 16-point step per thread.  The four first-pass
+// butterflies j = a + q' n/16 (q' = 0..3; a = Ns c' + k < n/16) produce exactly the inputs of the four second-pass
+// butterflies j' = 4 Ns c' + r Ns + k (r = 0..3), so the intermediate values stay in registers.  Every product and sum
+// is the one the two separate passes compute -- same operands, same order, same twiddle table entries -- so the result
+// is bit-identical; one shared-memory round trip and one barrier fewer per pair.
+// PAD_IN / PAD_OUT: the buffer read / written holds element i at i + i/16.  At Ns = 1 a thread owns 16 consecutive
+// outputs; without the padding a whole warp would store to one pair of banks.
+#ifndef VISTAF_FFT_FUSE44
+#define VISTAF_FFT_FUSE44 1
+#endif
+template <int SIGN, bool PAD_IN, bool PAD_OUT>
+__device__ __forceinline__ void stockham_pass_4x4(const float2* __restrict__ in, float2* __restrict__ out, int n, int Ns,
+                                                  const float2* __restrict__ tw) {
+  const int n16 = n >> 4, stride1 = n / (Ns * 4), stride2 = stride1 >> 2;
+  for (int a = threadIdx.x; a < n16; a += blockDim.x) {
+    const int k = a & (Ns - 1);                       // Ns is a power of two here
+    float2 x[16];
+#pragma unroll
+    for (int m = 0; m < 16; m++) { const int i = a + m * n16; x[m] = in[PAD_IN ? i + (i >> 4) : i]; }
+    // first pass: butterfly q' reads x[q' + 4 q] (q = 0..3), inputs q > 0 times W^(q k stride1) when Ns > 1
+    float2 w1[3];
+    if (Ns > 1) {
+#pragma unroll
+      for (int q = 1; q < 4; q++) w1[q - 1] = tw_get<SIGN>(tw, q * k * stride1);
+    }
+#pragma unroll
+    for (int qp = 0; qp < 4; qp++) {
+      float2 X[4] = {x[qp], x[qp + 4], x[qp + 8], x[qp + 12]};
+      if (Ns > 1) {
+#pragma unroll
+        for (int q = 1; q < 4; q++) X[q] = cmul(X[q], w1[q - 1]);
+      }
+      butterfly<SIGN, 4>(X);
+      x[qp] = X[0]; x[qp + 4] = X[1]; x[qp + 8] = X[2]; x[qp + 12] = X[3];      // output r of butterfly q' -> x[q' + 4 r]
+    }
+    // second pass (sequence size 4 Ns > 1): butterfly r reads x[q' + 4 r] (q' = 0..3), inputs q' > 0 times W^(q' (r Ns + k) stride2)
+    const int o0 = 16 * (a - k) + k;                 // 16 Ns c' + k
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+      float2 Z[4] = {x[4 * r], x[4 * r + 1], x[4 * r + 2], x[4 * r + 3]};
+      const int k2 = r * Ns + k;
+#pragma unroll
+      for (int qp = 1; qp < 4; qp++) Z[qp] = cmul(Z[qp], tw_get<SIGN>(tw, qp * k2 * stride2));
+      butterfly<SIGN, 4>(Z);
+#pragma unroll
+      for (int qq = 0; qq < 4; qq++) { const int i = o0 + r * Ns + qq * 4 * Ns; out[PAD_OUT ? i + (i >> 4) : i] = Z[qq]; }
+    }
+  }
+}
+
+// fft_smem for ONE sequence with radix-4 pairs fused (stockham_pass_4x4).  b must hold n + n/16 entries (the padded
+// intermediate of a first pair that is followed by a second pair lives there); a holds n.  Same result, bit for bit.
+template <int SIGN>
+__device__ float2* fft_smem_fused(float2* a, float2* b, const Fft1D& p) {
+  int Ns = 1, f = 0;
+  bool in_pad = false;
+  while (f < p.nf) {
+    const int r = p.radix[f];
+    __syncthreads();
+    const bool pair = VISTAF_FFT_FUSE44 && r == 4 && f + 1 < p.nf && p.radix[f + 1] == 4 && (Ns & (Ns - 1)) == 0 &&
+                      ((p.n >> 4) % Ns) == 0;
+    if (pair) {
+      // pad the output only at Ns = 1 (first pass: a -> b) and only when the reader is a fused pair as well
+      const bool out_pad = Ns == 1 && f + 3 < p.nf && p.radix[f + 2] == 4 && p.radix[f + 3] == 4 && ((p.n >> 4) % 16) == 0;
+      if (in_pad) stockham_pass_4x4<SIGN, true, false>(a, b, p.n, Ns, p.tw);
+      else if (out_pad) stockham_pass_4x4<SIGN, false, true>(a, b, p.n, Ns, p.tw);
+      else stockham_pass_4x4<SIGN, false, false>(a, b, p.n, Ns, p.tw);
+      in_pad = out_pad;
+      Ns *= 16;
+      f += 2;
+    } else {
+      switch (r) {
+        case 2: stockham_pass<SIGN, 2>(a, b, p.n, Ns, 1, p.n, p.tw); break;
+        case 3: stockham_pass<SIGN, 3>(a, b, p.n, Ns, 1, p.n, p.tw); break;
+        case 4: stockham_pass<SIGN, 4>(a, b, p.n, Ns, 1, p.n, p.tw); break;
+        case 5: stockham_pass<SIGN, 5>(a, b, p.n, Ns, 1, p.n, p.tw); break;
+        default: stockham_pass_generic<SIGN>(a, b, p.n, r, Ns, 1, p.n, p.tw); break;
+      }
+      Ns *= r;
+      f += 1;
+    }
+    float2* t = a;
+    a = b;
+    b = t;
+  }
+  __syncthreads();
+  return a;
+}
+
 // Host: factorise n (prefer radix 4, then 2, 3, 5, then remaining primes) and build the table.
 int fft1d_create(Fft1D* p, int n);   // allocates p->tw on the device
 void fft1d_destroy(Fft1D* p);

@@ -15,6 +15,8 @@
 #include <algorithm>
 
 #define TOPK 16
+// row transforms: two buffers of W float2, the second with W/16 entries of padding for fft_smem_fused
+#define ROWS_SMEM(W) (((size_t)2 * (size_t)(W) + (size_t)(W) / 16 + 1) * sizeof(float2))
 #define COLS_PER_BLOCK 2      // 2 columns x 2 buffers x 2161 float2 = 69 KB: three blocks per SM overlap each other's barriers
 #define COLS_THREADS 256
 #define COLS_PT 18             // bins per thread held in registers for the top-16 search: COLS_PER_BLOCK * H <= 18 * 256
@@ -252,7 +254,7 @@ __global__ void __launch_bounds__(256) k_temp_fft_rows(const float* __restrict__
       if (x < n) a[x] = make_float2(__fdiv_rn(u0[j], mu), has1 ? __fdiv_rn(u1[j], mu) : 0.f);
     }
   }
-  float2* z = fft_smem<-1>(a, bb, p, 1, n);
+  float2* z = fft_smem_fused<-1>(a, bb, p);
   float2* o0 = A + ((size_t)b * h + r) * wh;
   float2* o1 = o0 + wh;
   for (int k = threadIdx.x; k < wh; k += blockDim.x) {
@@ -557,7 +559,7 @@ __global__ void __launch_bounds__(256) k_temp_ifft_rows(const float2* __restrict
     int xs = S.peak_x + (int)threadIdx.x - R;
     if (xs >= 0 && xs < n) a[((xs - n / 2) % n + n) % n] = G[((size_t)b * h + y) * MAXBAND + threadIdx.x];
   }
-  float2* z = fft_smem<1>(a, bb, p, 1, n);
+  float2* z = fft_smem_fused<1>(a, bb, p);
   const size_t row = (size_t)y * n, fr = (size_t)b * h * n;
   const bool has_sat = S.sat_raw_count != 0;
   if (PASS == 1) {
@@ -1336,7 +1338,7 @@ extern "C" int vistaf_temp_plan_create(const VistafTempParams* P, VistafTempPlan
   p->H = P->height; p->W = P->width; p->Wh = P->width / 2 + 1;
   p->nblk_cols = cdiv(p->Wh, COLS_PER_BLOCK);
   if (fft1d_create(&p->fw, p->W) || fft1d_create(&p->fh, p->H)) return 1;
-  if ((size_t)p->W * 16 > 200 * 1024 || (size_t)COLS_PER_BLOCK * (p->H + 1) * 16 > 220 * 1024 ||
+  if (ROWS_SMEM(p->W) > 200 * 1024 || (size_t)COLS_PER_BLOCK * (p->H + 1) * 16 > 220 * 1024 ||
       COLS_PER_BLOCK * p->H > COLS_PT * COLS_THREADS)
     return vistaf_set_err("frame too large for the shared-memory FFT", cudaErrorInvalidValue, __FILE__, __LINE__);
   p->g_illum = make_gauss(P->illum_sigma);
@@ -1369,9 +1371,9 @@ extern "C" int vistaf_temp_plan_create(const VistafTempParams* P, VistafTempPlan
   CK(cudaMemcpy(p->lab_gamma, P->lab_gamma, sizeof(int) * 256, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(p->lab_cbrt, P->lab_cbrt, sizeof(int) * 3072, cudaMemcpyHostToDevice));
   // opt-in shared memory for the FFT kernels
-  CK(cudaFuncSetAttribute((const void*)k_temp_fft_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, p->W * 16));
-  CK(cudaFuncSetAttribute((const void*)k_temp_ifft_rows<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->W * 16));
-  CK(cudaFuncSetAttribute((const void*)k_temp_ifft_rows<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->W * 16));
+  CK(cudaFuncSetAttribute((const void*)k_temp_fft_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROWS_SMEM(p->W)));
+  CK(cudaFuncSetAttribute((const void*)k_temp_ifft_rows<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROWS_SMEM(p->W)));
+  CK(cudaFuncSetAttribute((const void*)k_temp_ifft_rows<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROWS_SMEM(p->W)));
   CK(cudaFuncSetAttribute((const void*)k_temp_fft_cols_peaks, cudaFuncAttributeMaxDynamicSharedMemorySize,
                           COLS_PER_BLOCK * (p->H + 1) * 16));
   CK(cudaFuncSetAttribute((const void*)k_temp_peak_select, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1456,7 +1458,7 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   VL(), k_temp_mu<<<nb, 1, 0, st>>>(sc);
   vistaf_stage_mark("T.fft_rows", st);
   // forward FFT + carrier peak
-  VL(), k_temp_fft_rows<<<dim3(cdiv(H, 2), nb), 256, (size_t)W * 16, st>>>(norm, A, sc, p->fw, H, Wh);
+  VL(), k_temp_fft_rows<<<dim3(cdiv(H, 2), nb), 256, ROWS_SMEM(W), st>>>(norm, A, sc, p->fw, H, Wh);
   vistaf_stage_mark("T.fft_cols_peaks", st);
   VL(), k_temp_fft_cols_peaks<<<dim3(p->nblk_cols, nb), COLS_THREADS, (size_t)COLS_PER_BLOCK * (H + 1) * 16, st>>>(A, cand, p->fh, W, Wh,
                                                                                                   P.dc_exclusion, sc);
@@ -1472,7 +1474,7 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   float2* Z = A;
   const int zw = p->x1 - p->x0;
   if ((size_t)zw * nrows > (size_t)H * Wh) return vistaf_set_err("temperature: ROI box larger than the spectrum plane", cudaErrorInvalidValue, __FILE__, __LINE__);
-  VL(), k_temp_ifft_rows<1><<<dim3(nrows, nb), 256, (size_t)W * 16, st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R,
+  VL(), k_temp_ifft_rows<1><<<dim3(nrows, nb), 256, ROWS_SMEM(W), st>>>(G, norm, gray8, p->roi, sat, maskA, sc, p->fw, H, p->y0, R,
                                                                       Z, p->x0, zw, nrows);
   VL(), k_temp_phi0<<<nb, 1, 0, st>>>(sc);
   VL(), k_temp_split<<<dim3(cdiv(zw, 256), cdiv(nrows, SPLIT_ROWS), nb), 256, 0, st>>>(Z, gray8, p->roi, sat, maskA, sc, H, W, p->y0, p->x0, zw, nrows);
