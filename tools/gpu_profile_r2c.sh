@@ -29,6 +29,9 @@ cap() {  # name regex skip count
   python tools/ncu_raw.py gpurun_out/cap_$1.ncu-rep > gpurun_out/r02_ncu_full_$1.txt 2>&1
   rm -f gpurun_out/cap_$1.ncu-rep gpurun_out/cap_$1.log
 }
+if [ "${1:-all}" = "all" ]; then
 cap blur_final 'k_blur_cols|k_blur_rows' 60 24
 cap sel_irls_final 'k_sel_s1|k_sel_s2|k_irls_accum|k_irls_compact' 150 30
+fi
+cap temp_fft_final 'k_temp_fft_cols_peaks|k_temp_fft_rows|k_temp_ifft_rows' 12 9
 du -sh gpurun_out

@@ -68,7 +68,8 @@ __device__ __forceinline__ void butterfly(float2 (&x)[R]) {
 // (exact for j < 2^16, Ns < 2^16).
 template <int SIGN, int R>
 __device__ __forceinline__ void stockham_pass(const float2* __restrict__ in, float2* __restrict__ out, int n,
-                                              int Ns, int nseq, int ld, const float2* __restrict__ tw) {
+                                              int Ns, int nseq, int ld, const float2* __restrict__ tw, int ld_out = -1) {
+  if (ld_out < 0) ld_out = ld;
   const int nb = n / R;              // butterflies per sequence
   const int stride = n / (Ns * R);   // twiddle index step
   const bool pow2 = (Ns & (Ns - 1)) == 0;
@@ -85,7 +86,7 @@ __device__ __forceinline__ void stockham_pass(const float2* __restrict__ in, flo
       if (q > 0 && Ns > 1) x[q] = cmul(x[q], tw_get<SIGN>(tw, q * k * stride));
     }
     butterfly<SIGN, R>(x);
-    float2* dst = out + s * ld + (j - k) * R + k;
+    float2* dst = out + s * ld_out + (j - k) * R + k;
 #pragma unroll
     for (int q = 0; q < R; q++) dst[q * Ns] = x[q];
     j += blockDim.x;
@@ -97,7 +98,8 @@ __device__ __forceinline__ void stockham_pass(const float2* __restrict__ in, flo
 template <int SIGN>
 __device__ __forceinline__ void stockham_pass_generic(const float2* __restrict__ in, float2* __restrict__ out, int n,
                                                       int r, int Ns, int nseq, int ld,
-                                                      const float2* __restrict__ tw) {
+                                                      const float2* __restrict__ tw, int ld_out = -1) {
+  if (ld_out < 0) ld_out = ld;
   const int nb = n / r;
   const int stride = n / (Ns * r);
   for (int t = threadIdx.x; t < n * nseq; t += blockDim.x) {
@@ -112,7 +114,7 @@ __device__ __forceinline__ void stockham_pass_generic(const float2* __restrict__
       float2 w = tw_get<SIGN>(tw, (int)(((long long)p * k * stride + (long long)((p * q) % r) * nb) % n));
       acc = cadd(acc, cmul(v, w));
     }
-    out[s * ld + (j - k) * r + k + q * Ns] = acc;
+    out[s * ld_out + (j - k) * r + k + q * Ns] = acc;
   }
 }
 
@@ -141,92 +143,128 @@ __device__ float2* fft_smem(float2* a, float2* b, const Fft1D& p, int nseq, int 
   return a;
 }
 
-// Two consecutive radix-4 passes (sequence sizes Ns and 4 Ns) as one 16-point step per thread.  The four first-pass
-// butterflies j = a + q' n/16 (q' = 0..3; a = Ns c' + k < n/16) produce exactly the inputs of the four second-pass
-// butterflies j' = 4 Ns c' + r Ns + k (r = 0..3), so the intermediate values stay in registers.  Every product and sum
-// is the one the two separate passes compute -- same operands, same order, same twiddle table entries -- so the result
-// is bit-identical; one shared-memory round trip and one barrier fewer per pair.
-// PAD_IN / PAD_OUT: the buffer read / written holds element i at i + i/16.  At Ns = 1 a thread owns 16 consecutive
-// outputs; without the padding a whole warp would store to one pair of banks.
-#ifndef VISTAF_FFT_FUSE44
-#define VISTAF_FFT_FUSE44 1
+// Two consecutive passes (radix R1 at sequence size Ns, then radix R2 at R1 Ns) as one R1 R2-point step per thread.
+// With nG = n / (R1 R2) and a = Ns c' + k < nG (k = a mod Ns; needs nG % Ns == 0), the R2 first-pass butterflies
+// j = a + q' nG (q' < R2) read the inputs a + (q' + R2 q) nG (q < R1) and produce exactly the inputs of the R1
+// second-pass butterflies j' = R1 Ns c' + r Ns + k (r < R1): output r of butterfly q' is input q' of butterfly r.  So
+// the intermediate values stay in registers.  Every product and sum is the one the two separate passes compute --
+// same operands, same order, same twiddle table entries -- so the result is bit-identical; one shared-memory round
+// trip and one barrier fewer per pair.
+// PAD_IN / PAD_OUT: the buffer read / written holds element i at i + i/16.  At Ns = 1 a thread owns R1 R2 = 16
+// consecutive outputs; without the padding a whole warp would store to one pair of banks.
+#ifndef VISTAF_FFT_FUSE
+#define VISTAF_FFT_FUSE 1
 #endif
-template <int SIGN, bool PAD_IN, bool PAD_OUT>
-__device__ __forceinline__ void stockham_pass_4x4(const float2* __restrict__ in, float2* __restrict__ out, int n, int Ns,
-                                                  const float2* __restrict__ tw) {
-  const int n16 = n >> 4, stride1 = n / (Ns * 4), stride2 = stride1 >> 2;
-  for (int a = threadIdx.x; a < n16; a += blockDim.x) {
-    const int k = a & (Ns - 1);                       // Ns is a power of two here
-    float2 x[16];
+template <int SIGN, int R1, int R2, bool PAD_IN, bool PAD_OUT>
+__device__ __forceinline__ void stockham_pass_pair(const float2* __restrict__ in, float2* __restrict__ out, int n, int Ns,
+                                                   int nseq, int ld_in, int ld_out, const float2* __restrict__ tw) {
+  constexpr int RR = R1 * R2;
+  const int nG = n / RR, stride1 = n / (Ns * R1), stride2 = n / (Ns * RR);
+  const bool pow2 = (Ns & (Ns - 1)) == 0;
+  for (int t = threadIdx.x; t < nG * nseq; t += blockDim.x) {
+    int s = 0, a = t;
+    while (a >= nG) { a -= nG; s++; }
+    const int k = pow2 ? (a & (Ns - 1)) : a % Ns;
+    const float2* src = in + s * ld_in;
+    float2* dst = out + s * ld_out;
+    float2 x[RR];
 #pragma unroll
-    for (int m = 0; m < 16; m++) { const int i = a + m * n16; x[m] = in[PAD_IN ? i + (i >> 4) : i]; }
-    // first pass: butterfly q' reads x[q' + 4 q] (q = 0..3), inputs q > 0 times W^(q k stride1) when Ns > 1
-    float2 w1[3];
+    for (int m = 0; m < RR; m++) { const int i = a + m * nG; x[m] = src[PAD_IN ? i + (i >> 4) : i]; }
+    // first pass: butterfly q' reads x[q' + R2 q] (q < R1); inputs q > 0 times W^(q k stride1) when Ns > 1
+    float2 w1[R1 - 1];
     if (Ns > 1) {
 #pragma unroll
-      for (int q = 1; q < 4; q++) w1[q - 1] = tw_get<SIGN>(tw, q * k * stride1);
+      for (int q = 1; q < R1; q++) w1[q - 1] = tw_get<SIGN>(tw, q * k * stride1);
     }
 #pragma unroll
-    for (int qp = 0; qp < 4; qp++) {
-      float2 X[4] = {x[qp], x[qp + 4], x[qp + 8], x[qp + 12]};
+    for (int qp = 0; qp < R2; qp++) {
+      float2 X[R1];
+#pragma unroll
+      for (int q = 0; q < R1; q++) X[q] = x[qp + R2 * q];
       if (Ns > 1) {
 #pragma unroll
-        for (int q = 1; q < 4; q++) X[q] = cmul(X[q], w1[q - 1]);
+        for (int q = 1; q < R1; q++) X[q] = cmul(X[q], w1[q - 1]);
       }
-      butterfly<SIGN, 4>(X);
-      x[qp] = X[0]; x[qp + 4] = X[1]; x[qp + 8] = X[2]; x[qp + 12] = X[3];      // output r of butterfly q' -> x[q' + 4 r]
-    }
-    // second pass (sequence size 4 Ns > 1): butterfly r reads x[q' + 4 r] (q' = 0..3), inputs q' > 0 times W^(q' (r Ns + k) stride2)
-    const int o0 = 16 * (a - k) + k;                 // 16 Ns c' + k
+      butterfly<SIGN, R1>(X);
 #pragma unroll
-    for (int r = 0; r < 4; r++) {
-      float2 Z[4] = {x[4 * r], x[4 * r + 1], x[4 * r + 2], x[4 * r + 3]};
+      for (int r = 0; r < R1; r++) x[qp + R2 * r] = X[r];          // output r of butterfly q'
+    }
+    // second pass (sequence size R1 Ns > 1): butterfly r reads x[q' + R2 r] (q' < R2); inputs q' > 0 times
+    // W^(q' (r Ns + k) stride2)
+    const int o0 = RR * (a - k) + k;                   // R1 R2 Ns c' + k
+#pragma unroll
+    for (int r = 0; r < R1; r++) {
+      float2 Z[R2];
+#pragma unroll
+      for (int qp = 0; qp < R2; qp++) Z[qp] = x[qp + R2 * r];
       const int k2 = r * Ns + k;
 #pragma unroll
-      for (int qp = 1; qp < 4; qp++) Z[qp] = cmul(Z[qp], tw_get<SIGN>(tw, qp * k2 * stride2));
-      butterfly<SIGN, 4>(Z);
+      for (int qp = 1; qp < R2; qp++) Z[qp] = cmul(Z[qp], tw_get<SIGN>(tw, qp * k2 * stride2));
+      butterfly<SIGN, R2>(Z);
 #pragma unroll
-      for (int qq = 0; qq < 4; qq++) { const int i = o0 + r * Ns + qq * 4 * Ns; out[PAD_OUT ? i + (i >> 4) : i] = Z[qq]; }
+      for (int qq = 0; qq < R2; qq++) { const int i = o0 + r * Ns + qq * R1 * Ns; dst[PAD_OUT ? i + (i >> 4) : i] = Z[qq]; }
     }
   }
 }
 
-// fft_smem for ONE sequence with radix-4 pairs fused (stockham_pass_4x4).  b must hold n + n/16 entries (the padded
-// intermediate of a first pair that is followed by a second pair lives there); a holds n.  Same result, bit for bit.
-template <int SIGN>
-__device__ float2* fft_smem_fused(float2* a, float2* b, const Fft1D& p) {
+// padded sequence length of the second buffer of fft_smem_fused
+__host__ __device__ inline int fft_fused_ldb(int n) { return n + n / 16 + 1; }
+
+// fft_smem with pairs of passes fused (stockham_pass_pair: 4.4, 3.3, 3.5).  a: nseq sequences at stride ld_a (>= n);
+// b: scratch, nseq sequences at stride ld_b >= fft_fused_ldb(n) (the padded intermediate of a first 4.4 pair that a
+// second pair reads lives there).  Returns the buffer that holds the result and its sequence stride in ld_res.  Same
+// result as fft_smem, bit for bit.
+// ODD = false keeps the 3.3 / 3.5 pairs (up to 15 values per thread next to the radix-5 butterfly's temporaries: ~100
+// registers) out of the kernel: the row transforms stay at 78 registers and three blocks per SM with the 4.4 pairs only.
+template <int SIGN, bool ODD>
+__device__ float2* fft_smem_fused(float2* a, float2* b, const Fft1D& p, int nseq, int ld_a, int ld_b, int& ld_res) {
   int Ns = 1, f = 0;
   bool in_pad = false;
+  const int n = p.n;
   while (f < p.nf) {
-    const int r = p.radix[f];
+    const int r1 = p.radix[f], r2 = f + 1 < p.nf ? p.radix[f + 1] : 0;
     __syncthreads();
-    const bool pair = VISTAF_FFT_FUSE44 && r == 4 && f + 1 < p.nf && p.radix[f + 1] == 4 && (Ns & (Ns - 1)) == 0 &&
-                      ((p.n >> 4) % Ns) == 0;
-    if (pair) {
-      // pad the output only at Ns = 1 (first pass: a -> b) and only when the reader is a fused pair as well
-      const bool out_pad = Ns == 1 && f + 3 < p.nf && p.radix[f + 2] == 4 && p.radix[f + 3] == 4 && ((p.n >> 4) % 16) == 0;
-      if (in_pad) stockham_pass_4x4<SIGN, true, false>(a, b, p.n, Ns, p.tw);
-      else if (out_pad) stockham_pass_4x4<SIGN, false, true>(a, b, p.n, Ns, p.tw);
-      else stockham_pass_4x4<SIGN, false, false>(a, b, p.n, Ns, p.tw);
+    const bool can = VISTAF_FFT_FUSE && r2 != 0 && n % (r1 * r2) == 0 && (n / (r1 * r2)) % Ns == 0;
+    const bool p44 = can && r1 == 4 && r2 == 4, p33 = ODD && can && r1 == 3 && r2 == 3, p35 = ODD && can && r1 == 3 && r2 == 5;
+    if (p44 || p33 || p35) {
+      // pad the output only at Ns = 1 of a 4.4 pair (first pass: a -> b) and only when a 4.4 or 3.3 pair reads it
+      bool out_pad = false;
+      if (p44 && Ns == 1 && f + 3 < p.nf) {
+        const int r3 = p.radix[f + 2], r4 = p.radix[f + 3];
+        out_pad = ((r3 == 4 && r4 == 4) || (ODD && r3 == 3 && r4 == 3)) && n % (16 * r3 * r4) == 0 && (n / (r3 * r4)) % 16 == 0;
+      }
+      if (p44) {
+        if (in_pad) stockham_pass_pair<SIGN, 4, 4, true, false>(a, b, n, Ns, nseq, ld_a, ld_b, p.tw);
+        else if (out_pad) stockham_pass_pair<SIGN, 4, 4, false, true>(a, b, n, Ns, nseq, ld_a, ld_b, p.tw);
+        else stockham_pass_pair<SIGN, 4, 4, false, false>(a, b, n, Ns, nseq, ld_a, ld_b, p.tw);
+      } else if constexpr (ODD) {
+        if (p33) {
+          if (in_pad) stockham_pass_pair<SIGN, 3, 3, true, false>(a, b, n, Ns, nseq, ld_a, ld_b, p.tw);
+          else stockham_pass_pair<SIGN, 3, 3, false, false>(a, b, n, Ns, nseq, ld_a, ld_b, p.tw);
+        } else {
+          stockham_pass_pair<SIGN, 3, 5, false, false>(a, b, n, Ns, nseq, ld_a, ld_b, p.tw);    // never reads a padded buffer (see out_pad)
+        }
+      }
       in_pad = out_pad;
-      Ns *= 16;
+      Ns *= r1 * r2;
       f += 2;
     } else {
-      switch (r) {
-        case 2: stockham_pass<SIGN, 2>(a, b, p.n, Ns, 1, p.n, p.tw); break;
-        case 3: stockham_pass<SIGN, 3>(a, b, p.n, Ns, 1, p.n, p.tw); break;
-        case 4: stockham_pass<SIGN, 4>(a, b, p.n, Ns, 1, p.n, p.tw); break;
-        case 5: stockham_pass<SIGN, 5>(a, b, p.n, Ns, 1, p.n, p.tw); break;
-        default: stockham_pass_generic<SIGN>(a, b, p.n, r, Ns, 1, p.n, p.tw); break;
+      // single pass; a padded input cannot reach here (out_pad requires a pair as the reader), strides may differ
+      switch (r1) {
+        case 2: stockham_pass<SIGN, 2>(a, b, n, Ns, nseq, ld_a, p.tw, ld_b); break;
+        case 3: stockham_pass<SIGN, 3>(a, b, n, Ns, nseq, ld_a, p.tw, ld_b); break;
+        case 4: stockham_pass<SIGN, 4>(a, b, n, Ns, nseq, ld_a, p.tw, ld_b); break;
+        case 5: stockham_pass<SIGN, 5>(a, b, n, Ns, nseq, ld_a, p.tw, ld_b); break;
+        default: stockham_pass_generic<SIGN>(a, b, n, r1, Ns, nseq, ld_a, p.tw, ld_b); break;
       }
-      Ns *= r;
+      Ns *= r1;
       f += 1;
     }
-    float2* t = a;
-    a = b;
-    b = t;
+    float2* t = a; a = b; b = t;
+    const int tl = ld_a; ld_a = ld_b; ld_b = tl;
   }
   __syncthreads();
+  ld_res = ld_a;
   return a;
 }
 

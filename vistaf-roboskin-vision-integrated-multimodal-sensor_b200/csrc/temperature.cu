@@ -16,7 +16,9 @@
 
 #define TOPK 16
 // row transforms: two buffers of W float2, the second with W/16 entries of padding for fft_smem_fused
-#define ROWS_SMEM(W) (((size_t)2 * (size_t)(W) + (size_t)(W) / 16 + 1) * sizeof(float2))
+#define ROWS_SMEM(W) (((size_t)(W) + (size_t)fft_fused_ldb(W)) * sizeof(float2))
+// column transform: COLS_PER_BLOCK sequences of H + 1 float2 and the scratch at the padded stride
+#define COLS_SMEM(H) ((size_t)COLS_PER_BLOCK * ((size_t)(H) + 1 + (size_t)fft_fused_ldb(H)) * sizeof(float2))
 #define COLS_PER_BLOCK 2      // 2 columns x 2 buffers x 2161 float2 = 69 KB: three blocks per SM overlap each other's barriers
 #define COLS_THREADS 256
 #define COLS_PT 18             // bins per thread held in registers for the top-16 search: COLS_PER_BLOCK * H <= 18 * 256
@@ -254,7 +256,8 @@ __global__ void __launch_bounds__(256) k_temp_fft_rows(const float* __restrict__
       if (x < n) a[x] = make_float2(__fdiv_rn(u0[j], mu), has1 ? __fdiv_rn(u1[j], mu) : 0.f);
     }
   }
-  float2* z = fft_smem_fused<-1>(a, bb, p);
+  int ldz;
+  float2* z = fft_smem_fused<-1, false>(a, bb, p, 1, n, fft_fused_ldb(n), ldz);
   float2* o0 = A + ((size_t)b * h + r) * wh;
   float2* o1 = o0 + wh;
   for (int k = threadIdx.x; k < wh; k += blockDim.x) {
@@ -272,7 +275,7 @@ __device__ __forceinline__ bool dc_excluded(int x, int y, int h, int w, int dc) 
 
 // Column pass over the half spectrum + fused |F| and per-block top-16 (the dense spectrum is never
 // written: only the band around the carrier is needed later and is recomputed from A).
-__global__ void __launch_bounds__(512) k_temp_fft_cols_peaks(const float2* __restrict__ A, Cand* __restrict__ cand,
+__global__ void __launch_bounds__(COLS_THREADS, 2) k_temp_fft_cols_peaks(const float2* __restrict__ A, Cand* __restrict__ cand,
                                                               Fft1D p, int w, int wh, int dc, TempScal* sc) {
   extern __shared__ float2 sm[];
   const int n = p.n, lds = n + 1, b = blockIdx.y, c0 = blockIdx.x * COLS_PER_BLOCK;
@@ -294,7 +297,8 @@ __global__ void __launch_bounds__(512) k_temp_fft_cols_peaks(const float2* __res
       if (t < nc * n) { const int y = t / nc, c = t - y * nc; a[c * lds + y] = v[j]; }
     }
   }
-  float2* F = fft_smem<-1>(a, bb, p, nc, lds);
+  int ldf;
+  float2* F = fft_smem_fused<-1, true>(a, bb, p, nc, lds, fft_fused_ldb(n), ldf);
   float* mag = (float*)(F == a ? bb : a);          // scratch buffer is free now
   __syncthreads();
   // the DC exclusion box only reaches columns |kx| <= dc: every other block skips the (modulo-heavy) box test
@@ -304,7 +308,7 @@ __global__ void __launch_bounds__(512) k_temp_fft_cols_peaks(const float2* __res
 #pragma unroll
     for (int q = 1; q < COLS_PER_BLOCK; q++) if (ky >= n) { ky -= n; c++; }
     const int kx = c0 + c;
-    float2 v = F[c * lds + ky];
+    float2 v = F[c * ldf + ky];
     float m = sqrtf(v.x * v.x + v.y * v.y);
     if (near_dc) {
       // entry 1: (kx, ky); entry 2 (twin, same magnitude): (-kx, -ky).  Drop the bin if both are excluded.
@@ -559,7 +563,8 @@ __global__ void __launch_bounds__(256) k_temp_ifft_rows(const float2* __restrict
     int xs = S.peak_x + (int)threadIdx.x - R;
     if (xs >= 0 && xs < n) a[((xs - n / 2) % n + n) % n] = G[((size_t)b * h + y) * MAXBAND + threadIdx.x];
   }
-  float2* z = fft_smem_fused<1>(a, bb, p);
+  int ldz;
+  float2* z = fft_smem_fused<1, false>(a, bb, p, 1, n, fft_fused_ldb(n), ldz);
   const size_t row = (size_t)y * n, fr = (size_t)b * h * n;
   const bool has_sat = S.sat_raw_count != 0;
   if (PASS == 1) {
@@ -1338,7 +1343,7 @@ extern "C" int vistaf_temp_plan_create(const VistafTempParams* P, VistafTempPlan
   p->H = P->height; p->W = P->width; p->Wh = P->width / 2 + 1;
   p->nblk_cols = cdiv(p->Wh, COLS_PER_BLOCK);
   if (fft1d_create(&p->fw, p->W) || fft1d_create(&p->fh, p->H)) return 1;
-  if (ROWS_SMEM(p->W) > 200 * 1024 || (size_t)COLS_PER_BLOCK * (p->H + 1) * 16 > 220 * 1024 ||
+  if (ROWS_SMEM(p->W) > 200 * 1024 || COLS_SMEM(p->H) > 220 * 1024 ||
       COLS_PER_BLOCK * p->H > COLS_PT * COLS_THREADS)
     return vistaf_set_err("frame too large for the shared-memory FFT", cudaErrorInvalidValue, __FILE__, __LINE__);
   p->g_illum = make_gauss(P->illum_sigma);
@@ -1375,7 +1380,7 @@ extern "C" int vistaf_temp_plan_create(const VistafTempParams* P, VistafTempPlan
   CK(cudaFuncSetAttribute((const void*)k_temp_ifft_rows<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROWS_SMEM(p->W)));
   CK(cudaFuncSetAttribute((const void*)k_temp_ifft_rows<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROWS_SMEM(p->W)));
   CK(cudaFuncSetAttribute((const void*)k_temp_fft_cols_peaks, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                          COLS_PER_BLOCK * (p->H + 1) * 16));
+                          (int)COLS_SMEM(p->H)));
   CK(cudaFuncSetAttribute((const void*)k_temp_peak_select, cudaFuncAttributeMaxDynamicSharedMemorySize,
                           2 * p->nblk_cols * TOPK * 4));
   CK(cudaDeviceSynchronize());
@@ -1460,7 +1465,7 @@ static int temp_chunk(VistafTempPlan* p, const uint8_t* frames, int nb, const Vi
   // forward FFT + carrier peak
   VL(), k_temp_fft_rows<<<dim3(cdiv(H, 2), nb), 256, ROWS_SMEM(W), st>>>(norm, A, sc, p->fw, H, Wh);
   vistaf_stage_mark("T.fft_cols_peaks", st);
-  VL(), k_temp_fft_cols_peaks<<<dim3(p->nblk_cols, nb), COLS_THREADS, (size_t)COLS_PER_BLOCK * (H + 1) * 16, st>>>(A, cand, p->fh, W, Wh,
+  VL(), k_temp_fft_cols_peaks<<<dim3(p->nblk_cols, nb), COLS_THREADS, COLS_SMEM(H), st>>>(A, cand, p->fh, W, Wh,
                                                                                                   P.dc_exclusion, sc);
   const int ncand = p->nblk_cols * TOPK;
   VL(), k_temp_peak_select<<<nb, 256, (size_t)2 * ncand * 4, st>>>(cand, sc, ncand, H, W, P.dc_exclusion, P.peak_max_dy_frac);
