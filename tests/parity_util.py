@@ -56,3 +56,20 @@ def check_ftp_masks(gpu_masks, hm_gpu, o, P, tol_mm=1e-3, max_ties=8):
     stats["height_px_near_ties_over_tol"] = int((d[~far] > tol_mm).sum()) if (~far).any() else 0
     assert stats["height_max_far"] <= tol_mm, f"height differs by {stats['height_max_far']} mm away from any mask tie"
     return stats
+
+
+def f14_case(h=1182, w=1182):
+    """The F14 test input (tests/test_round2_gpu.py::test_internal_holes_are_found_and_filled, tools/make_golden_f14.py):
+    a smooth height plane over a reliable disc with NaN islands -- four small interior ones (candidates), one large
+    (known fraction too low) and one at the mask edge (too close).  Returns (height, reliable, islands)."""
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+    rel = ((xx - 590) ** 2 + (yy - 600) ** 2) <= 400 ** 2
+    hm = (0.3 * np.sin(xx / 37.0) * np.cos(yy / 51.0) - 0.2).astype(np.float32)
+    hm[~rel] = np.nan
+    holes = np.zeros_like(rel)
+    for cy, cx, r in ((500, 500, 2), (620, 700, 3), (601, 595, 1), (700, 450, 3)):
+        holes |= ((xx - cx) ** 2 + (yy - cy) ** 2) <= r * r
+    holes |= ((xx - 800) ** 2 + (yy - 600) ** 2) <= 30 ** 2
+    holes |= ((xx - 590) ** 2 + (yy - 203) ** 2) <= 3 ** 2
+    hm[holes & rel] = np.nan
+    return hm, rel, holes

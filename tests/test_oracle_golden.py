@@ -134,3 +134,25 @@ def test_unwrap_oracle_wraps_and_is_path_independent_without_residues(golden):
     k = np.rint((u - r["wrapped"]) / (2 * np.pi))
     assert np.nanmax(np.abs(k[rel])) >= 1
     assert np.nanmax(np.abs(u[rel] - (r["wrapped"][rel] + 2 * np.pi * k[rel]))) < 1e-5
+
+
+def test_internal_hole_fill_equals_the_reference_functions():
+    """F14 (shape_ftp.py:1153-1203 composed as :1770-1801): the oracle's fill_internal_holes against a vector recorded
+    from the UNMODIFIED reference's own compute_internal_holes_within_mask + inpaint_only_mask on injected NaN islands
+    (tools/make_golden_f14.py).  Candidates and output_reliable bit-exact, filled heights bit-exact (same cv2.inpaint
+    input).  The CUDA path is compared with this oracle on the same input in tests/test_round2_gpu.py."""
+    import ftp_oracle as FO
+    from parity_util import f14_case
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "f14_reference.npz"))
+    hm, rel, islands = f14_case(int(g["shape"][0]), int(g["shape"][1]))
+    P = FO.FtpParams()
+    assert [P.hole_nb, P.hole_frac, P.hole_min_dist, P.inpaint_radius] == [float(x) if i in (1, 2) else int(x) for i, x in enumerate(g["constants"])]
+    filled, cand, out_rel = FO.fill_internal_holes(hm, rel, P)
+    n = hm.size
+    want_c = np.unpackbits(g["candidates_packed"])[:n].reshape(hm.shape).astype(bool)
+    want_or = np.unpackbits(g["output_reliable_packed"])[:n].reshape(hm.shape).astype(bool)
+    assert 20 < int(want_c.sum()) < int((islands & rel).sum())                 # some islands are candidates, some are not
+    np.testing.assert_array_equal(cand, want_c)
+    np.testing.assert_array_equal(out_rel, want_or)
+    np.testing.assert_array_equal(filled[g["cand_y"], g["cand_x"]].view(np.uint32), g["cand_value"].view(np.uint32))
+    assert np.isfinite(g["cand_value"]).all()
