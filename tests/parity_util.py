@@ -73,3 +73,23 @@ def f14_case(h=1182, w=1182):
     holes |= ((xx - 590) ** 2 + (yy - 203) ** 2) <= 3 ** 2
     hm[holes & rel] = np.nan
     return hm, rel, holes
+
+
+def residue_case(n=320, levels=0, seed=3):
+    """A path-dependent unwrap input (tools/make_golden_unwrap.py, tests/test_oracle_golden.py): a smooth phase of
+    amplitude ~3 pi wrapped into (-pi, pi], two opposite phase singularities inside a disc mask with a hole, and a rugged
+    quality map -- quantised to `levels` values when levels > 0, so that the flood order is decided by the heap's
+    tie-breaking (-q, y, x, py, px) almost everywhere.  Returns (wrapped float32, mask bool, quality float32)."""
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:n, 0:n].astype(np.float32)
+    c = (n - 1) / 2.0
+    phase = 9.0 * np.exp(-(((xx - 0.45 * n) ** 2 + (yy - 0.55 * n) ** 2) / (2 * (0.18 * n) ** 2))) + 0.01 * xx
+    vort = np.arctan2(yy - (0.40 * n + 0.5), xx - (0.35 * n + 0.5)) - np.arctan2(yy - (0.62 * n + 0.5), xx - (0.70 * n + 0.5))
+    wrapped = np.angle(np.exp(1j * (phase.astype(np.float64) + vort))).astype(np.float32)
+    mask = ((xx - c) ** 2 + (yy - c) ** 2) <= (0.47 * n) ** 2
+    mask &= ~(((xx - 0.6 * n) ** 2 + (yy - 0.3 * n) ** 2) <= (0.05 * n) ** 2)                   # a hole: loops around it
+    q = np.exp(-(((xx - c) ** 2 + (yy - c) ** 2) / (2 * (0.4 * n) ** 2))).astype(np.float32)
+    q = (q * (1.0 + 0.2 * rng.standard_normal(q.shape))).astype(np.float32)
+    if levels > 0:
+        q = (np.round(q * levels) / levels).astype(np.float32)
+    return wrapped, mask, q

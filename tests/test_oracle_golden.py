@@ -156,3 +156,24 @@ def test_internal_hole_fill_equals_the_reference_functions():
     np.testing.assert_array_equal(out_rel, want_or)
     np.testing.assert_array_equal(filled[g["cand_y"], g["cand_x"]].view(np.uint32), g["cand_value"].view(np.uint32))
     assert np.isfinite(g["cand_value"]).all()
+
+
+@pytest.mark.parametrize("name,kw", [("rugged", dict(n=320, levels=0, seed=3)), ("ties64", dict(n=320, levels=64, seed=4)),
+                                      ("ties8", dict(n=256, levels=8, seed=5))])
+def test_unwrap_oracle_equals_the_reference_flood_where_the_path_matters(name, kw):
+    """F10 with phase residues, a hole in the mask and quality ties (13 ... 70 030 distinct quality values over
+    45 - 70 k pixels): the result depends on the exact pop order of the reference's heapq flood, i.e. on the tuple ordering
+    (-q, y, x, py, px) (shape_ftp.py:1043-1080).  The oracle's C heap must give the same wrap count on every pixel as
+    the field recorded from the UNMODIFIED reference (tools/make_golden_unwrap.py)."""
+    from parity_util import residue_case
+    g = np.load(os.path.join(G, "unwrap_reference.npz"))
+    wrapped, mask, q = residue_case(**kw)
+    u = F.unwrap_quality_guided(wrapped, mask, q)
+    np.testing.assert_array_equal(np.isfinite(u), mask)
+    k = np.zeros(wrapped.shape, np.int8)
+    k[mask] = np.rint((u[mask].astype(np.float64) - wrapped[mask]) / (2 * np.pi)).astype(np.int8)
+    want = g[name + "__k"]
+    assert int(np.abs(want).max()) >= 1 and int((k != want).sum()) == 0
+    sub = g[name + "__u_sub4"]
+    with np.errstate(invalid="ignore"):
+        assert float(np.nanmax(np.abs(u[::4, ::4] - sub))) <= 5e-5          # rad: float32 path sums vs libm, as in the chain goldens
