@@ -32,9 +32,9 @@ def frames(case, sc=None):
 
 CASES = ["demo_TEMP_DEMO", "demo_ROUND_METAL", "syn_3", "syn_15"]
 # round 2 (tools/make_golden_r2.py): phase amplitude up to 3 pi (wrap counts != 0), the three remaining demo pairs
-FTP_CASES = CASES + ["syn3pi_21", "syn3pi_56", "demo_E", "demo_F", "demo_P"]
+FTP_CASES = CASES + ["syn3pi_21", "syn3pi_56", "demo_E", "demo_F", "demo_P", "synflat_33"]      # synflat: no indentation, force 0
 # ... a hot temperature field (blend band, isotonic clip), tilted stripes (warpAffine path of the oriented blur)
-TEMP_CASES = CASES + ["synhot_9", "synhot_12", "syntilt_5", "syntilt_6", "demo_E", "demo_F", "demo_P"]
+TEMP_CASES = CASES + ["synhot_9", "synhot_12", "syntilt_5", "syntilt_6", "demo_E", "demo_F", "demo_P", "synflat_33"]
 
 
 def test_golden_environment(golden):

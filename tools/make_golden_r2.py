@@ -4,6 +4,7 @@ whose helpers this reuses), MERGED into tests/golden/reference_outputs.{npz,json
   syn3pi_<seed>   synthetic pairs with phase amplitude up to 3 pi (wrap counts k != 0 in the unwrap, F10)
   synhot_<seed>   temperature field up to T0 + 35 degC (reaches the 32-34 degC blend band of T11 and the isotonic clip)
   syntilt_<seed>  stripes tilted by 1.5 deg (carrier angle != 0: the warpAffine path of the oriented blur, T12)
+  synflat_33      an undeformed frame with its own noise (phase amplitude 0): empty contact_kept, zero force and volume
   demo_E/F/P      the three remaining demo pairs (alignment on, as shipped); a pair on which the reference itself
                   raises (ECC) is recorded as {"raises": "..."}
 
@@ -30,6 +31,7 @@ if __name__ == "__main__":
     cases.append(("synhot_12", dict(seed=12, dT_max=35.0), "temp"))
     cases.append(("syntilt_5", dict(seed=5, tilt_deg=1.5), "temp"))
     cases.append(("syntilt_6", dict(seed=6, tilt_deg=-2.0), "temp"))
+    cases.append(("synflat_33", dict(seed=33, reference=True), "both"))      # no indentation at all: the blob filter keeps nothing, force 0
     for name, gen, what in cases:
         if only and name not in only:
             continue
